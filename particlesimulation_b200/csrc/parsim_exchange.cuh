@@ -1,0 +1,306 @@
+// parsim_exchange.cuh -- row-strip exchange over NCCL (NVLink 5 / NVSwitch).
+// Re-expresses the reference's MPI decomposition (mpi/parsim-mpi.cpp:338-342 strips,
+// :670-815 centre-of-mass ghost rows, :512-600 particle migration) with SERIAL semantics:
+// the periodic wrap rows are really used (the MPI variant drops them), movers that
+// the list update leaves behind are collision-checked on the strip they came from, and
+// arrivals carry their global source cell so the destination list order is the serial one.
+//
+// Three exchange points per step, all neighbour-only (strip r <-> r-1, r+1, periodic):
+//   halo      after the centre of mass: one cell row (3 doubles per cell) each way
+//   emigrants after the list update:    removed movers whose new cell is in the other strip
+//   late      after the collisions:     surviving strays that left the strip + tombstones
+// Payloads are KB-scale; a record is 8 doubles.
+#pragma once
+#include <limits.h>
+
+#include "parsim_rank.cuh"
+
+namespace parsim {
+
+constexpr int kRec = 8;  // doubles per migrant record: x y vx vy m (id|src<<32) (cell|kind<<32) pad
+
+__device__ __forceinline__ double pack_u64(unsigned long long v) { return __longlong_as_double((long long)v); }
+__device__ __forceinline__ unsigned long long unpack_u64(double d) { return (unsigned long long)__double_as_longlong(d); }
+
+// direction of a global cell that is outside this strip: 0 = up (row0-1), 1 = down, -1 = far
+__device__ __forceinline__ int strip_dir(const Geom &g, int cell_global) {
+    int row = cell_global / g.nc;
+    if (row == (g.row0 - 1 + g.nc) % g.nc) return 0;
+    if (row == (g.row0 + g.rows) % g.nc) return 1;
+    return -1;
+}
+
+__device__ __forceinline__ void write_record(double *buf, int slot, double2 p, double2 v, double m,
+                                             unsigned id, int src_cell, int cell, int kind) {
+    double *r = buf + (size_t)slot * kRec;
+    r[0] = p.x; r[1] = p.y; r[2] = v.x; r[3] = v.y; r[4] = m;
+    r[5] = pack_u64((unsigned long long)id | ((unsigned long long)(unsigned)src_cell << 32));
+    r[6] = pack_u64((unsigned long long)(unsigned)cell | ((unsigned long long)(unsigned)kind << 32));
+    r[7] = 0.0;
+}
+
+// hdr[0] / hdr[1] = records for the strip above / below
+__global__ void k_pack_emigrants(Geom g, int n, int mig_cap, const unsigned char *__restrict__ flags,
+                                 const double2 *__restrict__ pos, const double2 *__restrict__ vel,
+                                 const double *__restrict__ m, const unsigned *__restrict__ id,
+                                 const int *__restrict__ cell, const int *__restrict__ newcell,
+                                 double *send_up, double *send_dn, int *hdr, Counters *ctr) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || !(flags[i] & F_EMIGRANT)) return;
+    int dir = strip_dir(g, newcell[i]);
+    if (dir < 0) { ctr->error = DE_LONG_JUMP; return; }
+    int slot = atomicAdd(&hdr[dir], 1);
+    if (slot >= mig_cap) { ctr->error = DE_MIGRANT_OVERFLOW; return; }
+    write_record(dir ? send_dn : send_up, slot, pos[i], vel[i], m[i], id[i], cell[i] + g.cell_base,
+                 newcell[i], 0);
+}
+
+// guests: removed movers that arrived from the neighbouring strips; they sit behind the
+// residents until the rebin and are linked into their destination cell's arrival bag.
+__global__ void k_unpack_guests(Geom g, int n_rec, const double *__restrict__ recv, int first_idx,
+                                int guest_first, double2 *pos, double2 *vel, double *m, unsigned *id,
+                                int *cell, int *newcell, unsigned char *flags, int *guest_src,
+                                int *arr_head, int *arr_next, Counters *ctr) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_rec) return;
+    const double *r = recv + (size_t)t * kRec;
+    unsigned long long a = unpack_u64(r[5]), b = unpack_u64(r[6]);
+    int idx = first_idx + t;
+    int dstg = (int)(unsigned)(b & 0xffffffffu);
+    int dst = dstg - g.cell_base;
+    if (dst < 0 || dst >= g.ncells) { ctr->error = DE_LONG_JUMP; return; }
+    pos[idx] = make_double2(r[0], r[1]);
+    vel[idx] = make_double2(r[2], r[3]);
+    m[idx] = r[4];
+    id[idx] = (unsigned)(a & 0xffffffffu);
+    cell[idx] = -1;
+    newcell[idx] = dstg;
+    flags[idx] = F_MOVER | F_REMOVED | F_GUEST;
+    guest_src[guest_first + t] = (int)(unsigned)(a >> 32);
+    arr_next[idx] = atomicExch(&arr_head[dst], idx);
+}
+
+// after the collisions: strays that survived but now lie in another strip (kind 0) and
+// tombstones of particles that died here but lie in another strip (kind 1)
+__global__ void k_pack_late(Geom g, int n, int mig_cap, const unsigned char *__restrict__ flags,
+                            const int *__restrict__ partner, const double2 *__restrict__ pos,
+                            const double2 *__restrict__ vel, const double *__restrict__ m,
+                            const unsigned *__restrict__ id, const int *__restrict__ newcell,
+                            double *send_up, double *send_dn, int *hdr, Counters *ctr) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n || (flags[i] & F_EMIGRANT)) return;
+    int c = newcell[i] - g.cell_base;
+    if (c >= 0 && c < g.ncells) return;
+    int dir = strip_dir(g, newcell[i]);
+    if (dir < 0) { ctr->error = DE_LONG_JUMP; return; }
+    int slot = atomicAdd(&hdr[dir], 1);
+    if (slot >= mig_cap) { ctr->error = DE_MIGRANT_OVERFLOW; return; }
+    write_record(dir ? send_dn : send_up, slot, pos[i], vel[i], m[i], id[i], 0, newcell[i],
+                 partner[i] >= 0 ? 1 : 0);
+}
+
+__global__ void k_unpack_late(Geom g, int n_rec, const double *__restrict__ recv, int first_idx,
+                              int inbox_first, double2 *pos, double2 *vel, double *m, unsigned *id,
+                              int *dst, int *count, int *dead_new_count, unsigned *inbox_id,
+                              int *inbox_cell, Counters *ctr) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_rec) return;
+    const double *r = recv + (size_t)t * kRec;
+    unsigned long long a = unpack_u64(r[5]), b = unpack_u64(r[6]);
+    int idx = first_idx + t;
+    int cg = (int)(unsigned)(b & 0xffffffffu);
+    int kind = (int)(b >> 32);
+    int c = cg - g.cell_base;
+    if (c < 0 || c >= g.ncells) { ctr->error = DE_LONG_JUMP; return; }
+    unsigned pid = (unsigned)(a & 0xffffffffu);
+    id[idx] = pid;
+    if (kind == 0) {
+        pos[idx] = make_double2(r[0], r[1]);
+        vel[idx] = make_double2(r[2], r[3]);
+        m[idx] = r[4];
+        dst[idx] = c;
+        atomicAdd(&count[c], 1);
+        inbox_cell[inbox_first + t] = INT_MIN / 2;  // not a tombstone
+        inbox_id[inbox_first + t] = pid;
+    } else {
+        dst[idx] = -1;
+        atomicAdd(&dead_new_count[c], 1);
+        inbox_cell[inbox_first + t] = cg;
+        inbox_id[inbox_first + t] = pid;
+    }
+}
+
+// ---- host side -----------------------------------------------------------------------------
+struct ExchangeBufs {  // hangs off Rank through these statics-free helpers
+};
+
+#define PS_NCCL(c, call)                                                                   \
+    do {                                                                                   \
+        int r__ = (call);                                                                  \
+        if (r__ != 0)                                                                      \
+            return (c)->fail(std::string(#call) + ": " + nccl_api().GetErrorString(r__));  \
+    } while (0)
+
+inline int exchange_create(Rank *c, const unsigned char *nccl_id) {
+    NcclApi &api = nccl_api();
+    if (!api.load()) return c->fail(api.error);
+    if (!nccl_id) return c->fail("multi-rank context needs the NCCL unique id of rank 0");
+    NcclUniqueId id;
+    memcpy(id.internal, nccl_id, sizeof(id.internal));
+    PS_NCCL(c, api.CommInitRank(&c->comm.comm, c->nranks, id, c->rank));
+    c->up = (c->rank - 1 + c->nranks) % c->nranks;
+    c->dn = (c->rank + 1) % c->nranks;
+    const size_t rec = (size_t)c->mig_cap * kRec;
+    for (int d = 0; d < 2; d++) {
+        if (cudaMalloc((void **)&c->mig_send[d], rec * sizeof(double)) != cudaSuccess ||
+            cudaMalloc((void **)&c->mig_recv[d], rec * sizeof(double)) != cudaSuccess)
+            return c->fail("cudaMalloc of migrant buffers failed");
+    }
+    // hdr_send[0..1], hdr_recv[0..1]; inbox arrays behind guest_src
+    if (cudaMalloc((void **)&c->mig_hdr_send, 4 * sizeof(int)) != cudaSuccess)
+        return c->fail("cudaMalloc failed");
+    c->mig_hdr_recv = c->mig_hdr_send + 2;
+    if (cudaMalloc((void **)&c->guest_src, sizeof(int) * 6 * (size_t)c->mig_cap) != cudaSuccess)
+        return c->fail("cudaMalloc failed");
+    if (cudaMallocHost((void **)&c->h_mig_hdr, 4 * sizeof(int)) != cudaSuccess)
+        return c->fail("cudaMallocHost failed");
+    return 0;
+}
+
+inline void exchange_destroy(Rank *c) {
+    if (c->comm.comm) nccl_api().CommDestroy(c->comm.comm);
+    c->comm.comm = nullptr;
+    for (int d = 0; d < 2; d++) {
+        if (c->mig_send[d]) cudaFree(c->mig_send[d]);
+        if (c->mig_recv[d]) cudaFree(c->mig_recv[d]);
+    }
+    if (c->mig_hdr_send) cudaFree(c->mig_hdr_send);
+    if (c->h_mig_hdr) cudaFreeHost(c->h_mig_hdr);
+}
+
+inline int *inbox_cell_ptr(Rank *c) { return c->guest_src + 2 * (size_t)c->mig_cap; }
+inline unsigned *inbox_id_ptr(Rank *c) { return (unsigned *)(c->guest_src + 4 * (size_t)c->mig_cap); }
+
+// Ghost rows.  Receives are posted "from below" first so that with two strips (both
+// neighbours are the same peer) sends and receives pair up in issue order: what I send up is
+// the peer's row from below.
+inline int exchange_halo(Rank *c) {
+    NcclApi &api = nccl_api();
+    const Geom &g = c->g;
+    const size_t nc = (size_t)g.nc;
+    timed_begin(c, K_GHOST, 48.0 * nc);
+    PS_NCCL(c, api.GroupStart());
+    PS_NCCL(c, api.Send(c->com_xy + nc, 2 * nc, kNcclFloat64, c->up, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Send(c->com_m + nc, nc, kNcclFloat64, c->up, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Send(c->com_xy + g.rows * nc, 2 * nc, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Send(c->com_m + g.rows * nc, nc, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Recv(c->com_xy + (g.rows + 1) * nc, 2 * nc, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Recv(c->com_m + (g.rows + 1) * nc, nc, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Recv(c->com_xy, 2 * nc, kNcclFloat64, c->up, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Recv(c->com_m, nc, kNcclFloat64, c->up, c->comm.comm, c->stream));
+    PS_NCCL(c, api.GroupEnd());
+    timed_end(c);
+    return 0;
+}
+
+// Ship hdr_send[0] records up and hdr_send[1] records down; learn how many arrive.
+// recv[1] holds what came from below, recv[0] what came from above.
+inline int exchange_records(Rank *c, int *from_up, int *from_dn) {
+    NcclApi &api = nccl_api();
+    PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr, c->mig_hdr_send, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PS_NCCL(c, api.GroupStart());
+    PS_NCCL(c, api.Send(c->mig_hdr_send + 0, 1, kNcclInt32, c->up, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Send(c->mig_hdr_send + 1, 1, kNcclInt32, c->dn, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Recv(c->mig_hdr_recv + 1, 1, kNcclInt32, c->dn, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Recv(c->mig_hdr_recv + 0, 1, kNcclInt32, c->up, c->comm.comm, c->stream));
+    PS_NCCL(c, api.GroupEnd());
+    PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr + 2, c->mig_hdr_recv, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error) +
+                                        " (2 = particle jumped past the neighbouring strip, 3 = migrant buffer overflow)");
+    const int su = c->h_mig_hdr[0], sd = c->h_mig_hdr[1], ru = c->h_mig_hdr[2], rd = c->h_mig_hdr[3];
+    if (ru > c->mig_cap || rd > c->mig_cap) return c->fail("migrant buffer overflow on receive");
+    c->stats.migrants += su + sd;
+    if (su + sd + ru + rd > 0) {
+        PS_NCCL(c, api.GroupStart());
+        if (su) PS_NCCL(c, api.Send(c->mig_send[0], (size_t)su * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
+        if (sd) PS_NCCL(c, api.Send(c->mig_send[1], (size_t)sd * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+        if (rd) PS_NCCL(c, api.Recv(c->mig_recv[1], (size_t)rd * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+        if (ru) PS_NCCL(c, api.Recv(c->mig_recv[0], (size_t)ru * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
+        PS_NCCL(c, api.GroupEnd());
+    }
+    *from_up = ru;
+    *from_dn = rd;
+    return 0;
+}
+
+inline int exchange_emigrants(Rank *c) {
+    const Geom &g = c->g;
+    timed_begin(c, K_MIGRATE, 0);
+    PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 2 * sizeof(int), c->stream));
+    k_pack_emigrants<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
+        g, c->n_alive, c->mig_cap, c->flags, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->cell_cur,
+        c->newcell, c->mig_send[0], c->mig_send[1], c->mig_hdr_send, c->d_ctr);
+    int ru = 0, rd = 0;
+    if (exchange_records(c, &ru, &rd)) return 1;
+    if (c->n_alive + ru + rd > c->cap) return c->fail("strip capacity exceeded by arriving particles");
+    int first = c->n_alive;
+    if (ru)
+        k_unpack_guests<<<grid_for(ru), kThreads, 0, c->stream>>>(
+            g, ru, c->mig_recv[0], first, 0, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->cell_cur,
+            c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->d_ctr);
+    if (rd)
+        k_unpack_guests<<<grid_for(rd), kThreads, 0, c->stream>>>(
+            g, rd, c->mig_recv[1], first + ru, ru, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur,
+            c->cell_cur, c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->d_ctr);
+    timed_end(c);
+    c->n_guest = ru + rd;
+    return check_launch(c, "exchange_emigrants");
+}
+
+inline int exchange_late(Rank *c, int grave_first, int deaths, int *n_src, int *inbox) {
+    (void)grave_first; (void)deaths;
+    const Geom &g = c->g;
+    const int n_tot = c->n_alive + c->n_guest;
+    timed_begin(c, K_MIGRATE, 0);
+    PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 2 * sizeof(int), c->stream));
+    k_pack_late<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
+        g, n_tot, c->mig_cap, c->flags, c->partner, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur,
+        c->newcell, c->mig_send[0], c->mig_send[1], c->mig_hdr_send, c->d_ctr);
+    int ru = 0, rd = 0;
+    if (exchange_records(c, &ru, &rd)) return 1;
+    if (n_tot + ru + rd > c->cap) return c->fail("strip capacity exceeded by arriving particles");
+    if (ru)
+        k_unpack_late<<<grid_for(ru), kThreads, 0, c->stream>>>(
+            g, ru, c->mig_recv[0], n_tot, 0, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->dst,
+            c->count, c->dead_new_count, inbox_id_ptr(c), inbox_cell_ptr(c), c->d_ctr);
+    if (rd)
+        k_unpack_late<<<grid_for(rd), kThreads, 0, c->stream>>>(
+            g, rd, c->mig_recv[1], n_tot + ru, ru, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->dst,
+            c->count, c->dead_new_count, inbox_id_ptr(c), inbox_cell_ptr(c), c->d_ctr);
+    timed_end(c);
+    *n_src = n_tot + ru + rd;
+    *inbox = ru + rd;
+    return check_launch(c, "exchange_late");
+}
+
+inline int exchange_append_tombstones(Rank *c, int inbox_cnt) {
+    k_dead_append<<<grid_for(inbox_cnt), kThreads, 0, c->stream>>>(
+        c->g, inbox_cnt, inbox_id_ptr(c), inbox_cell_ptr(c), c->dead_start_alt, c->dead_new_count,
+        c->dead_id_alt, c->dead_cell_alt);
+    return check_launch(c, "k_dead_append(inbox)");
+}
+
+// sum of 4 doubles over all strips (particle 0 position, found flag, collisions)
+inline int exchange_allreduce4(Rank *c, double v[4]) {
+    NcclApi &api = nccl_api();
+    double *d = c->mig_send[0];
+    PS_CUDA(c, cudaMemcpyAsync(d, v, 4 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+    PS_NCCL(c, api.AllReduce(d, d, 4, kNcclFloat64, kNcclSum, c->comm.comm, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(v, d, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+}  // namespace parsim

@@ -1,0 +1,623 @@
+// parsim_kernels.cuh -- hand-written FP64 CUDA kernels (sm_100a) for the per-timestep loop of
+// `parsim` (reference: serial/parsim.cpp:422-448).  No tensor cores: nothing here is a dense
+// contraction.  Layout, roofline and algorithmic bytes of every kernel are in DESIGN.md.
+//
+// Device data model (one row strip of the grid per GPU):
+//   alive particles only, sorted by (cell, id):  pos (double2 x,y), vel (double2 vx,vy),
+//   m (double), id (u32), cell (local cell, int);  cell_start[C+1] is the CSR over cells.
+//   Dead particles are compacted out every step and leave a tombstone (cell, id) in a second
+//   CSR, because the reference keeps them in its per-cell lists where they decide which movers
+//   the list update leaves behind (serial/parsim.cpp:242-254).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace parsim {
+
+// serial/parsim.cpp:13-16
+constexpr double kG = 6.67408e-11;
+constexpr double kEpsilon = 0.005;
+constexpr double kDeltaT = 0.1;
+
+constexpr int kThreads = 256;
+
+// per-particle flags written by the list-update kernel
+enum : unsigned char {
+    F_MOVER = 1,    // position cell changed in this step (serial/parsim.cpp:183)
+    F_REMOVED = 2,  // list update moved it to the new cell's list (:250-251); mover && !removed = stray
+    F_EMIGRANT = 4, // removed mover whose new cell belongs to another strip (sent before collisions)
+    F_GUEST = 8,    // arrived from another strip this step (lives past n_alive until the rebin)
+};
+
+struct Geom {
+    double side;   // side_length
+    double cellw;  // side_length / grid_size, the divisor of serial/parsim.cpp:160-161,:268-269
+    int nc;        // grid_size (cells per side)
+    int row0;      // first global grid row of this strip
+    int rows;      // rows in this strip
+    int ncells;    // rows * nc
+    int cell_base; // row0 * nc : global cell index = local + cell_base
+};
+
+struct Counters {  // one per context, device memory, copied to the host once per step
+    unsigned long long collisions;
+    unsigned long long force_pairs;
+    unsigned long long collision_pairs;
+    unsigned long long movers;
+    unsigned long long strays;
+    int deaths_step;     // particles that died in this step's collision phase
+    int grave_count;     // entries in the graveyard (all dead so far, this strip)
+    int n_emigrants_up;  // removed movers sent to the strip above / below (pre-collision)
+    int n_emigrants_dn;
+    int n_late_up;       // surviving strays + tombstones sent after the collision phase
+    int n_late_dn;
+    int n_next;          // alive residents after this step's rebin
+    int error;           // sticky device-side error code (capacity overflow, long jump, ...)
+    int n_staged;        // upload cursor for multi-rank ingest
+    int pad;
+};
+
+enum DeviceError { DE_NONE = 0, DE_CAPACITY = 1, DE_LONG_JUMP = 2, DE_MIGRANT_OVERFLOW = 3 };
+
+// ---------------------------------------------------------------------------------------
+// cell of a position: (int)(x / (side/ncside)) with a true IEEE division by the quotient,
+// serial/parsim.cpp:160-163,:174-177,:268-272.  The reference leaves an out-of-range cell
+// to a [PANIC] print / UB (:276-280); here it is clamped so memory stays safe.
+__device__ __forceinline__ int cell_coord(double v, const Geom &g) {
+    int c = __double2int_rz(__ddiv_rn(v, g.cellw));
+    return min(max(c, 0), g.nc - 1);
+}
+__device__ __forceinline__ int global_cell(double2 p, const Geom &g) {
+    return cell_coord(p.y, g) * g.nc + cell_coord(p.x, g);
+}
+
+// ---------------------------------------------------------------------------------------
+// Upload: interleave host SoA (x,y,vx,vy,m) into the device layout and keep the particles of
+// this strip.  Slot order is irrelevant: the first rebin orders every cell by id.
+__global__ void k_ingest(Geom g, long long id_base, int count, const double *__restrict__ x,
+                         const double *__restrict__ y, const double *__restrict__ vx,
+                         const double *__restrict__ vy, const double *__restrict__ m,
+                         int single_rank, int capacity, double2 *pos, double2 *vel, double *mass,
+                         unsigned *id, Counters *ctr) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    double2 p = make_double2(x[t], y[t]);
+    int slot;
+    if (single_rank) {
+        slot = (int)(id_base + t);
+    } else {
+        int row = cell_coord(p.y, g);
+        if (row < g.row0 || row >= g.row0 + g.rows) return;
+        slot = atomicAdd(&ctr->n_staged, 1);
+        if (slot >= capacity) { ctr->error = DE_CAPACITY; return; }
+    }
+    pos[slot] = p;
+    vel[slot] = make_double2(vx[t], vy[t]);
+    mass[slot] = m[t];
+    id[slot] = (unsigned)(id_base + t);
+}
+
+// ---------------------------------------------------------------------------------------
+// Binning keys for particles in arbitrary order (step 0, or the full_rebin option):
+// dst[i] = local cell of the current position, histogram into count[] (north_star (a)).
+__global__ void k_bin_keys(Geom g, int n, const double2 *__restrict__ pos, int *__restrict__ dst,
+                           int *count) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int c = global_cell(pos[i], g) - g.cell_base;
+    dst[i] = c;  // uploads are filtered by strip, so 0 <= c < ncells
+    atomicAdd(&count[c], 1);
+}
+
+// ---------------------------------------------------------------------------------------
+// Device-wide exclusive scan of int counts (three small kernels; the data is 4 B per CELL,
+// not per particle).  out has N+1 entries, out[N] = total.
+constexpr int kScanItems = 8;
+constexpr int kScanTile = kThreads * kScanItems;
+
+__device__ __forceinline__ int block_exclusive_scan(int v, int *warp_sums, int &block_total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int inc = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += t;
+    }
+    if (lane == 31) warp_sums[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+        int w = lane < (kThreads / 32) ? warp_sums[lane] : 0;
+        int winc = w;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            int t = __shfl_up_sync(0xffffffffu, winc, o);
+            if (lane >= o) winc += t;
+        }
+        if (lane < (kThreads / 32)) warp_sums[lane] = winc - w;  // exclusive warp offsets
+        if (lane == 31) warp_sums[32] = winc;                    // block total
+    }
+    __syncthreads();
+    block_total = warp_sums[32];
+    int r = warp_sums[warp] + inc - v;
+    __syncthreads();
+    return r;
+}
+
+__global__ void k_scan_tile_sums(const int *__restrict__ in, const int *__restrict__ in2, int N,
+                                 int *tile_sums) {
+    __shared__ int ws[33];
+    int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    int s = 0;
+#pragma unroll
+    for (int j = 0; j < kScanItems; j++) {
+        int k = base + j;
+        if (k < N) s += in[k] + (in2 ? in2[k] : 0);
+    }
+    int tot;
+    block_exclusive_scan(s, ws, tot);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+}
+
+__global__ void k_scan_top(int *tile_sums, int ntiles, int *total_out, int *total_out2) {
+    __shared__ int ws[33];
+    int carry = 0;
+    for (int base = 0; base < ntiles; base += kThreads) {
+        int k = base + threadIdx.x;
+        int v = k < ntiles ? tile_sums[k] : 0;
+        int tot;
+        int ex = block_exclusive_scan(v, ws, tot);
+        if (k < ntiles) tile_sums[k] = carry + ex;
+        carry += tot;
+    }
+    if (threadIdx.x == 0) {
+        *total_out = carry;
+        if (total_out2) *total_out2 = carry;
+    }
+}
+
+// in2 (optional) is added element-wise to in: used for tombstones (old + new counts)
+__global__ void k_scan_apply(const int *__restrict__ in, const int *__restrict__ in2, int N,
+                             const int *__restrict__ tile_sums, int *__restrict__ out) {
+    __shared__ int ws[33];
+    int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    int v[kScanItems];
+    int s = 0;
+#pragma unroll
+    for (int j = 0; j < kScanItems; j++) {
+        int k = base + j;
+        v[j] = k < N ? in[k] + (in2 ? in2[k] : 0) : 0;
+        s += v[j];
+    }
+    int tot;
+    int ex = block_exclusive_scan(s, ws, tot) + tile_sums[blockIdx.x];
+#pragma unroll
+    for (int j = 0; j < kScanItems; j++) {
+        int k = base + j;
+        if (k < N) out[k] = ex;
+        ex += v[j];
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Rebin, pass 1: claim a slot inside the destination cell's segment.  The claim order is
+// arbitrary (atomics); pass 2 orders each cell by id, so the final layout is deterministic.
+// count[] is consumed back to zero by the atomicSub, so it needs no memset per step.
+__global__ void k_rebin_scatter(int n_src, const int *__restrict__ dst,
+                                const unsigned *__restrict__ id, const int *__restrict__ start,
+                                int *count, int *__restrict__ tmp_src, unsigned *__restrict__ tmp_id,
+                                int *__restrict__ cell_out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_src) return;
+    int c = dst[i];
+    if (c < 0) return;  // dead, or emigrated to another strip
+    int slot = start[c + 1] - atomicSub(&count[c], 1);
+    tmp_src[slot] = i;
+    tmp_id[slot] = id[i];
+    cell_out[slot] = c;
+}
+
+// Rebin, pass 2: rank by id inside the cell (the reference's bin-time list order is ascending
+// particle index, serial/parsim.cpp:265,:285) and move the 44-byte state once.
+__global__ void k_rebin_gather(const int *__restrict__ n_out_ptr, const int *__restrict__ cell_out,
+                               const int *__restrict__ start, const int *__restrict__ tmp_src,
+                               const unsigned *__restrict__ tmp_id,
+                               const double2 *__restrict__ pos_in, const double2 *__restrict__ vel_in,
+                               const double *__restrict__ m_in, double2 *__restrict__ pos_out,
+                               double2 *__restrict__ vel_out, double *__restrict__ m_out,
+                               unsigned *__restrict__ id_out) {
+    int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= *n_out_ptr) return;
+    int c = cell_out[p];
+    unsigned me = tmp_id[p];
+    int s = start[c], e = start[c + 1];
+    int rank = 0;
+    for (int q = s; q < e; q++) rank += (tmp_id[q] < me) ? 1 : 0;
+    int o = s + rank;
+    int src = tmp_src[p];
+    pos_out[o] = pos_in[src];
+    vel_out[o] = vel_in[src];
+    m_out[o] = m_in[src];
+    id_out[o] = me;
+}
+
+// ---------------------------------------------------------------------------------------
+// Centre of mass per cell (north_star (b); Cell::addParticle, serial/parsim.cpp:93-106 computes
+// the same weighted mean as a running average).  LANES lanes per cell, each lane sums a fixed
+// strided subsequence, then a fixed xor-shuffle tree: the order of additions depends only on
+// the cell's (id-sorted) contents, never on scheduling or on the number of GPUs.
+// com_xy / com_m carry one ghost row above and below the strip: index = (local_row+1)*nc + gx.
+template <int LANES>
+__global__ void k_com(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
+                      const int *__restrict__ cell_start, double2 *__restrict__ com_xy,
+                      double *__restrict__ com_m, unsigned long long *force_pairs) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    int c = t / LANES, lane = t % LANES;
+    int s = 0, e = 0;
+    if (c < g.ncells) { s = cell_start[c]; e = cell_start[c + 1]; }
+    double M = 0, Mx = 0, My = 0;
+    for (int k = s + lane; k < e; k += LANES) {
+        double mk = m[k];
+        double2 p = pos[k];
+        M += mk;
+        Mx = fma(mk, p.x, Mx);
+        My = fma(mk, p.y, My);
+    }
+#pragma unroll
+    for (int o = LANES / 2; o > 0; o >>= 1) {
+        M += __shfl_xor_sync(0xffffffffu, M, o);
+        Mx += __shfl_xor_sync(0xffffffffu, Mx, o);
+        My += __shfl_xor_sync(0xffffffffu, My, o);
+    }
+    if (lane == 0 && c < g.ncells) {
+        double2 r = make_double2(0.0, 0.0);
+        if (M > 0) r = make_double2(Mx / M, My / M);
+        com_xy[c + g.nc] = r;
+        com_m[c + g.nc] = M;
+        if (force_pairs) {
+            unsigned long long a = (unsigned long long)(e - s);
+            if (a > 1) atomicAdd(force_pairs, a * (a - 1));
+        }
+    }
+}
+
+// Single strip: the ghost rows are the strip's own last / first row (periodic wrap,
+// serial/parsim.cpp:332-333).  Multi-strip runs fill them over NCCL instead.
+__global__ void k_ghost_wrap(Geom g, double2 *com_xy, double *com_m) {
+    int gx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gx >= g.nc) return;
+    com_xy[gx] = com_xy[g.rows * g.nc + gx];
+    com_m[gx] = com_m[g.rows * g.nc + gx];
+    com_xy[(g.rows + 1) * g.nc + gx] = com_xy[g.nc + gx];
+    com_m[(g.rows + 1) * g.nc + gx] = com_m[g.nc + gx];
+}
+
+// ---------------------------------------------------------------------------------------
+// Forces + integration, fused (north_star (c)+(d)).
+//   own cell : direct pair sum over the cell's particles (serial/parsim.cpp:356-366,:127-148)
+//              -- the own cell's centre of mass is never a source (:305)
+//   8 others : centre of mass, shifted by +-side across the periodic border (:301-354,:109-125)
+//   then applyForce (:150-195): a = f/m, x += v dt + a dt^2/2, v += a dt, fmod wrap, new cell.
+// The force on i is G m_i sum_k m_k d_k/|d_k|^3, so a_i = G sum_k m_k d_k/|d_k|^3 needs no
+// division by m_i; |d|^-3 comes from one FP64 rsqrt instead of the reference's sqrt + 3
+// divisions (ulp-level differences).  Coincident points (d == 0, including
+// k == i) contribute nothing, as in :134-137.  The integration itself keeps the reference's
+// rounding sequence exactly (no FMA contraction).
+// Pre-move positions are read from pos_in by every thread of the cell, so post-move
+// positions go to pos_out.
+__device__ __forceinline__ void accumulate(double dx, double dy, double mk, double &ax, double &ay) {
+    double d2 = fma(dx, dx, dy * dy);
+    double r = d2 > 0.0 ? rsqrt(d2) : 0.0;
+    double w = mk * r * r * r;
+    ax = fma(w, dx, ax);
+    ay = fma(w, dy, ay);
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
+                  const double *__restrict__ m, const int *__restrict__ cell,
+                  const int *__restrict__ cell_start, const double2 *__restrict__ com_xy,
+                  const double *__restrict__ com_m, double2 *__restrict__ pos_out,
+                  double2 *__restrict__ vel, int *__restrict__ newcell, double2 *__restrict__ dbg_acc) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int c = cell[i];
+    const double2 p = pos_in[i];
+    const int s = cell_start[c], e = cell_start[c + 1];
+    double ax = 0.0, ay = 0.0;
+#pragma unroll 4
+    for (int k = s; k < e; k++) {
+        double2 q = __ldg(&pos_in[k]);
+        double mk = __ldg(&m[k]);
+        accumulate(q.x - p.x, q.y - p.y, mk, ax, ay);
+    }
+    const int lrow = c / g.nc;
+    const int gx = c - lrow * g.nc;
+    const int grow = g.row0 + lrow;
+#pragma unroll
+    for (int dxn = -1; dxn <= 1; dxn++) {
+        int nx = gx + dxn;
+        double sx = 0.0;
+        if (nx >= g.nc) sx = g.side; else if (nx < 0) sx = -g.side;
+        nx = (nx + g.nc) % g.nc;
+#pragma unroll
+        for (int dyn = -1; dyn <= 1; dyn++) {
+            if (dxn == 0 && dyn == 0) continue;
+            int ny = grow + dyn;
+            double sy = 0.0;
+            if (ny >= g.nc) sy = g.side; else if (ny < 0) sy = -g.side;
+            int q = (lrow + dyn + 1) * g.nc + nx;
+            double2 cm = __ldg(&com_xy[q]);
+            double M = __ldg(&com_m[q]);
+            accumulate((sx + cm.x) - p.x, (sy + cm.y) - p.y, M, ax, ay);
+        }
+    }
+    ax *= kG;
+    ay *= kG;
+    if (dbg_acc) dbg_acc[i] = make_double2(ax, ay);
+
+    // Particle::updatePositionAndVelocity, serial/parsim.cpp:54-60, same rounding sequence
+    double2 v = vel[i];
+    double x = __dadd_rn(p.x, __dadd_rn(__dmul_rn(v.x, kDeltaT),
+                                        __dmul_rn(__dmul_rn(__dmul_rn(0.5, ax), kDeltaT), kDeltaT)));
+    double y = __dadd_rn(p.y, __dadd_rn(__dmul_rn(v.y, kDeltaT),
+                                        __dmul_rn(__dmul_rn(__dmul_rn(0.5, ay), kDeltaT), kDeltaT)));
+    v.x = __dadd_rn(v.x, __dmul_rn(ax, kDeltaT));
+    v.y = __dadd_rn(v.y, __dmul_rn(ay, kDeltaT));
+    x = fmod(__dadd_rn(x, g.side), g.side);  // :171-172
+    y = fmod(__dadd_rn(y, g.side), g.side);
+    double2 pn = make_double2(x, y);
+    pos_out[i] = pn;
+    vel[i] = v;
+    newcell[i] = global_cell(pn, g);          // :174-177
+}
+
+// ---------------------------------------------------------------------------------------
+// List update (updateCellParticles, serial/parsim.cpp:234-259).  The reference erases at the
+// loop position and still advances it (:251-253): inside a run of consecutive leavers of a
+// cell's bin-time list, run positions 0,2,4,... are moved to their new cell's list and
+// 1,3,5,... stay listed in the old cell for this step's collision phase ("strays").
+// The bin-time list is id-ordered and contains dead placeholders, which break runs; the
+// alive part of it is exactly this cell's segment, the dead part is the tombstone CSR.
+__device__ __forceinline__ bool tombstone_between(const int *__restrict__ dead_start,
+                                                  const unsigned *__restrict__ dead_id, int c,
+                                                  unsigned lo, unsigned hi) {
+    if (!dead_start) return false;
+    for (int e = dead_start[c], end = dead_start[c + 1]; e < end; e++) {
+        unsigned d = dead_id[e];
+        if (d > lo && d < hi) return true;
+    }
+    return false;
+}
+
+__global__ void k_classify(Geom g, int n, const int *__restrict__ cell,
+                           const int *__restrict__ cell_start, const int *__restrict__ newcell,
+                           const unsigned *__restrict__ id, const int *__restrict__ dead_start,
+                           const unsigned *__restrict__ dead_id, unsigned char *__restrict__ flags,
+                           int *arr_head, int *__restrict__ arr_next, Counters *ctr) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int c = cell[i];
+    const int cg = c + g.cell_base;
+    const int dstg = newcell[i];
+    if (dstg == cg) { flags[i] = 0; return; }
+    // length of the run of consecutive leavers that ends just before i
+    int run = 0;
+    const int s = cell_start[c];
+    for (int t = i - 1; t >= s; t--) {
+        if (newcell[t] == cg) break;
+        if (tombstone_between(dead_start, dead_id, c, id[t], id[t + 1])) break;
+        run++;
+    }
+    const bool removed = (run & 1) == 0;
+    unsigned char f = F_MOVER;
+    if (removed) {
+        f |= F_REMOVED;
+        int dst = dstg - g.cell_base;
+        if (dst >= 0 && dst < g.ncells) {
+            arr_next[i] = atomicExch(&arr_head[dst], i);  // unordered bag; order comes from keys
+        } else {
+            f |= F_EMIGRANT;
+        }
+    } else {
+        atomicAdd(&ctr->strays, 1ull);
+    }
+    atomicAdd(&ctr->movers, 1ull);
+    flags[i] = f;
+}
+
+// ---------------------------------------------------------------------------------------
+// Collisions (checkCollisions, serial/parsim.cpp:388-420).  The reference sweeps each cell's
+// post-move list greedily (j ascending, k > j ascending) and counts a close pair iff neither
+// member is in the cell's set yet (:404-409); every member of any close pair dies (:414-418).
+// Equivalent order-free rule: with first(j) = the earliest list entry that is close to j,
+// a collision is counted exactly for the pairs with first(j) = k and first(k) = j.
+// "Earliest" is decided by a 64-bit list key instead of a memory position:
+//   stayers and strays keep their bin-time place  -> key = id
+//   arrivals are appended by (source cell, id)    -> key = 1<<63 | source cell << 32 | id
+// close(j,k) <=> sqrt(dx*dx + dy*dy) < EPSILON (:76-79,:400) <=> dx*dx + dy*dy < thr2 where
+// thr2 is the smallest double whose correctly rounded sqrt is >= EPSILON (host-computed), and
+// the sum is rounded exactly like the reference's (no FMA).
+__device__ __forceinline__ unsigned long long list_key(unsigned char f, int src_cell_global,
+                                                       unsigned id) {
+    if (f & F_REMOVED)
+        return (1ull << 63) | ((unsigned long long)(unsigned)src_cell_global << 32) | id;
+    return id;
+}
+
+__device__ __forceinline__ bool is_close(double2 a, double2 b, double thr2) {
+    double dx = a.x - b.x, dy = a.y - b.y;
+    return __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)) < thr2;
+}
+
+// n = residents (+ guests that arrived from other strips, which have cell[i] = -1 and carry
+// their source cell in guest_src[i - n_res]).
+__global__ void __launch_bounds__(kThreads)
+k_collide_find(Geom g, int n, int n_res, double thr2, const double2 *__restrict__ pos,
+               const int *__restrict__ cell, const int *__restrict__ cell_start,
+               const int *__restrict__ newcell, const unsigned *__restrict__ id,
+               const unsigned char *__restrict__ flags, const int *__restrict__ arr_head,
+               const int *__restrict__ arr_next, const int *__restrict__ guest_src,
+               int *__restrict__ partner, unsigned long long *collision_pairs) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const unsigned char f = flags[i];
+    if (f & F_EMIGRANT) { partner[i] = -1; return; }  // checked on the strip it moved to
+    const int L = (f & F_REMOVED) ? newcell[i] - g.cell_base : cell[i];
+    const double2 p = pos[i];
+    unsigned long long best = ~0ull;
+    int best_idx = -1;
+    const int s = cell_start[L], e = cell_start[L + 1];
+    // residents of L that are still listed there (stayers and strays), key = id, id-sorted
+#pragma unroll 4
+    for (int k = s; k < e; k++) {
+        double2 q = __ldg(&pos[k]);
+        unsigned char fk = __ldg(&flags[k]);
+        if (is_close(p, q, thr2) && k != i && !(fk & F_REMOVED)) {
+            unsigned long long key = id[k];
+            if (key < best) { best = key; best_idx = k; }
+        }
+    }
+    // arrivals appended to L's list
+    int walked = 0;
+    for (int k = arr_head[L]; k >= 0; k = arr_next[k]) {
+        walked++;
+        if (k == i) continue;
+        if (is_close(p, pos[k], thr2)) {
+            int src = k < n_res ? cell[k] + g.cell_base : guest_src[k - n_res];
+            unsigned long long key = list_key(F_REMOVED, src, id[k]);
+            if (key < best) { best = key; best_idx = k; }
+        }
+    }
+    partner[i] = best_idx;
+    if (collision_pairs) atomicAdd(collision_pairs, (unsigned long long)(e - s + walked));
+}
+
+// Count the mutual-first pairs, retire every particle that has any close partner, and
+// histogram the survivors by their new cell for the rebin (stream compaction, north_star (e)).
+// The dead go to the graveyard (frozen state for parsim_result / dumps) and, as (cell, id)
+// tombstones, to the dead CSR of the cell they now lie in.
+__global__ void __launch_bounds__(kThreads)
+k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner,
+          const int *__restrict__ newcell, const unsigned char *__restrict__ flags,
+          const double2 *__restrict__ pos, const double2 *__restrict__ vel,
+          const unsigned *__restrict__ id, int *__restrict__ dst, int *count, int *dead_new_count,
+          double2 *__restrict__ grave_pos, double2 *__restrict__ grave_vel,
+          unsigned *__restrict__ grave_id, int *__restrict__ grave_cell, Counters *ctr) {
+    __shared__ unsigned warp_cnt[kThreads / 32];
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned mine = 0;
+    if (i < n) {
+        const unsigned char f = flags[i];
+        int d = -1;
+        if (!(f & F_EMIGRANT)) {
+            const int p = partner[i];
+            const int cell_now = newcell[i] - g.cell_base;  // cell of the post-move position
+            if (p >= 0) {
+                if (partner[p] == i && i < p) mine = 1;
+                int slot = atomicAdd(&ctr->grave_count, 1);
+                grave_pos[slot] = pos[i];
+                grave_vel[slot] = vel[i];
+                grave_id[slot] = id[i];
+                grave_cell[slot] = newcell[i];  // global; tombstones of other strips are shipped
+                atomicAdd(&ctr->deaths_step, 1);
+                if (cell_now >= 0 && cell_now < g.ncells) atomicAdd(&dead_new_count[cell_now], 1);
+            } else if (cell_now >= 0 && cell_now < g.ncells) {
+                d = cell_now;
+                atomicAdd(&count[d], 1);
+            }
+            // else: surviving stray that left the strip -> sent by the late exchange
+        }
+        dst[i] = d;
+    }
+    unsigned w = __reduce_add_sync(0xffffffffu, mine);
+    if ((threadIdx.x & 31) == 0) warp_cnt[threadIdx.x >> 5] = w;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned tot = 0;
+#pragma unroll
+        for (int k = 0; k < kThreads / 32; k++) tot += warp_cnt[k];
+        if (tot) atomicAdd(&ctr->collisions, (unsigned long long)tot);
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// Tombstone CSR update: new = old entries (kept in place order) + this step's deaths.
+__global__ void k_add_counts(int n, int *__restrict__ acc, const int *__restrict__ add) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < n) acc[c] += add[c];
+}
+
+__global__ void k_dead_copy_old(int n_old_bound, const int *__restrict__ old_start, int ncells,
+                                const int *__restrict__ new_start, const unsigned *__restrict__ old_id,
+                                const int *__restrict__ old_cell, unsigned *__restrict__ new_id,
+                                int *__restrict__ new_cell) {
+    int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n_old_bound || e >= old_start[ncells]) return;  // old_start[ncells] = entries so far
+    int c = old_cell[e];
+    int o = new_start[c] + (e - old_start[c]);
+    new_id[o] = old_id[e];
+    new_cell[o] = c;
+}
+
+// entries [first, first+count) of the graveyard / of a received tombstone list
+__global__ void k_dead_append(Geom g, int count, const unsigned *__restrict__ src_id,
+                              const int *__restrict__ src_cell_global, const int *__restrict__ new_start,
+                              int *dead_new_count, unsigned *__restrict__ new_id,
+                              int *__restrict__ new_cell) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    int c = src_cell_global[t] - g.cell_base;
+    if (c < 0 || c >= g.ncells) return;  // lies in another strip: shipped, not stored here
+    int o = new_start[c + 1] - atomicSub(&dead_new_count[c], 1);
+    new_id[o] = src_id[t];
+    new_cell[o] = c;
+}
+
+// ---------------------------------------------------------------------------------------
+// Dumps (tests): scatter the device state into id-ordered arrays.
+__global__ void k_dump_alive(Geom g, int n, const double2 *__restrict__ pos,
+                             const double2 *__restrict__ vel, const double *__restrict__ m,
+                             const unsigned *__restrict__ id, const int *__restrict__ cell,
+                             const int *__restrict__ newcell, const unsigned char *__restrict__ flags,
+                             int have_new, int have_flags, double *x, double *y, double *vx, double *vy,
+                             double *mass, int *alive, int *cell_out, int *list_cell,
+                             unsigned long long *list_rank, unsigned char *owned) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned p = id[i];
+    double2 a = pos[i], v = vel[i];
+    x[p] = a.x; y[p] = a.y; vx[p] = v.x; vy[p] = v.y; mass[p] = m[i];
+    alive[p] = 1;
+    owned[p] = 1;
+    int cg = cell[i] + g.cell_base;
+    cell_out[p] = have_new ? newcell[i] : cg;
+    unsigned char f = have_flags ? flags[i] : 0;
+    list_cell[p] = (f & F_REMOVED) ? newcell[i] : cg;
+    list_rank[p] = list_key(f, cg, p);
+}
+
+__global__ void k_dump_dead(int n, const double2 *__restrict__ pos, const double2 *__restrict__ vel,
+                            const unsigned *__restrict__ id, const int *__restrict__ cellg, double *x,
+                            double *y, double *vx, double *vy, double *mass, int *alive, int *cell_out,
+                            int *list_cell, unsigned long long *list_rank, unsigned char *owned) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    unsigned p = id[i];
+    double2 a = pos[i], v = vel[i];
+    x[p] = a.x; y[p] = a.y; vx[p] = v.x; vy[p] = v.y; mass[p] = 0.0;
+    alive[p] = 0;
+    owned[p] = 1;
+    cell_out[p] = cellg[i];
+    list_cell[p] = -1;
+    list_rank[p] = 0;
+}
+
+// particle 0 for parsim_result: alive arrays first, then the graveyard
+__global__ void k_find_id(int n, const unsigned *__restrict__ id, const double2 *__restrict__ pos,
+                          unsigned want, double2 *out, int *found) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    if (id[i] == want) { *out = pos[i]; *found = 1; }
+}
+
+}  // namespace parsim

@@ -1,0 +1,213 @@
+// parsim_rank.cu -- one row strip on one GPU: allocation, upload, the step driver, dumps.
+#include "parsim_rank.cuh"
+
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "parsim_exchange.cuh"
+
+namespace parsim {
+
+template <typename T>
+static int dev_alloc(Rank *c, T **p, size_t count, bool zero = false) {
+    size_t bytes = sizeof(T) * (count ? count : 1);
+    cudaError_t e = cudaMalloc((void **)p, bytes);
+    if (e != cudaSuccess)
+        return c->fail("cudaMalloc(" + std::to_string(bytes) + " B): " + cudaGetErrorString(e));
+    if (zero) {
+        e = cudaMemset(*p, 0, bytes);
+        if (e != cudaSuccess) return c->fail(std::string("cudaMemset: ") + cudaGetErrorString(e));
+    }
+    return 0;
+}
+#define PS_ALLOC(c, p, count, zero) \
+    do { if (dev_alloc(c, &(p), (size_t)(count), zero)) return 1; } while (0)
+
+// smallest double t with sqrt(t) >= EPSILON: sqrt(s) < EPSILON <=> s < t (sqrt is monotonic and
+// correctly rounded), so the collision test needs no square root per pair.
+static double collision_threshold2() {
+    double t = kEpsilon * kEpsilon;
+    while (sqrt(t) >= kEpsilon) t = nextafter(t, 0.0);
+    while (sqrt(t) < kEpsilon) t = nextafter(t, INFINITY);
+    return t;
+}
+
+int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, int nranks,
+                int device, const unsigned char *nccl_id) {
+    if (!(side > 0)) return c->fail("side_length must be > 0");
+    if (ncside < 1) return c->fail("grid_size must be >= 1");
+    if (n_part < 1) return c->fail("n_particles must be >= 1");
+    if ((long long)ncside * ncside > 2000000000LL) return c->fail("grid_size^2 must fit an int (as in the reference)");
+    if (n_part > 4000000000LL) return c->fail("n_particles must fit 32-bit ids");
+    if (nranks < 1 || rank < 0 || rank >= nranks) return c->fail("bad rank / nranks");
+    if (nranks > ncside) return c->fail("more GPUs than grid rows");
+    c->side = side; c->nc = ncside; c->n_part = n_part;
+    c->rank = rank; c->nranks = nranks; c->device = device;
+    int ndev = 0;
+    PS_CUDA(c, cudaGetDeviceCount(&ndev));
+    if (ndev < 1) return c->fail("no CUDA device: parsim_b200 has no CPU fallback");
+    if (device < 0 || device >= ndev) return c->fail("CUDA device index out of range");
+    PS_CUDA(c, cudaSetDevice(device));
+    PS_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+
+    Geom &g = c->g;
+    g.side = side;
+    g.cellw = side / (double)ncside;  // side_length / grid_size with grid_size a long, :160
+    g.nc = (int)ncside;
+    g.row0 = (int)((long long)rank * ncside / nranks);
+    int row1 = (int)((long long)(rank + 1) * ncside / nranks);
+    g.rows = row1 - g.row0;
+    g.ncells = g.rows * g.nc;
+    g.cell_base = g.row0 * g.nc;
+    c->thr2 = collision_threshold2();
+    double ppc = (double)n_part / ((double)ncside * (double)ncside);
+    c->com_lanes = ppc <= 6 ? 4 : ppc <= 12 ? 8 : ppc <= 24 ? 16 : 32;
+
+    long long cap;
+    if (nranks == 1) {
+        cap = n_part;
+        c->mig_cap = 0;
+    } else {
+        long long per_row = n_part / ncside + 1;
+        long long mc = std::max<long long>(65536, 2 * per_row);
+        c->mig_cap = (int)std::min<long long>(mc, n_part);
+        cap = (long long)((double)n_part / nranks * c->capacity_factor) + 4LL * c->mig_cap + 1024;
+        cap = std::min<long long>(cap, n_part + 2LL * c->mig_cap);
+    }
+    if (cap > 2147480000LL) return c->fail("strip too large for 32-bit indices: use more GPUs");
+    c->cap = (int)cap;
+
+    const size_t N = (size_t)c->cap, C = (size_t)g.ncells;
+    PS_ALLOC(c, c->pos_cur, N, false); PS_ALLOC(c, c->pos_alt, N, false);
+    PS_ALLOC(c, c->vel_cur, N, false); PS_ALLOC(c, c->vel_alt, N, false);
+    PS_ALLOC(c, c->m_cur, N, false);   PS_ALLOC(c, c->m_alt, N, false);
+    PS_ALLOC(c, c->id_cur, N, false);  PS_ALLOC(c, c->id_alt, N, false);
+    PS_ALLOC(c, c->cell_cur, N, false); PS_ALLOC(c, c->cell_alt, N, false);
+    PS_ALLOC(c, c->cs_cur, C + 1, true); PS_ALLOC(c, c->cs_alt, C + 1, true);
+    PS_ALLOC(c, c->count, C, true);
+    PS_ALLOC(c, c->tile_sums, C / kScanTile + 2, true);
+    PS_ALLOC(c, c->dst, N, false); PS_ALLOC(c, c->newcell, N, false);
+    PS_ALLOC(c, c->partner, N, false); PS_ALLOC(c, c->tmp_src, N, false);
+    PS_ALLOC(c, c->tmp_id, N, false);
+    PS_ALLOC(c, c->arr_head, C, false); PS_ALLOC(c, c->arr_next, N, false);
+    PS_ALLOC(c, c->flags, N, true);
+    PS_ALLOC(c, c->com_xy, (size_t)(g.rows + 2) * g.nc, true);
+    PS_ALLOC(c, c->com_m, (size_t)(g.rows + 2) * g.nc, true);
+    PS_ALLOC(c, c->dead_count, C, true); PS_ALLOC(c, c->dead_new_count, C, true);
+    PS_ALLOC(c, c->dead_start_cur, C + 1, true); PS_ALLOC(c, c->dead_start_alt, C + 1, true);
+    PS_ALLOC(c, c->dead_id_cur, N, false); PS_ALLOC(c, c->dead_id_alt, N, false);
+    PS_ALLOC(c, c->dead_cell_cur, N, false); PS_ALLOC(c, c->dead_cell_alt, N, false);
+    PS_ALLOC(c, c->grave_pos, N, false); PS_ALLOC(c, c->grave_vel, N, false);
+    PS_ALLOC(c, c->grave_id, N, false); PS_ALLOC(c, c->grave_cell, N, false);
+    PS_ALLOC(c, c->d_ctr, 1, true);
+    PS_ALLOC(c, c->d_p0, 1, true);
+    PS_ALLOC(c, c->d_found, 1, true);
+    PS_CUDA(c, cudaMallocHost((void **)&c->h_ctr, sizeof(Counters)));
+    memset(c->h_ctr, 0, sizeof(Counters));
+    PS_CUDA(c, cudaEventCreate(&c->run_a));
+    PS_CUDA(c, cudaEventCreate(&c->run_b));
+    if (nranks > 1) {
+        if (exchange_create(c, nccl_id)) return 1;
+    }
+    PS_CUDA(c, cudaDeviceSynchronize());  // the zero-fills above ran on the legacy stream
+    return 0;
+}
+
+void rank_destroy(Rank *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->stream) cudaStreamSynchronize(c->stream);
+    exchange_destroy(c);
+    void *ptrs[] = {c->pos_cur, c->pos_alt, c->vel_cur, c->vel_alt, c->m_cur, c->m_alt, c->id_cur,
+                    c->id_alt, c->cell_cur, c->cell_alt, c->cs_cur, c->cs_alt, c->count, c->tile_sums,
+                    c->dst, c->newcell, c->partner, c->tmp_src, c->tmp_id, c->arr_head, c->arr_next,
+                    c->flags, c->com_xy, c->com_m, c->dbg_acc, c->dead_count, c->dead_new_count,
+                    c->dead_start_cur, c->dead_start_alt, c->dead_id_cur, c->dead_id_alt,
+                    c->dead_cell_cur, c->dead_cell_alt, c->grave_pos, c->grave_vel, c->grave_id,
+                    c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->stage[0],
+                    c->stage[1], c->stage[2], c->stage[3], c->stage[4]};
+    for (void *p : ptrs) if (p) cudaFree(p);
+    if (c->h_ctr) cudaFreeHost(c->h_ctr);
+    for (auto &t : c->pending) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+    for (auto &e : c->event_pool) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    if (c->run_a) cudaEventDestroy(c->run_a);
+    if (c->run_b) cudaEventDestroy(c->run_b);
+    if (c->stream) cudaStreamDestroy(c->stream);
+}
+
+// ---- upload -------------------------------------------------------------------------------
+static int reset_state(Rank *c) {
+    const size_t C = (size_t)c->g.ncells;
+    c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->next_stage = 0;
+    c->n_tomb = 0; c->n_grave = 0; c->steps_done = 0; c->collisions_total = 0;
+    c->have_newcell = c->have_flags = false;
+    c->pos_latest = c->pos_cur;
+    PS_CUDA(c, cudaMemsetAsync(c->d_ctr, 0, sizeof(Counters), c->stream));
+    PS_CUDA(c, cudaMemsetAsync(c->count, 0, sizeof(int) * C, c->stream));
+    PS_CUDA(c, cudaMemsetAsync(c->dead_count, 0, sizeof(int) * C, c->stream));
+    PS_CUDA(c, cudaMemsetAsync(c->dead_new_count, 0, sizeof(int) * C, c->stream));
+    PS_CUDA(c, cudaMemsetAsync(c->dead_start_cur, 0, sizeof(int) * (C + 1), c->stream));
+    return 0;
+}
+
+int rank_upload_begin(Rank *c) {
+    PS_CUDA(c, cudaSetDevice(c->device));
+    if (reset_state(c)) return 1;
+    c->uploading = true;
+    return 0;
+}
+
+int rank_upload_chunk(Rank *c, long long id_base, long long count, const double *x, const double *y,
+                      const double *vx, const double *vy, const double *m) {
+    if (!c->uploading) return c->fail("parsim_upload_chunk outside upload_begin/upload_end");
+    if (id_base < 0 || count < 0 || id_base + count > c->n_part)
+        return c->fail("upload chunk outside [0, n_part)");
+    PS_CUDA(c, cudaSetDevice(c->device));
+    const long long piece = 1 << 24;  // 16 Mi particles per staging pass (5 x 128 MiB)
+    if (!c->stage[0]) {
+        c->stage_cap = (int)std::min<long long>(piece, c->n_part);
+        for (int k = 0; k < 5; k++) PS_ALLOC(c, c->stage[k], c->stage_cap, false);
+    }
+    const double *src[5] = {x, y, vx, vy, m};
+    for (long long off = 0; off < count; off += c->stage_cap) {
+        int cnt = (int)std::min<long long>(c->stage_cap, count - off);
+        for (int k = 0; k < 5; k++)
+            PS_CUDA(c, cudaMemcpyAsync(c->stage[k], src[k] + off, sizeof(double) * cnt,
+                                       cudaMemcpyHostToDevice, c->stream));
+        PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest",
+                  k_ingest<<<grid_for(cnt), kThreads, 0, c->stream>>>(
+                      c->g, id_base + off, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
+                      c->stage[4], c->nranks == 1, c->cap - 2 * c->mig_cap, c->pos_cur, c->vel_cur,
+                      c->m_cur, c->id_cur, c->d_ctr));
+        // the staging buffers are reused by the next piece
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));
+    }
+    if (c->nranks == 1) c->n_alive = (int)std::max<long long>(c->n_alive, id_base + count);
+    return 0;
+}
+
+int rank_upload_end(Rank *c) {
+    if (!c->uploading) return c->fail("parsim_upload_end without parsim_upload_begin");
+    PS_CUDA(c, cudaSetDevice(c->device));
+    c->uploading = false;
+    PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->h_ctr->error == DE_CAPACITY)
+        return c->fail("strip capacity exceeded during upload (skewed distribution?): raise option "
+                       "\"capacity_pct\" before uploading");
+    if (c->nranks > 1) c->n_alive = c->h_ctr->n_staged;
+    else if (c->n_alive != c->n_part) return c->fail("upload did not cover all n_part particles");
+    c->pos_latest = c->pos_cur;
+    return 0;
+}
+
+int rank_init_device(Rank *c, long seed) {
+    (void)seed;
+    return c->fail("parsim_init_device: not implemented yet");
+}
+
+}  // namespace parsim
+
+#include "parsim_step.inl"

@@ -1,0 +1,183 @@
+// parsim_rank.cuh -- host-side state of ONE row strip on ONE GPU ("rank"), and the per-step
+// driver that launches the kernels of parsim_kernels.cuh in the reference's phase order
+// (ParticleSimulation::simulate, serial/parsim.cpp:432-441).
+#pragma once
+#include <cuda_runtime.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/parsim_b200.h"
+#include "parsim_kernels.cuh"
+#include "parsim_nccl.hpp"
+
+namespace parsim {
+
+enum KernelId {
+    K_INGEST = 0, K_BIN_KEYS, K_SCAN, K_REBIN_SCATTER, K_REBIN_GATHER, K_COM, K_GHOST, K_FORCE,
+    K_CLASSIFY, K_COLLIDE, K_RESOLVE, K_TOMBSTONES, K_MIGRATE, K_INIT, K_MISC, K_COUNT_
+};
+static_assert(K_COUNT_ <= PARSIM_NKERNELS, "grow PARSIM_NKERNELS");
+
+struct TimedLaunch {
+    cudaEvent_t a, b;
+    int k;
+};
+
+struct Rank {
+    // problem
+    double side = 0;
+    long nc = 0;
+    long long n_part = 0;
+    int rank = 0, nranks = 1, device = 0;
+    Geom g{};
+    double thr2 = 0;    // collision threshold on the squared distance (see k_collide_find)
+    int com_lanes = 32; // lanes per cell in k_com, from the GLOBAL particles-per-cell
+
+    // particle storage: alive residents [0, n_alive), guests after them until the rebin
+    int cap = 0;
+    int n_alive = 0;
+    int n_guest = 0;
+    bool sorted = false;   // cell order valid for the coming step
+    int next_stage = 0;    // debug stepping
+    double2 *pos_cur = nullptr, *pos_alt = nullptr;  // cur: pre-move (sorted); alt: post-move
+    double2 *vel_cur = nullptr, *vel_alt = nullptr;
+    double *m_cur = nullptr, *m_alt = nullptr;
+    unsigned *id_cur = nullptr, *id_alt = nullptr;
+    int *cell_cur = nullptr, *cell_alt = nullptr;
+    int *cs_cur = nullptr, *cs_alt = nullptr;  // cell_start[ncells+1]
+    double2 *pos_latest = nullptr;             // where the newest positions are (dumps)
+    bool have_newcell = false, have_flags = false;
+
+    int *count = nullptr, *tile_sums = nullptr;
+    int *dst = nullptr, *newcell = nullptr, *partner = nullptr, *tmp_src = nullptr;
+    int *arr_head = nullptr, *arr_next = nullptr, *guest_src = nullptr;
+    unsigned *tmp_id = nullptr;
+    unsigned char *flags = nullptr;
+    double2 *com_xy = nullptr;
+    double *com_m = nullptr;
+    double2 *dbg_acc = nullptr;
+
+    // tombstones (dead CSR) and graveyard
+    int *dead_count = nullptr, *dead_new_count = nullptr;
+    int *dead_start_cur = nullptr, *dead_start_alt = nullptr;
+    unsigned *dead_id_cur = nullptr, *dead_id_alt = nullptr;
+    int *dead_cell_cur = nullptr, *dead_cell_alt = nullptr;
+    int n_tomb = 0;  // entries in the dead CSR of this strip
+    double2 *grave_pos = nullptr, *grave_vel = nullptr;
+    unsigned *grave_id = nullptr;
+    int *grave_cell = nullptr;
+    int n_grave = 0;
+
+    Counters *d_ctr = nullptr, *h_ctr = nullptr;
+    double2 *d_p0 = nullptr;
+    int *d_found = nullptr;
+
+    // upload staging
+    double *stage[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    int stage_cap = 0;
+    bool uploading = false;
+
+    // multi-strip exchange (parsim_exchange.cuh)
+    NcclComm comm;
+    int up = 0, dn = 0;          // neighbour ranks (periodic)
+    int mig_cap = 0;             // records per direction
+    double *mig_send[2] = {nullptr, nullptr}, *mig_recv[2] = {nullptr, nullptr};
+    int *mig_hdr_send = nullptr, *mig_hdr_recv = nullptr, *h_mig_hdr = nullptr;
+
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    // options / stats
+    bool opt_stats = false, opt_full_rebin = false, opt_sync_check = false;
+    double capacity_factor = 1.35;
+    parsim_stats_t stats{};
+    std::vector<TimedLaunch> pending;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> event_pool;
+    cudaEvent_t run_a = nullptr, run_b = nullptr;
+    long long steps_done = 0;
+    unsigned long long collisions_total = 0;  // host mirror of d_ctr->collisions (this strip)
+
+    int fail(const std::string &what) {
+        err = what;
+        return 1;
+    }
+};
+
+#define PS_CUDA(c, call)                                                                        \
+    do {                                                                                        \
+        cudaError_t e__ = (call);                                                               \
+        if (e__ != cudaSuccess)                                                                 \
+            return (c)->fail(std::string(#call) + ": " + cudaGetErrorString(e__));              \
+    } while (0)
+
+inline int grid_for(long long n, int threads = kThreads) {
+    long long b = (n + threads - 1) / threads;
+    return (int)(b > 0 ? b : 1);
+}
+
+// ---- stats: CUDA events around every launch, on the launching stream -----------------------
+inline void timed_begin(Rank *c, int k, double bytes) {
+    if (!c->opt_stats) return;
+    std::pair<cudaEvent_t, cudaEvent_t> ev;
+    if (!c->event_pool.empty()) {
+        ev = c->event_pool.back();
+        c->event_pool.pop_back();
+    } else {
+        cudaEventCreate(&ev.first);
+        cudaEventCreate(&ev.second);
+    }
+    cudaEventRecord(ev.first, c->stream);
+    c->pending.push_back({ev.first, ev.second, k});
+    c->stats.kernel_launches[k]++;
+    c->stats.kernel_bytes[k] += bytes;
+}
+inline void timed_end(Rank *c) {
+    if (!c->opt_stats) return;
+    cudaEventRecord(c->pending.back().b, c->stream);
+}
+inline int timed_collect(Rank *c) {  // stream must be idle
+    for (auto &t : c->pending) {
+        float ms = 0;
+        PS_CUDA(c, cudaEventElapsedTime(&ms, t.a, t.b));
+        c->stats.kernel_ms[t.k] += ms;
+        c->event_pool.push_back({t.a, t.b});
+    }
+    c->pending.clear();
+    return 0;
+}
+
+inline int check_launch(Rank *c, const char *name) {
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return c->fail(std::string(name) + " launch: " + cudaGetErrorString(e));
+    if (c->opt_sync_check) {
+        e = cudaStreamSynchronize(c->stream);
+        if (e != cudaSuccess) return c->fail(std::string(name) + ": " + cudaGetErrorString(e));
+    }
+    return 0;
+}
+
+#define PS_LAUNCH(c, kid, bytes, name, ...)        \
+    do {                                           \
+        timed_begin(c, kid, bytes);                \
+        __VA_ARGS__;                               \
+        timed_end(c);                              \
+        if (check_launch(c, name)) return 1;       \
+    } while (0)
+
+int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, int nranks,
+                int device, const unsigned char *nccl_id);
+void rank_destroy(Rank *c);
+int rank_upload_begin(Rank *c);
+int rank_upload_chunk(Rank *c, long long id_base, long long count, const double *x, const double *y,
+                      const double *vx, const double *vy, const double *m);
+int rank_upload_end(Rank *c);
+int rank_init_device(Rank *c, long seed);
+int rank_stage(Rank *c, int stage);
+int rank_run(Rank *c, long n_steps);
+int rank_result_local(Rank *c, double *x0, double *y0, int *found, long long *collisions);
+int rank_dump(Rank *c, double *x, double *y, double *vx, double *vy, double *m, int *alive, int *cell,
+              int *list_cell, unsigned long long *list_rank, unsigned char *owned);
+int rank_dump_cells(Rank *c, double *mx, double *my, double *m);
+
+}  // namespace parsim

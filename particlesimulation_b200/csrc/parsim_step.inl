@@ -1,0 +1,213 @@
+// parsim_step.inl -- the per-step driver (included by parsim_rank.cu).
+// Stage numbering follows include/parsim_b200.h (parsim_debug_stage).
+namespace parsim {
+
+// exclusive scan of in[0..N) into out[0..N], out[N] = total (also stored to *total2 if given)
+static int device_scan(Rank *c, const int *in, int N, int *out, int *total2) {
+    int ntiles = (N + kScanTile - 1) / kScanTile;
+    PS_LAUNCH(c, K_SCAN, 12.0 * N, "k_scan", {
+        k_scan_tile_sums<<<ntiles, kThreads, 0, c->stream>>>(in, nullptr, N, c->tile_sums);
+        k_scan_top<<<1, kThreads, 0, c->stream>>>(c->tile_sums, ntiles, out + N, total2);
+        k_scan_apply<<<ntiles, kThreads, 0, c->stream>>>(in, nullptr, N, c->tile_sums, out);
+    });
+    return 0;
+}
+
+// Sort the n_src source entries (state in pos_src, vel_cur, m_cur, id_cur; destination cell in
+// dst[], already histogrammed into count[]) into (cell, id) order.  Output: pos_out, *_alt,
+// cs_alt; then the non-position buffers are swapped.  Entries with dst < 0 are dropped.
+static int rebin(Rank *c, int n_src, const double2 *pos_src, double2 *pos_out) {
+    const Geom &g = c->g;
+    if (device_scan(c, c->count, g.ncells, c->cs_alt, &c->d_ctr->n_next)) return 1;
+    PS_LAUNCH(c, K_REBIN_SCATTER, 20.0 * n_src, "k_rebin_scatter",
+              k_rebin_scatter<<<grid_for(n_src), kThreads, 0, c->stream>>>(
+                  n_src, c->dst, c->id_cur, c->cs_alt, c->count, c->tmp_src, c->tmp_id, c->cell_alt));
+    PS_LAUNCH(c, K_REBIN_GATHER, 100.0 * n_src, "k_rebin_gather",
+              k_rebin_gather<<<grid_for(n_src), kThreads, 0, c->stream>>>(
+                  &c->d_ctr->n_next, c->cell_alt, c->cs_alt, c->tmp_src, c->tmp_id, pos_src,
+                  c->vel_cur, c->m_cur, pos_out, c->vel_alt, c->m_alt, c->id_alt));
+    std::swap(c->vel_cur, c->vel_alt);
+    std::swap(c->m_cur, c->m_alt);
+    std::swap(c->id_cur, c->id_alt);
+    std::swap(c->cell_cur, c->cell_alt);
+    std::swap(c->cs_cur, c->cs_alt);
+    return 0;
+}
+
+// Merge new tombstones into the dead CSR.  Sources: this step's graveyard slice and (multi
+// strip) the tombstones received from the neighbours; both were already counted into
+// dead_new_count[] for the cells of this strip.
+static int tombstones_update(Rank *c, int grave_first, int grave_cnt, int inbox_cnt) {
+    const Geom &g = c->g;
+    int bound_old = c->n_tomb;
+    PS_LAUNCH(c, K_TOMBSTONES, 12.0 * g.ncells, "k_add_counts",
+              k_add_counts<<<grid_for(g.ncells), kThreads, 0, c->stream>>>(g.ncells, c->dead_count,
+                                                                           c->dead_new_count));
+    if (device_scan(c, c->dead_count, g.ncells, c->dead_start_alt, nullptr)) return 1;
+    if (bound_old > 0)
+        PS_LAUNCH(c, K_TOMBSTONES, 16.0 * bound_old, "k_dead_copy_old",
+                  k_dead_copy_old<<<grid_for(bound_old), kThreads, 0, c->stream>>>(
+                      bound_old, c->dead_start_cur, g.ncells, c->dead_start_alt, c->dead_id_cur,
+                      c->dead_cell_cur, c->dead_id_alt, c->dead_cell_alt));
+    if (grave_cnt > 0)
+        PS_LAUNCH(c, K_TOMBSTONES, 16.0 * grave_cnt, "k_dead_append",
+                  k_dead_append<<<grid_for(grave_cnt), kThreads, 0, c->stream>>>(
+                      g, grave_cnt, c->grave_id + grave_first, c->grave_cell + grave_first,
+                      c->dead_start_alt, c->dead_new_count, c->dead_id_alt, c->dead_cell_alt));
+    if (inbox_cnt > 0 && exchange_append_tombstones(c, inbox_cnt)) return 1;
+    std::swap(c->dead_start_cur, c->dead_start_alt);
+    std::swap(c->dead_id_cur, c->dead_id_alt);
+    std::swap(c->dead_cell_cur, c->dead_cell_alt);
+    c->n_tomb = bound_old + grave_cnt + inbox_cnt;  // upper bound; exact total is dead_start[ncells]
+    return 0;
+}
+
+template <int LANES>
+static void launch_com(Rank *c) {
+    long long threads = (long long)c->g.ncells * LANES;
+    k_com<LANES><<<grid_for(threads), kThreads, 0, c->stream>>>(
+        c->g, c->pos_cur, c->m_cur, c->cs_cur, c->com_xy, c->com_m,
+        c->opt_stats ? &c->d_ctr->force_pairs : nullptr);
+}
+
+// stage 0: binning (only when the cell order is not valid yet) + centre of mass + ghost rows
+static int stage_bin_com(Rank *c) {
+    const Geom &g = c->g;
+    if (!c->sorted) {
+        PS_LAUNCH(c, K_BIN_KEYS, 20.0 * c->n_alive, "k_bin_keys",
+                  k_bin_keys<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(g, c->n_alive, c->pos_cur,
+                                                                               c->dst, c->count));
+        if (rebin(c, c->n_alive, c->pos_cur, c->pos_alt)) return 1;
+        std::swap(c->pos_cur, c->pos_alt);
+        c->sorted = true;
+    }
+    PS_LAUNCH(c, K_COM, 24.0 * c->n_alive + 24.0 * g.ncells, "k_com", {
+        switch (c->com_lanes) {
+        case 4: launch_com<4>(c); break;
+        case 8: launch_com<8>(c); break;
+        case 16: launch_com<16>(c); break;
+        default: launch_com<32>(c); break;
+        }
+    });
+    if (c->nranks == 1) {
+        PS_LAUNCH(c, K_GHOST, 96.0 * g.nc, "k_ghost_wrap",
+                  k_ghost_wrap<<<grid_for(g.nc), kThreads, 0, c->stream>>>(g, c->com_xy, c->com_m));
+    } else if (exchange_halo(c)) {
+        return 1;
+    }
+    c->pos_latest = c->pos_cur;
+    c->have_newcell = c->have_flags = false;
+    return 0;
+}
+
+// stage 1: forces + integration
+static int stage_force(Rank *c) {
+    PS_LAUNCH(c, K_FORCE, 80.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate",
+              k_force_integrate<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
+                  c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,
+                  c->pos_alt, c->vel_cur, c->newcell, c->dbg_acc));
+    c->pos_latest = c->pos_alt;
+    c->have_newcell = true;
+    return 0;
+}
+
+// stage 2: list update (movers / strays), and emigrants to the neighbouring strips
+static int stage_lists(Rank *c) {
+    const Geom &g = c->g;
+    PS_CUDA(c, cudaMemsetAsync(c->arr_head, 0xFF, sizeof(int) * (size_t)g.ncells, c->stream));
+    PS_LAUNCH(c, K_CLASSIFY, 9.0 * c->n_alive + 4.0 * g.ncells, "k_classify",
+              k_classify<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
+                  g, c->n_alive, c->cell_cur, c->cs_cur, c->newcell, c->id_cur,
+                  c->n_tomb > 0 ? c->dead_start_cur : nullptr, c->dead_id_cur, c->flags, c->arr_head,
+                  c->arr_next, c->d_ctr));
+    c->n_guest = 0;
+    if (c->nranks > 1 && exchange_emigrants(c)) return 1;
+    c->have_flags = true;
+    return 0;
+}
+
+// stage 3: collisions, compaction, and the (cell, id) order for the next step
+static int stage_collide(Rank *c) {
+    const Geom &g = c->g;
+    const int n_tot = c->n_alive + c->n_guest;
+    PS_LAUNCH(c, K_COLLIDE, 21.0 * n_tot + 8.0 * g.ncells, "k_collide_find",
+              k_collide_find<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
+                  g, n_tot, c->n_alive, c->thr2, c->pos_alt, c->cell_cur, c->cs_cur, c->newcell,
+                  c->id_cur, c->flags, c->arr_head, c->arr_next, c->guest_src, c->partner,
+                  c->opt_stats ? &c->d_ctr->collision_pairs : nullptr));
+    PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->deaths_step, 0, sizeof(int), c->stream));
+    PS_LAUNCH(c, K_RESOLVE, 17.0 * n_tot, "k_resolve",
+              k_resolve<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
+                  g, n_tot, c->n_alive, c->partner, c->newcell, c->flags, c->pos_alt, c->vel_cur,
+                  c->id_cur, c->dst, c->count, c->dead_new_count, c->grave_pos, c->grave_vel,
+                  c->grave_id, c->grave_cell, c->d_ctr));
+    PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaStreamSynchronize(c->stream));
+    if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error));
+    const int deaths = c->h_ctr->deaths_step;
+    const int grave_first = c->n_grave;
+    c->n_grave = c->h_ctr->grave_count;
+    int n_src = n_tot, inbox = 0, n_next;
+    if (c->nranks > 1) {
+        if (exchange_late(c, grave_first, deaths, &n_src, &inbox)) return 1;
+    }
+    if (deaths > 0 || inbox > 0) {
+        if (tombstones_update(c, grave_first, deaths, inbox)) return 1;
+    }
+    if (rebin(c, n_src, c->pos_alt, c->pos_cur)) return 1;
+    if (c->nranks == 1) {
+        n_next = n_tot - deaths;
+    } else {
+        PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));
+        n_next = c->h_ctr->n_next;
+    }
+    c->stats.alive_particle_steps += c->n_alive;
+    c->stats.deaths += deaths;
+    c->n_alive = n_next;
+    c->n_guest = 0;
+    c->pos_latest = c->pos_cur;
+    c->have_newcell = c->have_flags = false;
+    c->steps_done++;
+    c->stats.steps++;
+    return 0;
+}
+
+int rank_stage(Rank *c, int stage) {
+    PS_CUDA(c, cudaSetDevice(c->device));
+    if (c->uploading) return c->fail("upload not finished");
+    if (stage != c->next_stage)
+        return c->fail("stages must run in order; expected stage " + std::to_string(c->next_stage));
+    int rc = 0;
+    switch (stage) {
+    case 0: rc = stage_bin_com(c); break;
+    case 1: rc = stage_force(c); break;
+    case 2: rc = stage_lists(c); break;
+    case 3: rc = stage_collide(c); break;
+    default: return c->fail("stage must be 0..3");
+    }
+    if (rc) return rc;
+    c->next_stage = (stage + 1) & 3;
+    return 0;
+}
+
+int rank_run(Rank *c, long n_steps) {
+    PS_CUDA(c, cudaSetDevice(c->device));
+    if (c->uploading) return c->fail("upload not finished");
+    if (c->next_stage != 0) return c->fail("parsim_run in the middle of a debug-staged step");
+    PS_CUDA(c, cudaEventRecord(c->run_a, c->stream));
+    for (long t = 0; t < n_steps; t++) {
+        if (stage_bin_com(c) || stage_force(c) || stage_lists(c) || stage_collide(c)) return 1;
+    }
+    PS_CUDA(c, cudaEventRecord(c->run_b, c->stream));
+    PS_CUDA(c, cudaStreamSynchronize(c->stream));
+    float ms = 0;
+    PS_CUDA(c, cudaEventElapsedTime(&ms, c->run_a, c->run_b));
+    c->stats.run_ms += ms;
+    c->stats.particle_slots += (long long)c->n_part * n_steps;
+    return timed_collect(c);
+}
+
+}  // namespace parsim
+
+#include "parsim_dump.inl"
