@@ -1,0 +1,347 @@
+#!/usr/bin/env python3
+"""bench.py -- particle-steps/s of the parsim step loop on N B200s (BASELINE.json's metric).
+
+    python bench.py --gpus 1 --steps K --warmup W
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...      # the reference's own CPU code on the host cores
+
+A bench "step" is ONE complete run of the workload: `n_step` simulation timesteps from the seeded
+initial condition (the reference times exactly that: serial/parsim.cpp:475-477).  At N=1 the
+workload is BASELINE.json configs[2] (seed=7 side=100 ncside=1000 n_part=1e8 n_step=10, the
+HBM-roofline run; configs[1] is selectable with --workload config2).  At N>1 the same density
+is weak-scaled: n_part = N*1e8, ncside = round(1000*sqrt(N)), side = ncside/10, row strips.
+
+value  : device-timed, initial state already resident in HBM (parsim_reset + parsim_run)
+e2e    : host-timed through the C ABI with HOST buffers: parsim_upload from pinned memory,
+         parsim_run, parsim_result -- host<->device copies inside the timed region
+"""
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (seed, side, ncside, n_part, n_step, expected collisions at N=1 or None)
+    "config3": (7, 100.0, 1000, 100_000_000, 10, 29214105),
+    "config2": (1, 10.0, 100, 1_000_000, 20, 331425),
+    "config4w": (3, 354.0, 3536, 100_000_000, 10, 6103556),  # config 4 density, 1e8 per GPU
+}
+# bounded CPU sample of the same density (ppc = 100, cell = 0.1): config 3 at 1/100 size
+CPU_SAMPLE = {"config3": "7 10 100 1000000 10", "config2": "1 10 100 1000000 20",
+              "config4w": "3 35.4 354 1000000 10"}
+
+
+def workload_for(name, n_gpus, scale):
+    seed, side, nc, n, steps, expect = WORKLOADS[name]
+    if scale != 1.0:  # smoke-test sizes: same density, fewer cells
+        f = math.sqrt(scale)
+        nc = max(3, round(nc * f))
+        side = side / WORKLOADS[name][2] * nc
+        n = max(10, int(n * scale))
+        expect = None
+    if n_gpus > 1:
+        cellw = side / nc
+        nc = round(nc * math.sqrt(n_gpus))
+        side = nc * cellw
+        n = n * n_gpus
+        expect = None
+    return seed, side, nc, n, steps, expect
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("hbm_gbs", 6650.0), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm, mx, pw, reasons = [], [], [], set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[1])); mx.append(float(r[2])); pw.append(float(r[3]))
+            except Exception:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        load = [s for s, p in zip(sm, pw) if p >= 0.5 * max(pw)] or sm
+        load.sort()
+        return {"sm_mhz": load[len(load) // 2], "sm_max_mhz": max(mx), "power_w_max": max(pw),
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def run_reference_binary(binary, sample, threads):
+    env = dict(os.environ, OMP_NUM_THREADS=str(threads))
+    t = time.time()
+    p = subprocess.run([binary] + sample.split(), capture_output=True, text=True, env=env, check=True)
+    wall = time.time() - t
+    try:
+        secs = float(p.stderr.strip().splitlines()[-1].rstrip("s"))  # the reference's own timer
+        if secs < 2.0:
+            secs = wall  # "%.1lfs" is too coarse for short runs
+    except Exception:
+        secs = wall
+    n, steps = int(sample.split()[3]), int(sample.split()[4])
+    return n * steps / secs, secs, p.stdout.split()
+
+
+def cpu_baseline(workload, threads=1):
+    """The reference's own CPU code on this box's host cores, on a bounded sample of the workload
+    (same particles-per-cell and cell size, 1/100 of the particles)."""
+    sample = CPU_SAMPLE[workload]
+    ref = os.path.join(ROOT, "oracle", "_ref", "parsim-omp" if threads > 1 else "parsim")
+    kind = "reference"
+    if not os.path.exists(ref):
+        ref, kind, threads = os.path.join(ROOT, "oracle", "parsim_oracle"), "port", 1
+        if not os.path.exists(ref):
+            subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True, capture_output=True)
+    v, secs, out = run_reference_binary(ref, sample, threads)
+    return {"value": v, "unit": "particle-steps/s", "cores": threads, "kind": kind,
+            "sample": f"{os.path.basename(ref)} {sample} ({secs:.1f} s; same density, 1/100 of the particles)",
+            "stdout": out}
+
+
+def main_reference(a):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    seed, side, nc, n, nstep, _ = workload_for(a.workload, a.gpus, a.scale)
+    sample = CPU_SAMPLE[a.workload].split()
+    work = int(sample[3]) * int(sample[4])
+    secs = []
+    base = None
+    for i in range(a.warmup + a.steps):
+        base = cpu_baseline(a.workload, threads)
+        if i >= a.warmup:
+            secs.append(work / base["value"])
+    ms = 1e3 * sum(secs) / len(secs)
+    value = work / (ms / 1e3)
+    base["value"] = value
+    print(json.dumps({
+        "impl": "reference", "metric": "particle-steps/s", "value": value, "unit": "particle-steps/s",
+        "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic (seeded init_particles)",
+        "config": {"workload": f"{a.workload}: seed={seed} side={side:g} ncside={nc} n_part={n} n_step={nstep}",
+                   "measured_on": "bounded CPU sample " + CPU_SAMPLE[a.workload]},
+        "cpu_baseline": base,
+        "e2e": {"value": value, "unit": "particle-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+
+def main_ours(a):
+    import ctypes as C
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    from particlesimulation_b200 import ParticleSimulation, _lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != a.gpus:
+        raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
+    torch.cuda.set_device(local)
+    nccl_id = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        box = [None]
+        if rank == 0:
+            buf = (C.c_ubyte * 128)()
+            if _lib.load().parsim_nccl_unique_id(buf):
+                raise SystemExit("parsim_nccl_unique_id failed")
+            box[0] = bytes(buf)
+        dist.broadcast_object_list(box, src=0)
+        nccl_id = box[0]
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    seed, side, nc, n, nstep, expect = workload_for(a.workload, a.gpus, a.scale)
+    kw = dict(rank=rank, nranks=world, device=local, nccl_id=nccl_id) if world > 1 else {}
+    sim = ParticleSimulation(seed, side, nc, n, device_init=True, options={"keep_initial": 1}, **kw)
+    # host copies of this rank's inputs in pinned memory, for the end-to-end leg (untimed)
+    ids, x, y, vx, vy, m = sim.download()
+    cnt = len(ids)
+    pinned = [torch.from_numpy(np.ascontiguousarray(v)).pin_memory() for v in (x, y, vx, vy, m)]
+    pinned_ids = torch.from_numpy(ids.astype(np.int64)).to(torch.int32).pin_memory() if world > 1 else None
+    if world == 1:
+        assert np.array_equal(ids, np.arange(n, dtype=np.uint32))  # upload order = id order
+    del ids, x, y, vx, vy, m
+
+    stream = torch.cuda.ExternalStream(sim.lib.parsim_stream(sim._ctx), device=torch.device("cuda", local))
+
+    def one_run():
+        sim.reset()
+        sim.simulate(nstep)
+
+    # ---- device-resident leg: `value` -----------------------------------------------------
+    for _ in range(a.warmup):
+        one_run()
+    sim.set_option("stats", 1)
+    sim.stats_reset()
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(a.steps):
+        one_run()
+    e1.record(stream)
+    barrier()
+    ms_total = max_over_ranks(e0.elapsed_time(e1))
+    clk = clocks.stop()
+    st = sim.stats()
+    x0, y0, collisions = sim.result()
+    sim.set_option("stats", 0)
+    work = float(n) * nstep
+    value = work * a.steps / (ms_total / 1e3)
+
+    # ---- end-to-end leg: host buffers through the C ABI -------------------------------------
+    def one_e2e():
+        if world == 1:
+            sim.upload_ptrs([t.data_ptr() for t in pinned])
+        else:
+            sim.upload_strip_ptrs(cnt, pinned_ids.data_ptr(), [t.data_ptr() for t in pinned])
+        sim.simulate(nstep)
+        return sim.result()
+
+    one_e2e()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        res = one_e2e()
+    barrier()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    e2e_value = work * a.steps / e2e_s
+    assert res[2] == collisions, "end-to-end run disagrees with the device-resident run"
+
+    if rank != 0:
+        return
+    # ---- roofline of the dominant kernel + the per-kernel table -----------------------------
+    hbm_peak, peak_src = peaks()
+    kern = {k: v for k, v in st["kernels"].items() if v["launches"] > 0}
+    dom = max(kern, key=lambda k: kern[k]["ms"])
+    table = {}
+    for k, v in kern.items():
+        gbs = v["bytes"] / (v["ms"] * 1e-3) / 1e9 if v["ms"] > 0 else 0.0
+        table[k] = {"ms_per_step": v["ms"] / a.steps, "launches_per_step": v["launches"] / a.steps,
+                    "algorithmic_GB_per_step": v["bytes"] / a.steps / 1e9, "achieved_GBps": gbs,
+                    "hbm_frac": gbs / hbm_peak}
+    d = kern[dom]
+    achieved = d["bytes"] / (d["ms"] * 1e-3) / 1e9
+    fp64_peak = sim.fp64_peak_tflops()
+    force_flops = 17.0 * st["force_pairs"] / 2 + 120.0 * st["alive_particle_steps"]
+    coll_flops = 7.0 * st["collision_pairs"] / 2
+    f_ms, c_ms = kern["force_integrate"]["ms"], kern["collide_find"]["ms"]
+    fp64 = {"peak_tflops_measured_fma_chain": fp64_peak,
+            "force_integrate": {"algorithmic_tflops": force_flops / (f_ms * 1e-3) / 1e12,
+                                "frac": force_flops / (f_ms * 1e-3) / 1e12 / fp64_peak,
+                                "ordered_pairs_per_step": st["force_pairs"] / a.steps},
+            "collide_find": {"algorithmic_tflops": coll_flops / (c_ms * 1e-3) / 1e12,
+                             "frac": coll_flops / (c_ms * 1e-3) / 1e12 / fp64_peak,
+                             "ordered_pairs_per_step": st["collision_pairs"] / a.steps}}
+    traffic = None
+    tp = os.path.join(ROOT, "profiles", "traffic.json")
+    if os.path.exists(tp):
+        traffic = json.load(open(tp)).get(dom)
+    out = {
+        "metric": "particle-steps/s", "value": value, "unit": "particle-steps/s", "n_gpus": a.gpus,
+        "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_total / a.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": f"synthetic (seeded init_particles, seed {seed}, generated on the device)",
+        "config": {"workload": f"{a.workload}: seed={seed} side={side:g} ncside={nc} n_part={n} n_step={nstep}"
+                               + (" (BASELINE configs[2] density weak-scaled by row strips)" if world > 1 else ""),
+                   "step": f"one full run of {nstep} timesteps from the initial condition",
+                   "l2": "inputs (4.4 GB/GPU) are larger than L2; no flush needed",
+                   "parallelism": f"row strips x{world}" if world > 1 else "single GPU"},
+        "clocks": clk,
+        "e2e": {"value": e2e_value, "unit": "particle-steps/s", "h2d_bytes_per_step": 40 * cnt + (4 * cnt if world > 1 else 0),
+                "d2h_bytes_per_step": 24, "ms_per_step": 1e3 * e2e_s / a.steps},
+        "gpu_launches": int(sum(v["launches"] for v in kern.values())),
+        "roofline": {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
+                     "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
+                     "note": "the dominant kernel is FP64-CUDA-core bound (in-cell pair loop), see fp64"},
+        "fp64": fp64, "kernels": table,
+        "result": {"x0": round(x0, 3), "y0": round(y0, 3), "collisions": collisions,
+                   "reference_collisions": expect, "parity_ok": (collisions == expect) if expect else None},
+        "counters": {k: st[k] / a.steps for k in ("movers", "strays", "deaths", "migrants", "alive_particle_steps")},
+    }
+    if world == 1 and not a.no_cpu_baseline:
+        cb = cpu_baseline(a.workload, 1)
+        cb.pop("stdout", None)
+        out["cpu_baseline"] = cb
+    print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
+    ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (smoke tests only)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    a = ap.parse_args()
+    if a.impl == "reference":
+        main_reference(a)
+    else:
+        main_ours(a)
+    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        import torch.distributed as dist
+        if dist.is_initialized():
+            dist.destroy_process_group()

@@ -57,6 +57,17 @@ int parsim_upload_begin(parsim_ctx *ctx);
 int parsim_upload_chunk(parsim_ctx *ctx, long long id_base, long long count, const double *x,
                         const double *y, const double *vx, const double *vy, const double *m);
 int parsim_upload_end(parsim_ctx *ctx);
+/* Pieces with explicit particle ids (a rank of a multi-process job that already holds only
+ * its own strip's particles in host memory); same begin/end bracket. */
+int parsim_upload_chunk_ids(parsim_ctx *ctx, long long count, const unsigned *ids, const double *x,
+                            const double *y, const double *vx, const double *vy, const double *m);
+/* The alive particles of this context's strip, in device order, into host arrays of
+ * `capacity` elements; *count = how many.  One strip per context. */
+int parsim_download(parsim_ctx *ctx, long long capacity, unsigned *ids, double *x, double *y,
+                    double *vx, double *vy, double *m, long long *count);
+/* Restart from the state last uploaded, using a device-resident copy (option "keep_initial"
+ * must be 1 before the upload): no host traffic. */
+int parsim_reset(parsim_ctx *ctx);
 /* Host-side (C++) restatement of RandomGenerator + init_particles (serial/parsim.cpp:18-48,
  * :220-232): fills particles [first, first+count) of the seeded stream into host arrays of
  * `count` elements.  Needs no GPU.  Both distributions (seed < 0: truncated normal). */
@@ -125,7 +136,10 @@ const char *parsim_kernel_name(int k); /* NULL past the last kernel */
 int parsim_stats(parsim_ctx *ctx, parsim_stats_t *out);
 int parsim_stats_reset(parsim_ctx *ctx);
 
-/* options: "stats" (0/1), "full_rebin" (0/1: rebuild the cell order from scratch every step
+/* FP64 FMA-chain microbenchmark on this context's GPU (the FP64 roofline denominator). */
+int parsim_fp64_peak(parsim_ctx *ctx, double *tflops);
+
+/* options: "keep_initial" (0/1, see parsim_reset), "stats" (0/1), "full_rebin" (0/1: rebuild the cell order from scratch every step
  * instead of merging movers), "sync_check" (0/1: synchronise + check after every kernel). */
 int parsim_set_option(parsim_ctx *ctx, const char *name, long long value);
 

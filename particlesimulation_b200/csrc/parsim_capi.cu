@@ -119,7 +119,31 @@ int parsim_upload_begin(parsim_ctx *ctx) { return for_ranks(ctx, rank_upload_beg
 int parsim_upload_chunk(parsim_ctx *ctx, long long id_base, long long count, const double *x,
                         const double *y, const double *vx, const double *vy, const double *m) {
     if (!x || !y || !vx || !vy || !m) return ctx_fail(ctx, "parsim_upload: NULL array");
-    return for_ranks(ctx, [&](Rank *c) { return rank_upload_chunk(c, id_base, count, x, y, vx, vy, m); });
+    return for_ranks(ctx, [&](Rank *c) { return rank_upload_chunk(c, id_base, nullptr, count, x, y, vx, vy, m); });
+}
+
+int parsim_upload_chunk_ids(parsim_ctx *ctx, long long count, const unsigned *ids, const double *x,
+                            const double *y, const double *vx, const double *vy, const double *m) {
+    if (!ids || !x || !y || !vx || !vy || !m) return ctx_fail(ctx, "parsim_upload_chunk_ids: NULL array");
+    return for_ranks(ctx, [&](Rank *c) { return rank_upload_chunk(c, 0, ids, count, x, y, vx, vy, m); });
+}
+
+int parsim_reset(parsim_ctx *ctx) { return for_ranks(ctx, rank_reset); }
+
+int parsim_download(parsim_ctx *ctx, long long capacity, unsigned *ids, double *x, double *y, double *vx,
+                    double *vy, double *m, long long *count) {
+    if (ctx->ranks.size() != 1) return ctx_fail(ctx, "parsim_download: one strip per context only");
+    if (!ids || !x || !y || !vx || !vy || !m || !count) return ctx_fail(ctx, "parsim_download: NULL array");
+    Rank *c = ctx->ranks[0].get();
+    if (rank_download(c, capacity, ids, x, y, vx, vy, m, count)) return ctx_fail(ctx, c->err);
+    return 0;
+}
+
+int parsim_fp64_peak(parsim_ctx *ctx, double *tflops) {
+    Rank *c = ctx->ranks[0].get();
+    if (!tflops) return ctx_fail(ctx, "tflops is NULL");
+    if (rank_fp64_peak(c, tflops)) return ctx_fail(ctx, c->err);
+    return 0;
 }
 
 int parsim_upload_end(parsim_ctx *ctx) { return for_ranks(ctx, rank_upload_end); }
@@ -256,6 +280,7 @@ int parsim_set_option(parsim_ctx *ctx, const char *name, long long value) {
         if (n == "stats") c->opt_stats = value != 0;
         else if (n == "full_rebin") c->opt_full_rebin = value != 0;
         else if (n == "sync_check") c->opt_sync_check = value != 0;
+        else if (n == "keep_initial") c->opt_keep_initial = value != 0;
         else if (n == "debug_acc") {
             if (value && !c->dbg_acc) {
                 cudaSetDevice(c->device);

@@ -74,7 +74,8 @@ __device__ __forceinline__ int global_cell(double2 p, const Geom &g) {
 // ---------------------------------------------------------------------------------------
 // Upload: interleave host SoA (x,y,vx,vy,m) into the device layout and keep the particles of
 // this strip.  Slot order is irrelevant: the first rebin orders every cell by id.
-__global__ void k_ingest(Geom g, long long id_base, int count, const double *__restrict__ x,
+__global__ void k_ingest(Geom g, long long id_base, const unsigned *__restrict__ ids, int count,
+                         const double *__restrict__ x,
                          const double *__restrict__ y, const double *__restrict__ vx,
                          const double *__restrict__ vy, const double *__restrict__ m,
                          int single_rank, int capacity, double2 *pos, double2 *vel, double *mass,
@@ -83,8 +84,9 @@ __global__ void k_ingest(Geom g, long long id_base, int count, const double *__r
     if (t >= count) return;
     double2 p = make_double2(x[t], y[t]);
     int slot;
+    const unsigned pid = ids ? ids[t] : (unsigned)(id_base + t);
     if (single_rank) {
-        slot = (int)(id_base + t);
+        slot = (int)pid;
     } else {
         int row = cell_coord(p.y, g);
         if (row < g.row0 || row >= g.row0 + g.rows) return;
@@ -94,7 +96,87 @@ __global__ void k_ingest(Geom g, long long id_base, int count, const double *__r
     pos[slot] = p;
     vel[slot] = make_double2(vx[t], vy[t]);
     mass[slot] = m[t];
-    id[slot] = (unsigned)(id_base + t);
+    id[slot] = pid;
+}
+
+// ---------------------------------------------------------------------------------------
+// Device-side init_particles for seeds >= 0 (serial/parsim.cpp:220-232 with the uniform
+// generator :26-32).  xorshift32 is linear over GF(2): state_{k+1} = M state_k with a 32x32 bit
+// matrix M, so any thread can jump to its own offset of the ONE sequential stream.  Thread t
+// generates particles t, t+T, t+2T, ...: it starts at M^(5t) s0 (binary method over the
+// precomputed powers M^(2^j)) and advances by M^(5T - 5) between particles.  Matrices are stored
+// by columns (col[b] = M e_b), so M v is the xor of the columns selected by the bits of v.
+struct XsMatrix { unsigned col[32]; };
+struct XsJumpTable {
+    XsMatrix pow2[34];  // M^(2^j)
+    XsMatrix stride;    // M^(5T - 5): from the state after a particle's 5 draws to the next one's
+};
+
+__device__ __forceinline__ unsigned xs_apply(const XsMatrix &A, unsigned v) {
+    unsigned r = 0;
+#pragma unroll
+    for (int b = 0; b < 32; b++) r ^= ((v >> b) & 1u) ? A.col[b] : 0u;
+    return r;
+}
+
+__device__ __forceinline__ double xs_draw(unsigned &s) {
+    unsigned before = s;
+    s ^= s << 13;
+    s ^= s >> 17;
+    s ^= s << 5;
+    int sum = (int)(before + s);
+    return __dadd_rn(0.5, __dmul_rn(0.2328306e-09, (double)sum));  // no FMA: reference rounding
+}
+
+__global__ void k_init_particles(Geom g, const XsJumpTable *__restrict__ jt, unsigned s0, long long n_part,
+                                 int single_rank, int capacity, double2 *pos, double2 *vel, double *mass,
+                                 unsigned *id, Counters *ctr) {
+    const long long T = (long long)gridDim.x * blockDim.x;
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_part) return;
+    unsigned s = s0;
+    unsigned long long jump = 5ull * (unsigned long long)t;
+    for (int j = 0; jump; j++, jump >>= 1)
+        if (jump & 1ull) s = xs_apply(jt->pow2[j], s);
+    const double ncd = (double)g.nc;
+    const double cc = (double)((long long)g.nc * g.nc);
+    const double nd = (double)n_part;
+    for (long long i = t; i < n_part; i += T) {
+        double x = __dmul_rn(xs_draw(s), g.side);
+        double y = __dmul_rn(xs_draw(s), g.side);
+        double vx = __ddiv_rn(__ddiv_rn(__dmul_rn(__dadd_rn(xs_draw(s), -0.5), g.side), ncd), 5.0);
+        double vy = __ddiv_rn(__ddiv_rn(__dmul_rn(__dadd_rn(xs_draw(s), -0.5), g.side), ncd), 5.0);
+        double m = __dmul_rn(__ddiv_rn(__ddiv_rn(__dmul_rn(__dmul_rn(xs_draw(s), 0.01), cc), nd), kG),
+                             0.005 * 0.005);
+        s = xs_apply(jt->stride, s);
+        int slot;
+        if (single_rank) {
+            slot = (int)i;
+        } else {
+            int row = cell_coord(y, g);
+            if (row < g.row0 || row >= g.row0 + g.rows) continue;
+            slot = atomicAdd(&ctr->n_staged, 1);
+            if (slot >= capacity) { ctr->error = DE_CAPACITY; continue; }
+        }
+        pos[slot] = make_double2(x, y);
+        vel[slot] = make_double2(vx, vy);
+        mass[slot] = m;
+        id[slot] = (unsigned)i;
+    }
+}
+
+// FP64 FMA-chain microbenchmark: the measured FP64 peak that the force / collision kernels are
+// compared against (no such number is in MEASURED_PEAKS.json).
+__global__ void k_fp64_peak(int iters, double *out) {
+    double a0 = threadIdx.x * 1e-3, a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5,
+           a6 = a0 + 6, a7 = a0 + 7;
+    const double b = 0.999999, c = 1e-9;
+    for (int i = 0; i < iters; i++) {
+        a0 = fma(a0, b, c); a1 = fma(a1, b, c); a2 = fma(a2, b, c); a3 = fma(a3, b, c);
+        a4 = fma(a4, b, c); a5 = fma(a5, b, c); a6 = fma(a6, b, c); a7 = fma(a7, b, c);
+    }
+    double r = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+    if (r == 123.456) out[0] = r;
 }
 
 // ---------------------------------------------------------------------------------------
@@ -246,6 +328,21 @@ __global__ void k_rebin_gather(const int *__restrict__ n_out_ptr, const int *__r
 // strided subsequence, then a fixed xor-shuffle tree: the order of additions depends only on
 // the cell's (id-sorted) contents, never on scheduling or on the number of GPUs.
 // com_xy / com_m carry one ghost row above and below the strip: index = (local_row+1)*nc + gx.
+// stats helper: one global atomic per block instead of one per thread
+__device__ __forceinline__ void block_add_u64(unsigned long long v, unsigned long long *dst) {
+    __shared__ unsigned long long acc;
+    if (threadIdx.x == 0) acc = 0;
+    __syncthreads();
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&acc, v);
+    __syncthreads();
+    if (threadIdx.x == 0 && acc) atomicAdd(dst, acc);
+}
+
 template <int LANES>
 __global__ void k_com(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
                       const int *__restrict__ cell_start, double2 *__restrict__ com_xy,
@@ -268,16 +365,16 @@ __global__ void k_com(Geom g, const double2 *__restrict__ pos, const double *__r
         Mx += __shfl_xor_sync(0xffffffffu, Mx, o);
         My += __shfl_xor_sync(0xffffffffu, My, o);
     }
+    unsigned long long pairs = 0;
     if (lane == 0 && c < g.ncells) {
         double2 r = make_double2(0.0, 0.0);
         if (M > 0) r = make_double2(Mx / M, My / M);
         com_xy[c + g.nc] = r;
         com_m[c + g.nc] = M;
-        if (force_pairs) {
-            unsigned long long a = (unsigned long long)(e - s);
-            if (a > 1) atomicAdd(force_pairs, a * (a - 1));
-        }
+        unsigned long long a = (unsigned long long)(e - s);
+        pairs = a * (a - 1);
     }
+    if (force_pairs) block_add_u64(pairs, force_pairs);  // stats only (uniform branch)
 }
 
 // Single strip: the ghost rows are the strip's own last / first row (periodic wrap,
@@ -459,37 +556,41 @@ k_collide_find(Geom g, int n, int n_res, double thr2, const double2 *__restrict_
                const int *__restrict__ arr_next, const int *__restrict__ guest_src,
                int *__restrict__ partner, unsigned long long *collision_pairs) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const unsigned char f = flags[i];
-    if (f & F_EMIGRANT) { partner[i] = -1; return; }  // checked on the strip it moved to
-    const int L = (f & F_REMOVED) ? newcell[i] - g.cell_base : cell[i];
-    const double2 p = pos[i];
-    unsigned long long best = ~0ull;
-    int best_idx = -1;
-    const int s = cell_start[L], e = cell_start[L + 1];
-    // residents of L that are still listed there (stayers and strays), key = id, id-sorted
+    unsigned long long tested = 0;
+    if (i < n) {
+        const unsigned char f = flags[i];
+        int best_idx = -1;
+        if (!(f & F_EMIGRANT)) {  // emigrants are checked on the strip they moved to
+            const int L = (f & F_REMOVED) ? newcell[i] - g.cell_base : cell[i];
+            const double2 p = pos[i];
+            unsigned long long best = ~0ull;
+            const int s = cell_start[L], e = cell_start[L + 1];
+            // residents of L that are still listed there (stayers and strays), key = id, id-sorted
 #pragma unroll 4
-    for (int k = s; k < e; k++) {
-        double2 q = __ldg(&pos[k]);
-        unsigned char fk = __ldg(&flags[k]);
-        if (is_close(p, q, thr2) && k != i && !(fk & F_REMOVED)) {
-            unsigned long long key = id[k];
-            if (key < best) { best = key; best_idx = k; }
+            for (int k = s; k < e; k++) {
+                double2 q = __ldg(&pos[k]);
+                unsigned char fk = __ldg(&flags[k]);
+                if (is_close(p, q, thr2) && k != i && !(fk & F_REMOVED)) {
+                    unsigned long long key = id[k];
+                    if (key < best) { best = key; best_idx = k; }
+                }
+            }
+            // arrivals appended to L's list
+            int walked = 0;
+            for (int k = arr_head[L]; k >= 0; k = arr_next[k]) {
+                walked++;
+                if (k == i) continue;
+                if (is_close(p, pos[k], thr2)) {
+                    int src = k < n_res ? cell[k] + g.cell_base : guest_src[k - n_res];
+                    unsigned long long key = list_key(F_REMOVED, src, id[k]);
+                    if (key < best) { best = key; best_idx = k; }
+                }
+            }
+            tested = (unsigned long long)(e - s + walked);
         }
+        partner[i] = best_idx;
     }
-    // arrivals appended to L's list
-    int walked = 0;
-    for (int k = arr_head[L]; k >= 0; k = arr_next[k]) {
-        walked++;
-        if (k == i) continue;
-        if (is_close(p, pos[k], thr2)) {
-            int src = k < n_res ? cell[k] + g.cell_base : guest_src[k - n_res];
-            unsigned long long key = list_key(F_REMOVED, src, id[k]);
-            if (key < best) { best = key; best_idx = k; }
-        }
-    }
-    partner[i] = best_idx;
-    if (collision_pairs) atomicAdd(collision_pairs, (unsigned long long)(e - s + walked));
+    if (collision_pairs) block_add_u64(tested, collision_pairs);  // stats only (uniform branch)
 }
 
 // Count the mutual-first pairs, retire every particle that has any close partner, and
@@ -506,6 +607,7 @@ k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner,
     __shared__ unsigned warp_cnt[kThreads / 32];
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned mine = 0;
+    bool dying = false;
     if (i < n) {
         const unsigned char f = flags[i];
         int d = -1;
@@ -514,12 +616,7 @@ k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner,
             const int cell_now = newcell[i] - g.cell_base;  // cell of the post-move position
             if (p >= 0) {
                 if (partner[p] == i && i < p) mine = 1;
-                int slot = atomicAdd(&ctr->grave_count, 1);
-                grave_pos[slot] = pos[i];
-                grave_vel[slot] = vel[i];
-                grave_id[slot] = id[i];
-                grave_cell[slot] = newcell[i];  // global; tombstones of other strips are shipped
-                atomicAdd(&ctr->deaths_step, 1);
+                dying = true;
                 if (cell_now >= 0 && cell_now < g.ncells) atomicAdd(&dead_new_count[cell_now], 1);
             } else if (cell_now >= 0 && cell_now < g.ncells) {
                 d = cell_now;
@@ -528,6 +625,21 @@ k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner,
             // else: surviving stray that left the strip -> sent by the late exchange
         }
         dst[i] = d;
+    }
+    // graveyard slots: one atomic per warp (the whole warp is converged here)
+    const unsigned dm = __ballot_sync(0xffffffffu, dying);
+    if (dm) {
+        const int lane = threadIdx.x & 31;
+        int base = 0;
+        if (lane == __ffs(dm) - 1) base = atomicAdd(&ctr->grave_count, __popc(dm));
+        base = __shfl_sync(0xffffffffu, base, __ffs(dm) - 1);
+        if (dying) {
+            int slot = base + __popc(dm & ((1u << lane) - 1u));
+            grave_pos[slot] = pos[i];
+            grave_vel[slot] = vel[i];
+            grave_id[slot] = id[i];
+            grave_cell[slot] = newcell[i];  // global; tombstones of other strips are shipped
+        }
     }
     unsigned w = __reduce_add_sync(0xffffffffu, mine);
     if ((threadIdx.x & 31) == 0) warp_cnt[threadIdx.x >> 5] = w;

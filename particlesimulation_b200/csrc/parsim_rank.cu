@@ -65,6 +65,10 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     double ppc = (double)n_part / ((double)ncside * (double)ncside);
     c->com_lanes = ppc <= 6 ? 4 : ppc <= 12 ? 8 : ppc <= 24 ? 16 : 32;
 
+    if (const char *e = getenv("PARSIM_CAPACITY_PCT")) {
+        double pct = atof(e);
+        if (pct >= 100) c->capacity_factor = pct / 100.0;
+    }
     long long cap;
     if (nranks == 1) {
         cap = n_part;
@@ -126,7 +130,8 @@ void rank_destroy(Rank *c) {
                     c->flags, c->com_xy, c->com_m, c->dbg_acc, c->dead_count, c->dead_new_count,
                     c->dead_start_cur, c->dead_start_alt, c->dead_id_cur, c->dead_id_alt,
                     c->dead_cell_cur, c->dead_cell_alt, c->grave_pos, c->grave_vel, c->grave_id,
-                    c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->stage[0],
+                    c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->pos0, c->vel0,
+                    c->m0, c->id0, c->stage_ids, c->stage[0],
                     c->stage[1], c->stage[2], c->stage[3], c->stage[4]};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
@@ -138,7 +143,10 @@ void rank_destroy(Rank *c) {
 }
 
 // ---- upload -------------------------------------------------------------------------------
+static int keep_initial(Rank *c);
+
 static int reset_state(Rank *c) {
+    c->n_uploaded = 0;
     const size_t C = (size_t)c->g.ncells;
     c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->next_stage = 0;
     c->n_tomb = 0; c->n_grave = 0; c->steps_done = 0; c->collisions_total = 0;
@@ -159,16 +167,17 @@ int rank_upload_begin(Rank *c) {
     return 0;
 }
 
-int rank_upload_chunk(Rank *c, long long id_base, long long count, const double *x, const double *y,
-                      const double *vx, const double *vy, const double *m) {
+int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long count, const double *x,
+                      const double *y, const double *vx, const double *vy, const double *m) {
     if (!c->uploading) return c->fail("parsim_upload_chunk outside upload_begin/upload_end");
-    if (id_base < 0 || count < 0 || id_base + count > c->n_part)
+    if (count < 0 || (!ids && (id_base < 0 || id_base + count > c->n_part)))
         return c->fail("upload chunk outside [0, n_part)");
     PS_CUDA(c, cudaSetDevice(c->device));
     const long long piece = 1 << 24;  // 16 Mi particles per staging pass (5 x 128 MiB)
     if (!c->stage[0]) {
         c->stage_cap = (int)std::min<long long>(piece, c->n_part);
         for (int k = 0; k < 5; k++) PS_ALLOC(c, c->stage[k], c->stage_cap, false);
+        PS_ALLOC(c, c->stage_ids, c->stage_cap, false);
     }
     const double *src[5] = {x, y, vx, vy, m};
     for (long long off = 0; off < count; off += c->stage_cap) {
@@ -176,15 +185,18 @@ int rank_upload_chunk(Rank *c, long long id_base, long long count, const double 
         for (int k = 0; k < 5; k++)
             PS_CUDA(c, cudaMemcpyAsync(c->stage[k], src[k] + off, sizeof(double) * cnt,
                                        cudaMemcpyHostToDevice, c->stream));
+        if (ids)
+            PS_CUDA(c, cudaMemcpyAsync(c->stage_ids, ids + off, sizeof(unsigned) * cnt,
+                                       cudaMemcpyHostToDevice, c->stream));
         PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest",
                   k_ingest<<<grid_for(cnt), kThreads, 0, c->stream>>>(
-                      c->g, id_base + off, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
+                      c->g, id_base + off, ids ? c->stage_ids : nullptr, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
                       c->stage[4], c->nranks == 1, c->cap - 2 * c->mig_cap, c->pos_cur, c->vel_cur,
                       c->m_cur, c->id_cur, c->d_ctr));
         // the staging buffers are reused by the next piece
         PS_CUDA(c, cudaStreamSynchronize(c->stream));
     }
-    if (c->nranks == 1) c->n_alive = (int)std::max<long long>(c->n_alive, id_base + count);
+    c->n_uploaded += count;
     return 0;
 }
 
@@ -195,17 +207,131 @@ int rank_upload_end(Rank *c) {
     PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->h_ctr->error == DE_CAPACITY)
-        return c->fail("strip capacity exceeded during upload (skewed distribution?): raise option "
-                       "\"capacity_pct\" before uploading");
+        return c->fail("strip capacity exceeded during upload (skewed distribution?): set the environment "
+                       "variable PARSIM_CAPACITY_PCT (default 135 = 1.35 x n_part / n_gpus) before creating");
     if (c->nranks > 1) c->n_alive = c->h_ctr->n_staged;
-    else if (c->n_alive != c->n_part) return c->fail("upload did not cover all n_part particles");
+    else if (c->n_uploaded != c->n_part) return c->fail("upload did not cover all n_part particles");
+    else c->n_alive = (int)c->n_part;
+    c->pos_latest = c->pos_cur;
+    return keep_initial(c);
+}
+
+// option "keep_initial": a device-resident copy of the uploaded state, so that parsim_reset can
+// restart the same problem without touching the host (bench: inputs already in HBM).
+static int keep_initial(Rank *c) {
+    if (!c->opt_keep_initial) return 0;
+    const size_t N = (size_t)c->cap;
+    if (!c->pos0) {
+        PS_ALLOC(c, c->pos0, N, false); PS_ALLOC(c, c->vel0, N, false);
+        PS_ALLOC(c, c->m0, N, false); PS_ALLOC(c, c->id0, N, false);
+    }
+    const size_t n = (size_t)c->n_alive;
+    PS_CUDA(c, cudaMemcpyAsync(c->pos0, c->pos_cur, sizeof(double2) * n, cudaMemcpyDeviceToDevice, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->vel0, c->vel_cur, sizeof(double2) * n, cudaMemcpyDeviceToDevice, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->m0, c->m_cur, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->id0, c->id_cur, sizeof(unsigned) * n, cudaMemcpyDeviceToDevice, c->stream));
+    PS_CUDA(c, cudaStreamSynchronize(c->stream));
+    c->n0 = c->n_alive;
+    return 0;
+}
+
+int rank_reset(Rank *c) {
+    PS_CUDA(c, cudaSetDevice(c->device));
+    if (!c->pos0 || c->n0 <= 0) return c->fail("parsim_reset: set option keep_initial=1 before uploading");
+    if (reset_state(c)) return 1;
+    const size_t n = (size_t)c->n0;
+    PS_CUDA(c, cudaMemcpyAsync(c->pos_cur, c->pos0, sizeof(double2) * n, cudaMemcpyDeviceToDevice, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->vel_cur, c->vel0, sizeof(double2) * n, cudaMemcpyDeviceToDevice, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->m_cur, c->m0, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->id_cur, c->id0, sizeof(unsigned) * n, cudaMemcpyDeviceToDevice, c->stream));
+    c->n_alive = c->n0;
     c->pos_latest = c->pos_cur;
     return 0;
 }
 
+// strip particles (alive residents, current order) to host SoA + ids; *count_out = how many
+int rank_download(Rank *c, long long capacity, unsigned *ids, double *x, double *y, double *vx,
+                  double *vy, double *m, long long *count_out) {
+    PS_CUDA(c, cudaSetDevice(c->device));
+    PS_CUDA(c, cudaStreamSynchronize(c->stream));
+    const size_t n = (size_t)c->n_alive;
+    *count_out = (long long)n;
+    if ((long long)n > capacity) return c->fail("parsim_download: host arrays too small");
+    std::vector<double2> tmp(n);
+    PS_CUDA(c, cudaMemcpy(tmp.data(), c->pos_latest, sizeof(double2) * n, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < n; i++) { x[i] = tmp[i].x; y[i] = tmp[i].y; }
+    PS_CUDA(c, cudaMemcpy(tmp.data(), c->vel_cur, sizeof(double2) * n, cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < n; i++) { vx[i] = tmp[i].x; vy[i] = tmp[i].y; }
+    PS_CUDA(c, cudaMemcpy(m, c->m_cur, sizeof(double) * n, cudaMemcpyDeviceToHost));
+    PS_CUDA(c, cudaMemcpy(ids, c->id_cur, sizeof(unsigned) * n, cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+// ---- device-side init_particles --------------------------------------------------------------
+static unsigned xs_step_host(unsigned s) { s ^= s << 13; s ^= s >> 17; s ^= s << 5; return s; }
+static unsigned xs_apply_host(const XsMatrix &A, unsigned v) {
+    unsigned r = 0;
+    for (int b = 0; b < 32; b++) if ((v >> b) & 1u) r ^= A.col[b];
+    return r;
+}
+static XsMatrix xs_mul_host(const XsMatrix &A, const XsMatrix &B) {  // A * B
+    XsMatrix R;
+    for (int b = 0; b < 32; b++) R.col[b] = xs_apply_host(A, B.col[b]);
+    return R;
+}
+
 int rank_init_device(Rank *c, long seed) {
-    (void)seed;
-    return c->fail("parsim_init_device: not implemented yet");
+    PS_CUDA(c, cudaSetDevice(c->device));
+    const int iseed = (int)seed;  // main stores the seed in an int, serial/parsim.cpp:465
+    if (iseed < 0)
+        return c->fail("parsim_init_device: negative seeds use rejection sampling (serial/parsim.cpp:34-43);"
+                       " generate on the host and upload");
+    if (reset_state(c)) return 1;
+    const int blocks = 148 * 8;
+    const unsigned long long T = (unsigned long long)blocks * kThreads;
+    XsJumpTable jt;
+    for (int b = 0; b < 32; b++) jt.pow2[0].col[b] = xs_step_host(1u << b);
+    for (int j = 1; j < 34; j++) jt.pow2[j] = xs_mul_host(jt.pow2[j - 1], jt.pow2[j - 1]);
+    XsMatrix acc;
+    for (int b = 0; b < 32; b++) acc.col[b] = 1u << b;  // identity
+    unsigned long long e = 5ull * T - 5ull;
+    for (int j = 0; e; j++, e >>= 1) if (e & 1ull) acc = xs_mul_host(jt.pow2[j], acc);
+    jt.stride = acc;
+    XsJumpTable *d_jt = nullptr;
+    PS_ALLOC(c, d_jt, 1, false);
+    PS_CUDA(c, cudaMemcpyAsync(d_jt, &jt, sizeof(jt), cudaMemcpyHostToDevice, c->stream));
+    const unsigned s0 = (unsigned)abs(iseed) + 987654321u;  // :24
+    PS_LAUNCH(c, K_INIT, 44.0 * c->n_part, "k_init_particles",
+              k_init_particles<<<blocks, kThreads, 0, c->stream>>>(
+                  c->g, d_jt, s0, c->n_part, c->nranks == 1, c->cap - 2 * c->mig_cap, c->pos_cur,
+                  c->vel_cur, c->m_cur, c->id_cur, c->d_ctr));
+    c->uploading = true;
+    c->n_uploaded = c->n_part;
+    int rc = rank_upload_end(c);
+    cudaFree(d_jt);
+    return rc;
+}
+
+int rank_fp64_peak(Rank *c, double *tflops) {
+    PS_CUDA(c, cudaSetDevice(c->device));
+    const int iters = 1 << 15, blocks = 148 * 8;
+    double *d = nullptr;
+    PS_ALLOC(c, d, 1, true);
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++) {
+        cudaEventRecord(a, c->stream);
+        k_fp64_peak<<<blocks, kThreads, 0, c->stream>>>(iters, d);
+        cudaEventRecord(b, c->stream);
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, a, b);
+        if (rep > 0 && ms < best) best = ms;
+    }
+    cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(d);
+    *tflops = 2.0 * 8.0 * iters * (double)blocks * kThreads / (best * 1e-3) / 1e12;
+    return 0;
 }
 
 }  // namespace parsim

@@ -75,7 +75,15 @@ struct Rank {
 
     // upload staging
     double *stage[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    unsigned *stage_ids = nullptr;
     int stage_cap = 0;
+    long long n_uploaded = 0;
+    // option keep_initial: device copy of the uploaded state for parsim_reset
+    bool opt_keep_initial = false;
+    double2 *pos0 = nullptr, *vel0 = nullptr;
+    double *m0 = nullptr;
+    unsigned *id0 = nullptr;
+    int n0 = 0;
     bool uploading = false;
 
     // multi-strip exchange (parsim_exchange.cuh)
@@ -169,8 +177,12 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
                 int device, const unsigned char *nccl_id);
 void rank_destroy(Rank *c);
 int rank_upload_begin(Rank *c);
-int rank_upload_chunk(Rank *c, long long id_base, long long count, const double *x, const double *y,
-                      const double *vx, const double *vy, const double *m);
+int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long count, const double *x,
+                      const double *y, const double *vx, const double *vy, const double *m);
+int rank_reset(Rank *c);
+int rank_download(Rank *c, long long capacity, unsigned *ids, double *x, double *y, double *vx,
+                  double *vy, double *m, long long *count_out);
+int rank_fp64_peak(Rank *c, double *tflops);
 int rank_upload_end(Rank *c);
 int rank_init_device(Rank *c, long seed);
 int rank_stage(Rank *c, int stage);

@@ -10,6 +10,7 @@ static int device_scan(Rank *c, const int *in, int N, int *out, int *total2) {
         k_scan_top<<<1, kThreads, 0, c->stream>>>(c->tile_sums, ntiles, out + N, total2);
         k_scan_apply<<<ntiles, kThreads, 0, c->stream>>>(in, nullptr, N, c->tile_sums, out);
     });
+    if (c->opt_stats) c->stats.kernel_launches[K_SCAN] += 2;  // three kernels per scan
     return 0;
 }
 
@@ -135,7 +136,6 @@ static int stage_collide(Rank *c) {
                   g, n_tot, c->n_alive, c->thr2, c->pos_alt, c->cell_cur, c->cs_cur, c->newcell,
                   c->id_cur, c->flags, c->arr_head, c->arr_next, c->guest_src, c->partner,
                   c->opt_stats ? &c->d_ctr->collision_pairs : nullptr));
-    PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->deaths_step, 0, sizeof(int), c->stream));
     PS_LAUNCH(c, K_RESOLVE, 17.0 * n_tot, "k_resolve",
               k_resolve<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
                   g, n_tot, c->n_alive, c->partner, c->newcell, c->flags, c->pos_alt, c->vel_cur,
@@ -144,8 +144,8 @@ static int stage_collide(Rank *c) {
     PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error));
-    const int deaths = c->h_ctr->deaths_step;
     const int grave_first = c->n_grave;
+    const int deaths = c->h_ctr->grave_count - grave_first;
     c->n_grave = c->h_ctr->grave_count;
     int n_src = n_tot, inbox = 0, n_next;
     if (c->nranks > 1) {

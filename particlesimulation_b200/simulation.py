@@ -98,7 +98,7 @@ class ParticleSimulation:
     """ParticleSimulation(seed, side, ncside, n_part) -> .simulate(n_steps) -> .print_result()."""
 
     def __init__(self, seed, side, ncside, n_part, n_gpus=1, arrays=None, rank=None, nranks=1,
-                 device=0, nccl_id=None, device_init=False):
+                 device=0, nccl_id=None, device_init=False, options=None, upload=True):
         self.lib = _lib.load()
         self.side, self.ncside, self.n_part = float(side), int(ncside), int(n_part)
         self._ctx = C.c_void_p()
@@ -113,9 +113,11 @@ class ParticleSimulation:
         if rc:
             self._ctx = C.c_void_p()
             raise ParsimError(self.lib.parsim_last_error(None).decode())
+        for k, v in (options or {}).items():
+            self.set_option(k, v)
         if device_init:
             self._check(self.lib.parsim_init_device(self._ctx, int(seed)))
-        else:
+        elif upload:
             if arrays is None:
                 arrays = init_particles(seed, side, ncside, n_part)
             self.upload(*arrays)
@@ -135,6 +137,39 @@ class ParticleSimulation:
         """Upload from raw host addresses (e.g. pinned torch tensors' data_ptr())."""
         cast = [C.cast(C.c_void_p(p), C.POINTER(C.c_double)) for p in ptrs]
         self._check(self.lib.parsim_upload(self._ctx, *cast))
+
+    def upload_strip_ptrs(self, count, id_ptr, ptrs):
+        """Upload `count` particles with explicit ids from raw host addresses."""
+        self._check(self.lib.parsim_upload_begin(self._ctx))
+        cast = [C.cast(C.c_void_p(p), C.POINTER(C.c_double)) for p in ptrs]
+        self._check(self.lib.parsim_upload_chunk_ids(
+            self._ctx, int(count), C.cast(C.c_void_p(id_ptr), C.POINTER(C.c_uint)), *cast))
+        self._check(self.lib.parsim_upload_end(self._ctx))
+
+    def download(self, capacity=None):
+        """ids, x, y, vx, vy, m of the alive particles of this strip (device order)."""
+        cnt = C.c_longlong()
+        if capacity is None:  # ask for the count first (a capacity of 0 only reports it)
+            one = np.zeros(1)
+            oid = np.zeros(1, dtype=np.uint32)
+            self.lib.parsim_download(self._ctx, 0, oid.ctypes.data_as(C.POINTER(C.c_uint)),
+                                     *[_dptr(one)] * 5, C.byref(cnt))
+            capacity = cnt.value
+        cap = max(int(capacity), 1)
+        ids = np.zeros(cap, dtype=np.uint32)
+        arrs = [np.zeros(cap) for _ in range(5)]
+        self._check(self.lib.parsim_download(self._ctx, cap, ids.ctypes.data_as(C.POINTER(C.c_uint)),
+                                             *[_dptr(a) for a in arrs], C.byref(cnt)))
+        n = cnt.value
+        return (ids[:n],) + tuple(a[:n] for a in arrs)
+
+    def reset(self):
+        self._check(self.lib.parsim_reset(self._ctx))
+
+    def fp64_peak_tflops(self):
+        v = C.c_double()
+        self._check(self.lib.parsim_fp64_peak(self._ctx, C.byref(v)))
+        return v.value
 
     def simulate(self, n_time_steps):  # serial/parsim.cpp:422
         self._check(self.lib.parsim_run(self._ctx, int(n_time_steps)))

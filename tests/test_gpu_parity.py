@@ -153,3 +153,52 @@ def test_cli_matches_reference_output():
         assert p.returncode == 0, p.stderr
         assert p.stdout == exp
         assert p.stderr.strip().endswith("s")
+
+
+@pytest.mark.parametrize("args", [(1, 2, 3, 10), (7, 100, 1000, 300000), (0, 5, 7, 1000), (123456, 10, 100, 1 << 20)])
+def test_device_init_is_bit_identical_to_host_init(args):
+    """parsim_init_device (xorshift32 jump-ahead) == init_particles (serial/parsim.cpp:220-232)."""
+    g = ParticleSimulation(*args, device_init=True)
+    ids, x, y, vx, vy, m = g.download()
+    hx, hy, hvx, hvy, hm = init_particles(*args)
+    order = np.argsort(ids)
+    assert np.array_equal(ids[order], np.arange(args[3], dtype=np.uint32))
+    for dev, host in ((x, hx), (y, hy), (vx, hvx), (vy, hvy), (m, hm)):
+        assert np.array_equal(dev[order], host)
+    g.close()
+
+
+def test_device_init_rejects_negative_seed():
+    with pytest.raises(Exception):
+        ParticleSimulation(-3, 2, 3, 10, device_init=True)
+
+
+def test_reset_and_id_upload_reproduce_the_run():
+    args = (1, 10, 100, 100000)
+    a = ParticleSimulation(*args, options={"keep_initial": 1})
+    a.simulate(5)
+    first = a.result()
+    a.reset()
+    a.simulate(5)
+    assert a.result() == first and first[2] == 5226
+    # same particles handed over in a shuffled order with explicit ids
+    x, y, vx, vy, m = init_particles(*args)
+    perm = np.random.default_rng(0).permutation(args[3])
+    arrs = [np.ascontiguousarray(v[perm]) for v in (x, y, vx, vy, m)]
+    ids = np.ascontiguousarray(perm.astype(np.uint32))
+    b = ParticleSimulation(*args, upload=False)
+    b.upload_strip_ptrs(args[3], ids.ctypes.data, [v.ctypes.data for v in arrs])
+    b.simulate(5)
+    assert b.result() == first
+    a.close(); b.close()
+
+
+def test_stats_counters():
+    g = ParticleSimulation(1, 10, 100, 100000, options={"stats": 1})
+    g.simulate(3)
+    s = g.stats()
+    assert s["steps"] == 3 and s["particle_slots"] == 300000
+    assert s["kernels"]["force_integrate"]["launches"] == 3 and s["kernels"]["force_integrate"]["ms"] > 0
+    assert s["movers"] > 0 and s["deaths"] > 0 and s["force_pairs"] > 0 and s["collision_pairs"] > 0
+    assert g.fp64_peak_tflops() > 5
+    g.close()
