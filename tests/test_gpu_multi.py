@@ -1,0 +1,68 @@
+"""Row-strip multi-GPU path (NCCL halos + migrants): N strips must reproduce the single-GPU run
+bit for bit -- same collision count, same alive set, identical positions -- because every
+reduction has a fixed order that does not depend on the decomposition."""
+import json
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from conftest import ROOT
+from particlesimulation_b200 import ParticleSimulation
+
+pytestmark = pytest.mark.gpu
+
+
+def ngpu():
+    import torch
+    return torch.cuda.device_count()
+
+
+CASES = [(1, 10, 100, 100000, 5), (5, 1, 20, 20000, 4), (-7, 10, 50, 20000, 5), (3, 1, 2, 200, 3),
+         (9, 0.3, 4, 3000, 6), (1, 2, 3, 10, 3), (7, 30, 300, 2000000, 4)]
+
+
+@pytest.mark.parametrize("n_gpus", [2, 3, 4, 8])
+@pytest.mark.parametrize("case", CASES, ids=lambda c: " ".join(map(str, c)))
+def test_strips_match_single_gpu(case, n_gpus):
+    seed, side, nc, n, steps = case
+    if ngpu() < n_gpus:
+        pytest.skip(f"needs {n_gpus} GPUs")
+    if n_gpus > nc:
+        pytest.skip("more strips than rows")
+    os.environ["PARSIM_CAPACITY_PCT"] = "400"  # tiny / skewed cases: generous strip capacity
+    one = ParticleSimulation(seed, side, nc, n)
+    many = ParticleSimulation(seed, side, nc, n, n_gpus=n_gpus)
+    for t in range(steps):
+        one.simulate(1)
+        many.simulate(1)
+        assert one.result() == many.result(), f"step {t}"
+    a, b = one.dump(), many.dump()
+    assert b["owned"].all()
+    for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+        assert np.array_equal(a[k], b[k]), k
+    one.close(); many.close()
+
+
+@pytest.mark.parametrize("n_gpus", [2, 4, 8])
+def test_bench_under_torchrun(n_gpus):
+    if ngpu() < n_gpus:
+        pytest.skip(f"needs {n_gpus} GPUs")
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n_gpus}",
+           "--master-addr", "127.0.0.1", "--master-port", "29511", os.path.join(ROOT, "bench.py"),
+           "--gpus", str(n_gpus), "--steps", "1", "--warmup", "1", "--scale", "0.02"]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert p.returncode == 0, p.stderr[-3000:]
+    line = [l for l in p.stdout.splitlines() if l.startswith("{")][-1]
+    d = json.loads(line)
+    assert d["n_gpus"] == n_gpus and d["value"] > 0 and d["e2e"]["value"] > 0
+    # the same problem on one GPU gives the same collision count
+    one = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "1", "--warmup", "1",
+                          "--scale", str(0.02 * n_gpus), "--no-cpu-baseline"], capture_output=True, text=True, timeout=600)
+    assert one.returncode == 0, one.stderr[-3000:]
+    d1 = json.loads([l for l in one.stdout.splitlines() if l.startswith("{")][-1])
+    if d1["config"]["workload"].split("n_part=")[1] == d["config"]["workload"].split("n_part=")[1] and \
+            d1["config"]["workload"].split("ncside=")[1].split()[0] == d["config"]["workload"].split("ncside=")[1].split()[0]:
+        assert d1["result"]["collisions"] == d["result"]["collisions"]
