@@ -139,8 +139,7 @@ int parsim_stats_reset(parsim_ctx *ctx);
 /* FP64 FMA-chain microbenchmark on this context's GPU (the FP64 roofline denominator). */
 int parsim_fp64_peak(parsim_ctx *ctx, double *tflops);
 
-/* options: "keep_initial" (0/1, see parsim_reset), "stats" (0/1), "full_rebin" (0/1: rebuild the cell order from scratch every step
- * instead of merging movers), "sync_check" (0/1: synchronise + check after every kernel). */
+/* options: "keep_initial" (0/1, see parsim_reset), "stats" (0/1), "sync_check" (0/1: synchronise + check after every kernel). */
 int parsim_set_option(parsim_ctx *ctx, const char *name, long long value);
 
 /* Raw device pointer of the CUDA stream the kernels run on (cudaStream_t), for callers that

@@ -232,7 +232,7 @@ const char *parsim_kernel_name(int k) {
     static const char *names[K_COUNT_] = {
         "ingest", "bin_keys", "scan", "rebin_scatter", "rebin_gather", "com", "ghost_rows",
         "force_integrate", "classify_movers", "collide_find", "collide_resolve", "tombstones",
-        "migrate", "init_particles", "misc"};
+        "migrate", "init_particles", "merge_move"};
     return (k >= 0 && k < K_COUNT_) ? names[k] : nullptr;
 }
 
@@ -278,7 +278,6 @@ int parsim_set_option(parsim_ctx *ctx, const char *name, long long value) {
     for (auto &rp : ctx->ranks) {
         Rank *c = rp.get();
         if (n == "stats") c->opt_stats = value != 0;
-        else if (n == "full_rebin") c->opt_full_rebin = value != 0;
         else if (n == "sync_check") c->opt_sync_check = value != 0;
         else if (n == "keep_initial") c->opt_keep_initial = value != 0;
         else if (n == "debug_acc") {

@@ -14,6 +14,7 @@
 #include <limits.h>
 
 #include "parsim_rank.cuh"
+#include "parsim_merge.cuh"
 
 namespace parsim {
 
@@ -58,7 +59,7 @@ __global__ void k_pack_emigrants(Geom g, int n, int mig_cap, const unsigned char
 // guests: removed movers that arrived from the neighbouring strips; they sit behind the
 // residents until the rebin and are linked into their destination cell's arrival bag.
 __global__ void k_unpack_guests(Geom g, int n_rec, const double *__restrict__ recv, int first_idx,
-                                int guest_first, double2 *pos, double2 *vel, double *m, unsigned *id,
+                                int guest_first, double2 *pos, float2 *posf, double2 *vel, double *m, unsigned *id,
                                 int *cell, int *newcell, unsigned char *flags, int *guest_src,
                                 int *arr_head, int *arr_next, Counters *ctr) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -70,6 +71,7 @@ __global__ void k_unpack_guests(Geom g, int n_rec, const double *__restrict__ re
     int dst = dstg - g.cell_base;
     if (dst < 0 || dst >= g.ncells) { ctr->error = DE_LONG_JUMP; return; }
     pos[idx] = make_double2(r[0], r[1]);
+    posf[idx] = make_float2((float)r[0], (float)r[1]);
     vel[idx] = make_double2(r[2], r[3]);
     m[idx] = r[4];
     id[idx] = (unsigned)(a & 0xffffffffu);
@@ -82,27 +84,29 @@ __global__ void k_unpack_guests(Geom g, int n_rec, const double *__restrict__ re
 
 // after the collisions: strays that survived but now lie in another strip (kind 0) and
 // tombstones of particles that died here but lie in another strip (kind 1)
-__global__ void k_pack_late(Geom g, int n, int mig_cap, const unsigned char *__restrict__ flags,
-                            const int *__restrict__ partner, const double2 *__restrict__ pos,
+__global__ void k_pack_late(Geom g, int n, int mig_cap, const unsigned char *__restrict__ fate,
+                            const double2 *__restrict__ pos,
                             const double2 *__restrict__ vel, const double *__restrict__ m,
                             const unsigned *__restrict__ id, const int *__restrict__ newcell,
                             double *send_up, double *send_dn, int *hdr, Counters *ctr) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n || (flags[i] & F_EMIGRANT)) return;
-    int c = newcell[i] - g.cell_base;
-    if (c >= 0 && c < g.ncells) return;
+    if (i >= n) return;
+    const int ft = fate[i];
+    if (ft != FATE_LEFT_ALIVE && ft != FATE_LEFT_DEAD) return;
     int dir = strip_dir(g, newcell[i]);
     if (dir < 0) { ctr->error = DE_LONG_JUMP; return; }
     int slot = atomicAdd(&hdr[dir], 1);
     if (slot >= mig_cap) { ctr->error = DE_MIGRANT_OVERFLOW; return; }
     write_record(dir ? send_dn : send_up, slot, pos[i], vel[i], m[i], id[i], 0, newcell[i],
-                 partner[i] >= 0 ? 1 : 0);
+                 ft == FATE_LEFT_DEAD ? 1 : 0);
 }
 
+// late arrivals join the extended arrays behind residents and guests, as entries of the move
+// bag (alive) or the dead bag (tombstone) of the cell they lie in
 __global__ void k_unpack_late(Geom g, int n_rec, const double *__restrict__ recv, int first_idx,
-                              int inbox_first, double2 *pos, double2 *vel, double *m, unsigned *id,
-                              int *dst, int *count, int *dead_new_count, unsigned *inbox_id,
-                              int *inbox_cell, Counters *ctr) {
+                              double2 *pos, double2 *vel, double *m, unsigned *id, unsigned char *fate,
+                              int *count, int *dead_new_count, int *mv_head, int *dm_head, int *mv_next,
+                              Counters *ctr) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_rec) return;
     const double *r = recv + (size_t)t * kRec;
@@ -112,28 +116,22 @@ __global__ void k_unpack_late(Geom g, int n_rec, const double *__restrict__ recv
     int kind = (int)(b >> 32);
     int c = cg - g.cell_base;
     if (c < 0 || c >= g.ncells) { ctr->error = DE_LONG_JUMP; return; }
-    unsigned pid = (unsigned)(a & 0xffffffffu);
-    id[idx] = pid;
+    id[idx] = (unsigned)(a & 0xffffffffu);
     if (kind == 0) {
         pos[idx] = make_double2(r[0], r[1]);
         vel[idx] = make_double2(r[2], r[3]);
         m[idx] = r[4];
-        dst[idx] = c;
+        fate[idx] = FATE_MOVE;
         atomicAdd(&count[c], 1);
-        inbox_cell[inbox_first + t] = INT_MIN / 2;  // not a tombstone
-        inbox_id[inbox_first + t] = pid;
+        mv_next[idx] = atomicExch(&mv_head[c], idx);
     } else {
-        dst[idx] = -1;
+        fate[idx] = FATE_DEAD_MOVED;
         atomicAdd(&dead_new_count[c], 1);
-        inbox_cell[inbox_first + t] = cg;
-        inbox_id[inbox_first + t] = pid;
+        mv_next[idx] = atomicExch(&dm_head[c], idx);
     }
 }
 
 // ---- host side -----------------------------------------------------------------------------
-struct ExchangeBufs {  // hangs off Rank through these statics-free helpers
-};
-
 #define PS_NCCL(c, call)                                                                   \
     do {                                                                                   \
         int r__ = (call);                                                                  \
@@ -156,11 +154,11 @@ inline int exchange_create(Rank *c, const unsigned char *nccl_id) {
             cudaMalloc((void **)&c->mig_recv[d], rec * sizeof(double)) != cudaSuccess)
             return c->fail("cudaMalloc of migrant buffers failed");
     }
-    // hdr_send[0..1], hdr_recv[0..1]; inbox arrays behind guest_src
+    // hdr_send[0..1], hdr_recv[0..1]
     if (cudaMalloc((void **)&c->mig_hdr_send, 4 * sizeof(int)) != cudaSuccess)
         return c->fail("cudaMalloc failed");
     c->mig_hdr_recv = c->mig_hdr_send + 2;
-    if (cudaMalloc((void **)&c->guest_src, sizeof(int) * 6 * (size_t)c->mig_cap) != cudaSuccess)
+    if (cudaMalloc((void **)&c->guest_src, sizeof(int) * 2 * (size_t)c->mig_cap) != cudaSuccess)
         return c->fail("cudaMalloc failed");
     if (cudaMallocHost((void **)&c->h_mig_hdr, 4 * sizeof(int)) != cudaSuccess)
         return c->fail("cudaMallocHost failed");
@@ -177,9 +175,6 @@ inline void exchange_destroy(Rank *c) {
     if (c->mig_hdr_send) cudaFree(c->mig_hdr_send);
     if (c->h_mig_hdr) cudaFreeHost(c->h_mig_hdr);
 }
-
-inline int *inbox_cell_ptr(Rank *c) { return c->guest_src + 2 * (size_t)c->mig_cap; }
-inline unsigned *inbox_id_ptr(Rank *c) { return (unsigned *)(c->guest_src + 4 * (size_t)c->mig_cap); }
 
 // Ghost rows.  Receives are posted "from below" first so that with two strips (both
 // neighbours are the same peer) sends and receives pair up in issue order: what I send up is
@@ -248,48 +243,40 @@ inline int exchange_emigrants(Rank *c) {
     int first = c->n_alive;
     if (ru)
         k_unpack_guests<<<grid_for(ru), kThreads, 0, c->stream>>>(
-            g, ru, c->mig_recv[0], first, 0, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->cell_cur,
+            g, ru, c->mig_recv[0], first, 0, c->pos_alt, c->posf, c->vel_cur, c->m_cur, c->id_cur, c->cell_cur,
             c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->d_ctr);
     if (rd)
         k_unpack_guests<<<grid_for(rd), kThreads, 0, c->stream>>>(
-            g, rd, c->mig_recv[1], first + ru, ru, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur,
+            g, rd, c->mig_recv[1], first + ru, ru, c->pos_alt, c->posf, c->vel_cur, c->m_cur, c->id_cur,
             c->cell_cur, c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->d_ctr);
     timed_end(c);
     c->n_guest = ru + rd;
     return check_launch(c, "exchange_emigrants");
 }
 
-inline int exchange_late(Rank *c, int grave_first, int deaths, int *n_src, int *inbox) {
-    (void)grave_first; (void)deaths;
+inline int exchange_late(Rank *c, int *n_src, int *n_tombstones_in) {
     const Geom &g = c->g;
     const int n_tot = c->n_alive + c->n_guest;
     timed_begin(c, K_MIGRATE, 0);
     PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 2 * sizeof(int), c->stream));
     k_pack_late<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
-        g, n_tot, c->mig_cap, c->flags, c->partner, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur,
-        c->newcell, c->mig_send[0], c->mig_send[1], c->mig_hdr_send, c->d_ctr);
+        g, n_tot, c->mig_cap, c->fate, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->newcell,
+        c->mig_send[0], c->mig_send[1], c->mig_hdr_send, c->d_ctr);
     int ru = 0, rd = 0;
     if (exchange_records(c, &ru, &rd)) return 1;
     if (n_tot + ru + rd > c->cap) return c->fail("strip capacity exceeded by arriving particles");
     if (ru)
         k_unpack_late<<<grid_for(ru), kThreads, 0, c->stream>>>(
-            g, ru, c->mig_recv[0], n_tot, 0, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->dst,
-            c->count, c->dead_new_count, inbox_id_ptr(c), inbox_cell_ptr(c), c->d_ctr);
+            g, ru, c->mig_recv[0], n_tot, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->fate, c->count,
+            c->dead_new_count, c->mv_head, c->dm_head, c->mv_next, c->d_ctr);
     if (rd)
         k_unpack_late<<<grid_for(rd), kThreads, 0, c->stream>>>(
-            g, rd, c->mig_recv[1], n_tot + ru, ru, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->dst,
-            c->count, c->dead_new_count, inbox_id_ptr(c), inbox_cell_ptr(c), c->d_ctr);
+            g, rd, c->mig_recv[1], n_tot + ru, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->fate,
+            c->count, c->dead_new_count, c->mv_head, c->dm_head, c->mv_next, c->d_ctr);
     timed_end(c);
     *n_src = n_tot + ru + rd;
-    *inbox = ru + rd;
+    *n_tombstones_in = ru + rd;  // upper bound
     return check_launch(c, "exchange_late");
-}
-
-inline int exchange_append_tombstones(Rank *c, int inbox_cnt) {
-    k_dead_append<<<grid_for(inbox_cnt), kThreads, 0, c->stream>>>(
-        c->g, inbox_cnt, inbox_id_ptr(c), inbox_cell_ptr(c), c->dead_start_alt, c->dead_new_count,
-        c->dead_id_alt, c->dead_cell_alt);
-    return check_launch(c, "k_dead_append(inbox)");
 }
 
 // sum of 4 doubles over all strips (particle 0 position, found flag, collisions)

@@ -71,6 +71,21 @@ __device__ __forceinline__ int global_cell(double2 p, const Geom &g) {
     return cell_coord(p.y, g) * g.nc + cell_coord(p.x, g);
 }
 
+// stats helper: one global atomic per block instead of one per thread
+__device__ __forceinline__ void block_add_u64(unsigned long long v, unsigned long long *dst) {
+    __shared__ unsigned long long acc;
+    if (threadIdx.x == 0) acc = 0;
+    __syncthreads();
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&acc, v);
+    __syncthreads();
+    if (threadIdx.x == 0 && acc) atomicAdd(dst, acc);
+}
+
 // ---------------------------------------------------------------------------------------
 // Upload: interleave host SoA (x,y,vx,vy,m) into the device layout and keep the particles of
 // this strip.  Slot order is irrelevant: the first rebin orders every cell by id.
@@ -328,21 +343,6 @@ __global__ void k_rebin_gather(const int *__restrict__ n_out_ptr, const int *__r
 // strided subsequence, then a fixed xor-shuffle tree: the order of additions depends only on
 // the cell's (id-sorted) contents, never on scheduling or on the number of GPUs.
 // com_xy / com_m carry one ghost row above and below the strip: index = (local_row+1)*nc + gx.
-// stats helper: one global atomic per block instead of one per thread
-__device__ __forceinline__ void block_add_u64(unsigned long long v, unsigned long long *dst) {
-    __shared__ unsigned long long acc;
-    if (threadIdx.x == 0) acc = 0;
-    __syncthreads();
-    v += __shfl_xor_sync(0xffffffffu, v, 16);
-    v += __shfl_xor_sync(0xffffffffu, v, 8);
-    v += __shfl_xor_sync(0xffffffffu, v, 4);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
-    if ((threadIdx.x & 31) == 0 && v) atomicAdd(&acc, v);
-    __syncthreads();
-    if (threadIdx.x == 0 && acc) atomicAdd(dst, acc);
-}
-
 template <int LANES>
 __global__ void k_com(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
                       const int *__restrict__ cell_start, double2 *__restrict__ com_xy,
@@ -401,10 +401,21 @@ __global__ void k_ghost_wrap(Geom g, double2 *com_xy, double *com_m) {
 // rounding sequence exactly (no FMA contraction).
 // Pre-move positions are read from pos_in by every thread of the cell, so post-move
 // positions go to pos_out.
+// 1/sqrt(a) for a normal positive double: MUFU.RSQ64H seed (about 23 good bits) and one
+// third-order correction -> ~1 ulp.  No special-case branch: the caller discards a == 0.
+__device__ __forceinline__ double rsqrt_pos(double a) {
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
+    double e = fma(a, -(y * y), 1.0);
+    double p = fma(e, 0.375, 0.5);
+    return fma(p, y * e, y);
+}
+
 __device__ __forceinline__ void accumulate(double dx, double dy, double mk, double &ax, double &ay) {
     double d2 = fma(dx, dx, dy * dy);
-    double r = d2 > 0.0 ? rsqrt(d2) : 0.0;
-    double w = mk * r * r * r;
+    double r = rsqrt_pos(d2);
+    double w = (mk * r) * (r * r);
+    w = d2 > 0.0 ? w : 0.0;  // coincident points (and k == i) contribute nothing, :134-137
     ax = fma(w, dx, ax);
     ay = fma(w, dy, ay);
 }
@@ -414,7 +425,8 @@ k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
                   const double *__restrict__ m, const int *__restrict__ cell,
                   const int *__restrict__ cell_start, const double2 *__restrict__ com_xy,
                   const double *__restrict__ com_m, double2 *__restrict__ pos_out,
-                  double2 *__restrict__ vel, int *__restrict__ newcell, double2 *__restrict__ dbg_acc) {
+                  float2 *__restrict__ posf_out, double2 *__restrict__ vel, int *__restrict__ newcell,
+                  double2 *__restrict__ dbg_acc) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int c = cell[i];
@@ -464,6 +476,7 @@ k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
     y = fmod(__dadd_rn(y, g.side), g.side);
     double2 pn = make_double2(x, y);
     pos_out[i] = pn;
+    posf_out[i] = make_float2((float)x, (float)y);  // collision pre-filter, see k_collide_find
     vel[i] = v;
     newcell[i] = global_cell(pn, g);          // :174-177
 }
@@ -486,40 +499,48 @@ __device__ __forceinline__ bool tombstone_between(const int *__restrict__ dead_s
     return false;
 }
 
-__global__ void k_classify(Geom g, int n, const int *__restrict__ cell,
-                           const int *__restrict__ cell_start, const int *__restrict__ newcell,
-                           const unsigned *__restrict__ id, const int *__restrict__ dead_start,
-                           const unsigned *__restrict__ dead_id, unsigned char *__restrict__ flags,
-                           int *arr_head, int *__restrict__ arr_next, Counters *ctr) {
+__global__ void __launch_bounds__(kThreads)
+k_classify(Geom g, int n, const int *__restrict__ cell, const int *__restrict__ cell_start,
+           const int *__restrict__ newcell, const unsigned *__restrict__ id,
+           const int *__restrict__ dead_start, const unsigned *__restrict__ dead_id,
+           unsigned char *__restrict__ flags, int *arr_head, int *__restrict__ arr_next,
+           unsigned long long *stat_movers, unsigned long long *stat_strays) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const int c = cell[i];
-    const int cg = c + g.cell_base;
-    const int dstg = newcell[i];
-    if (dstg == cg) { flags[i] = 0; return; }
-    // length of the run of consecutive leavers that ends just before i
-    int run = 0;
-    const int s = cell_start[c];
-    for (int t = i - 1; t >= s; t--) {
-        if (newcell[t] == cg) break;
-        if (tombstone_between(dead_start, dead_id, c, id[t], id[t + 1])) break;
-        run++;
-    }
-    const bool removed = (run & 1) == 0;
-    unsigned char f = F_MOVER;
-    if (removed) {
-        f |= F_REMOVED;
-        int dst = dstg - g.cell_base;
-        if (dst >= 0 && dst < g.ncells) {
-            arr_next[i] = atomicExch(&arr_head[dst], i);  // unordered bag; order comes from keys
-        } else {
-            f |= F_EMIGRANT;
+    unsigned long long mover = 0, stray = 0;
+    if (i < n) {
+        const int c = cell[i];
+        const int cg = c + g.cell_base;
+        const int dstg = newcell[i];
+        unsigned char f = 0;
+        if (dstg != cg) {
+            // length of the run of consecutive leavers that ends just before i
+            int run = 0;
+            const int s = cell_start[c];
+            for (int t = i - 1; t >= s; t--) {
+                if (newcell[t] == cg) break;
+                if (tombstone_between(dead_start, dead_id, c, id[t], id[t + 1])) break;
+                run++;
+            }
+            f = F_MOVER;
+            mover = 1;
+            if ((run & 1) == 0) {
+                f |= F_REMOVED;
+                int dst = dstg - g.cell_base;
+                if (dst >= 0 && dst < g.ncells) {
+                    arr_next[i] = atomicExch(&arr_head[dst], i);  // unordered bag; order comes from keys
+                } else {
+                    f |= F_EMIGRANT;
+                }
+            } else {
+                stray = 1;
+            }
         }
-    } else {
-        atomicAdd(&ctr->strays, 1ull);
+        flags[i] = f;
     }
-    atomicAdd(&ctr->movers, 1ull);
-    flags[i] = f;
+    if (stat_movers) {  // stats only (uniform branch)
+        block_add_u64(mover, stat_movers);
+        block_add_u64(stray, stat_strays);
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -549,7 +570,8 @@ __device__ __forceinline__ bool is_close(double2 a, double2 b, double thr2) {
 // n = residents (+ guests that arrived from other strips, which have cell[i] = -1 and carry
 // their source cell in guest_src[i - n_res]).
 __global__ void __launch_bounds__(kThreads)
-k_collide_find(Geom g, int n, int n_res, double thr2, const double2 *__restrict__ pos,
+k_collide_find(Geom g, int n, int n_res, double thr2, float thrf, const double2 *__restrict__ pos,
+               const float2 *__restrict__ posf,
                const int *__restrict__ cell, const int *__restrict__ cell_start,
                const int *__restrict__ newcell, const unsigned *__restrict__ id,
                const unsigned char *__restrict__ flags, const int *__restrict__ arr_head,
@@ -563,16 +585,21 @@ k_collide_find(Geom g, int n, int n_res, double thr2, const double2 *__restrict_
         if (!(f & F_EMIGRANT)) {  // emigrants are checked on the strip they moved to
             const int L = (f & F_REMOVED) ? newcell[i] - g.cell_base : cell[i];
             const double2 p = pos[i];
+            const float2 pf = posf[i];
             unsigned long long best = ~0ull;
             const int s = cell_start[L], e = cell_start[L + 1];
-            // residents of L that are still listed there (stayers and strays), key = id, id-sorted
+            // residents of L that are still listed there (stayers and strays), key = id, id-sorted.
+            // FP32 pre-filter: thrf over-covers the rounding of the float copies, so every pair
+            // that is close in FP64 passes it; the decision itself is the exact FP64 test.
 #pragma unroll 4
             for (int k = s; k < e; k++) {
-                double2 q = __ldg(&pos[k]);
-                unsigned char fk = __ldg(&flags[k]);
-                if (is_close(p, q, thr2) && k != i && !(fk & F_REMOVED)) {
-                    unsigned long long key = id[k];
-                    if (key < best) { best = key; best_idx = k; }
+                float2 qf = __ldg(&posf[k]);
+                float fx = qf.x - pf.x, fy = qf.y - pf.y;
+                if (fmaf(fx, fx, fy * fy) < thrf) {
+                    if (k != i && !(flags[k] & F_REMOVED) && is_close(p, pos[k], thr2)) {
+                        unsigned long long key = id[k];
+                        if (key < best) { best = key; best_idx = k; }
+                    }
                 }
             }
             // arrivals appended to L's list
@@ -593,96 +620,11 @@ k_collide_find(Geom g, int n, int n_res, double thr2, const double2 *__restrict_
     if (collision_pairs) block_add_u64(tested, collision_pairs);  // stats only (uniform branch)
 }
 
-// Count the mutual-first pairs, retire every particle that has any close partner, and
-// histogram the survivors by their new cell for the rebin (stream compaction, north_star (e)).
-// The dead go to the graveyard (frozen state for parsim_result / dumps) and, as (cell, id)
-// tombstones, to the dead CSR of the cell they now lie in.
-__global__ void __launch_bounds__(kThreads)
-k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner,
-          const int *__restrict__ newcell, const unsigned char *__restrict__ flags,
-          const double2 *__restrict__ pos, const double2 *__restrict__ vel,
-          const unsigned *__restrict__ id, int *__restrict__ dst, int *count, int *dead_new_count,
-          double2 *__restrict__ grave_pos, double2 *__restrict__ grave_vel,
-          unsigned *__restrict__ grave_id, int *__restrict__ grave_cell, Counters *ctr) {
-    __shared__ unsigned warp_cnt[kThreads / 32];
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    unsigned mine = 0;
-    bool dying = false;
-    if (i < n) {
-        const unsigned char f = flags[i];
-        int d = -1;
-        if (!(f & F_EMIGRANT)) {
-            const int p = partner[i];
-            const int cell_now = newcell[i] - g.cell_base;  // cell of the post-move position
-            if (p >= 0) {
-                if (partner[p] == i && i < p) mine = 1;
-                dying = true;
-                if (cell_now >= 0 && cell_now < g.ncells) atomicAdd(&dead_new_count[cell_now], 1);
-            } else if (cell_now >= 0 && cell_now < g.ncells) {
-                d = cell_now;
-                atomicAdd(&count[d], 1);
-            }
-            // else: surviving stray that left the strip -> sent by the late exchange
-        }
-        dst[i] = d;
-    }
-    // graveyard slots: one atomic per warp (the whole warp is converged here)
-    const unsigned dm = __ballot_sync(0xffffffffu, dying);
-    if (dm) {
-        const int lane = threadIdx.x & 31;
-        int base = 0;
-        if (lane == __ffs(dm) - 1) base = atomicAdd(&ctr->grave_count, __popc(dm));
-        base = __shfl_sync(0xffffffffu, base, __ffs(dm) - 1);
-        if (dying) {
-            int slot = base + __popc(dm & ((1u << lane) - 1u));
-            grave_pos[slot] = pos[i];
-            grave_vel[slot] = vel[i];
-            grave_id[slot] = id[i];
-            grave_cell[slot] = newcell[i];  // global; tombstones of other strips are shipped
-        }
-    }
-    unsigned w = __reduce_add_sync(0xffffffffu, mine);
-    if ((threadIdx.x & 31) == 0) warp_cnt[threadIdx.x >> 5] = w;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        unsigned tot = 0;
-#pragma unroll
-        for (int k = 0; k < kThreads / 32; k++) tot += warp_cnt[k];
-        if (tot) atomicAdd(&ctr->collisions, (unsigned long long)tot);
-    }
-}
-
 // ---------------------------------------------------------------------------------------
-// Tombstone CSR update: new = old entries (kept in place order) + this step's deaths.
-__global__ void k_add_counts(int n, int *__restrict__ acc, const int *__restrict__ add) {
+// Tombstone counts: total per cell += this step's deaths (and the per-step array is cleared).
+__global__ void k_add_counts(int n, int *__restrict__ acc, int *__restrict__ add) {
     int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c < n) acc[c] += add[c];
-}
-
-__global__ void k_dead_copy_old(int n_old_bound, const int *__restrict__ old_start, int ncells,
-                                const int *__restrict__ new_start, const unsigned *__restrict__ old_id,
-                                const int *__restrict__ old_cell, unsigned *__restrict__ new_id,
-                                int *__restrict__ new_cell) {
-    int e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= n_old_bound || e >= old_start[ncells]) return;  // old_start[ncells] = entries so far
-    int c = old_cell[e];
-    int o = new_start[c] + (e - old_start[c]);
-    new_id[o] = old_id[e];
-    new_cell[o] = c;
-}
-
-// entries [first, first+count) of the graveyard / of a received tombstone list
-__global__ void k_dead_append(Geom g, int count, const unsigned *__restrict__ src_id,
-                              const int *__restrict__ src_cell_global, const int *__restrict__ new_start,
-                              int *dead_new_count, unsigned *__restrict__ new_id,
-                              int *__restrict__ new_cell) {
-    int t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= count) return;
-    int c = src_cell_global[t] - g.cell_base;
-    if (c < 0 || c >= g.ncells) return;  // lies in another strip: shipped, not stored here
-    int o = new_start[c + 1] - atomicSub(&dead_new_count[c], 1);
-    new_id[o] = src_id[t];
-    new_cell[o] = c;
+    if (c < n) { acc[c] += add[c]; add[c] = 0; }
 }
 
 // ---------------------------------------------------------------------------------------

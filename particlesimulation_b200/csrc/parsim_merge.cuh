@@ -1,0 +1,238 @@
+// parsim_merge.cuh -- end-of-step compaction and re-ordering without a sort (north_star (a)+(e)).
+//
+// Only ~1 % of the particles change cell per step (|v| dt <= 0.01 cell, serial/parsim.cpp:227-228)
+// and the alive array is already ordered by (cell, id), so the order for the next step is built
+// by a per-cell MERGE instead of a counting sort:
+//   k_resolve : per particle -- who died (any close partner), which close pairs count as a
+//               collision (mutual-first rule, see k_collide_find), and a one-byte fate; survivors
+//               that stay are counted per cell with ONE atomic per (warp, cell); the few movers
+//               are pushed on their destination cell's bag.
+//   scan      : new cell_start / tombstone_start from the two count arrays.
+//   k_move    : one lane group per destination cell -- copies the stayers of the old segment in
+//               order (coalesced reads and writes), drops the dead, merges the bag by id, and
+//               rebuilds the cell's tombstone list.  No atomics, deterministic layout.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "parsim_kernels.cuh"
+
+namespace parsim {
+namespace cg = cooperative_groups;
+
+enum Fate : unsigned char {
+    FATE_STAY = 0,        // alive, same cell
+    FATE_DEAD_HERE = 1,   // died, lies in the cell it was binned in
+    FATE_MOVE = 2,        // alive, lies in another cell of this strip (in the move bag)
+    FATE_DEAD_MOVED = 3,  // died, lies in another cell of this strip (in the dead bag)
+    FATE_EMIGRATED = 4,   // handed to another strip before the collision phase
+    FATE_LEFT_ALIVE = 5,  // alive, lies in another strip (sent by the late exchange)
+    FATE_LEFT_DEAD = 6,   // died here, lies in another strip (its tombstone is sent)
+};
+
+// entries [0, n_res) are residents (cell[i] valid), [n_res, n) guests from other strips.
+// Persistent blocks walk tiles of kThreads * kResolveRows entries, so the two contended global
+// counters cost one atomic per TILE (graveyard slots) and one per BLOCK (collision total)
+// instead of one per warp -- same-address atomics serialise in L2 at about 1 ns each.
+constexpr int kResolveRows = 8;
+
+__global__ void __launch_bounds__(kThreads)
+k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner, const int *__restrict__ cell,
+          const int *__restrict__ newcell, const unsigned char *__restrict__ flags,
+          const double2 *__restrict__ pos, const double2 *__restrict__ vel,
+          const unsigned *__restrict__ id, unsigned char *__restrict__ fate, int *count,
+          int *dead_new_count, int *mv_head, int *dm_head, int *__restrict__ mv_next,
+          double2 *__restrict__ grave_pos, double2 *__restrict__ grave_vel,
+          unsigned *__restrict__ grave_id, int *__restrict__ grave_cell, Counters *ctr) {
+    constexpr int kWarps = kThreads / 32;
+    __shared__ int warp_dying[kResolveRows][kWarps];
+    __shared__ int tile_base;
+    __shared__ unsigned warp_cnt[kWarps];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned mine = 0;
+    const int tile_len = kThreads * kResolveRows;
+    for (long long t0 = (long long)blockIdx.x * tile_len; t0 < n; t0 += (long long)gridDim.x * tile_len) {
+        unsigned char fts[kResolveRows];
+        unsigned dying_mask[kResolveRows];
+#pragma unroll
+        for (int r = 0; r < kResolveRows; r++) {
+            const long long ii = t0 + (long long)r * kThreads + threadIdx.x;
+            const int i = (int)ii;
+            int c = -2 - lane;  // lanes past the end match nobody
+            int ft = 255, nl = -1;
+            if (ii < n) {
+                c = i < n_res ? cell[i] : -40 - lane;  // guests have no bin-time cell
+                nl = newcell[i] - g.cell_base;
+                const bool in_strip = nl >= 0 && nl < g.ncells;
+                if (flags[i] & F_EMIGRANT) {
+                    ft = FATE_EMIGRATED;
+                } else {
+                    const int p = partner[i];
+                    const bool dead = p >= 0;
+                    if (dead && partner[p] == i && i < p) mine++;  // mutual-first pair, counted once
+                    if (!in_strip) ft = dead ? FATE_LEFT_DEAD : FATE_LEFT_ALIVE;
+                    else if (nl == c) ft = dead ? FATE_DEAD_HERE : FATE_STAY;
+                    else ft = dead ? FATE_DEAD_MOVED : FATE_MOVE;
+                }
+                fate[i] = (unsigned char)ft;
+            }
+            // per-cell counts: the array is cell-ordered, so a warp touches 1-3 cells
+            const unsigned grp = __match_any_sync(0xffffffffu, c);
+            const unsigned stay = __ballot_sync(0xffffffffu, ft == FATE_STAY);
+            const unsigned dhere = __ballot_sync(0xffffffffu, ft == FATE_DEAD_HERE);
+            if (c >= 0 && lane == __ffs(grp) - 1) {
+                int ns = __popc(grp & stay), nd = __popc(grp & dhere);
+                if (ns) atomicAdd(&count[c], ns);
+                if (nd) atomicAdd(&dead_new_count[c], nd);
+            }
+            if (ft == FATE_MOVE) {
+                atomicAdd(&count[nl], 1);
+                mv_next[i] = atomicExch(&mv_head[nl], i);
+            } else if (ft == FATE_DEAD_MOVED) {
+                atomicAdd(&dead_new_count[nl], 1);
+                mv_next[i] = atomicExch(&dm_head[nl], i);
+            }
+            const bool dying = ft == FATE_DEAD_HERE || ft == FATE_DEAD_MOVED || ft == FATE_LEFT_DEAD;
+            const unsigned dm = __ballot_sync(0xffffffffu, dying);
+            fts[r] = (unsigned char)ft;
+            dying_mask[r] = dm;
+            if (lane == 0) warp_dying[r][warp] = __popc(dm);
+        }
+        __syncthreads();
+        // graveyard (frozen state of the dead, for parsim_result / dumps): one reservation per tile
+        if (threadIdx.x == 0) {
+            int tot = 0;
+            for (int r = 0; r < kResolveRows; r++)
+                for (int w = 0; w < kWarps; w++) { int v = warp_dying[r][w]; warp_dying[r][w] = tot; tot += v; }
+            tile_base = tot ? atomicAdd(&ctr->grave_count, tot) : 0;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int r = 0; r < kResolveRows; r++) {
+            const int ft = fts[r];
+            if (ft == FATE_DEAD_HERE || ft == FATE_DEAD_MOVED || ft == FATE_LEFT_DEAD) {
+                const int i = (int)(t0 + (long long)r * kThreads + threadIdx.x);
+                const int slot = tile_base + warp_dying[r][warp] + __popc(dying_mask[r] & ((1u << lane) - 1u));
+                grave_pos[slot] = pos[i];
+                grave_vel[slot] = vel[i];
+                grave_id[slot] = id[i];
+                grave_cell[slot] = newcell[i];
+            }
+        }
+        __syncthreads();  // warp_dying / tile_base are reused by the next tile
+    }
+    unsigned w = __reduce_add_sync(0xffffffffu, mine);
+    if (lane == 0) warp_cnt[warp] = w;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        unsigned tot = 0;
+#pragma unroll
+        for (int k = 0; k < kWarps; k++) tot += warp_cnt[k];
+        if (tot) atomicAdd(&ctr->collisions, (unsigned long long)tot);
+    }
+}
+
+struct MoveArgs {
+    const int *cs_old, *cs_new;          // cell_start before / after
+    const int *ds_old, *ds_new;          // tombstone_start before / after (ds_new == nullptr: no dead yet)
+    const unsigned char *fate;
+    const double2 *pos_in, *vel_in;      // state of this step, old order (+ guests / immigrants behind)
+    const double *m_in;
+    const unsigned *id_in;
+    int *mv_head, *dm_head, *arr_head;   // bags; reset to -1 here for the next step
+    int *count;                          // per-cell survivor counts; reset to 0 here
+    const int *mv_next;
+    const unsigned *dead_old;
+    double2 *pos_out, *vel_out;
+    double *m_out;
+    unsigned *id_out;
+    int *cell_out;
+    unsigned *dead_new;
+};
+
+template <int LANES>
+__global__ void __launch_bounds__(kThreads) k_move(Geom g, MoveArgs a) {
+    auto tile = cg::tiled_partition<LANES>(cg::this_thread_block());
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) / LANES;
+    if (c >= g.ncells) return;  // whole tiles leave together
+    const int lane = tile.thread_rank();
+    const unsigned lt = (1u << lane) - 1u;
+    const int s = a.cs_old[c], e = a.cs_old[c + 1];
+    const int ns = a.cs_new[c];
+
+    // the first LANES arrivals live in registers (lane j holds arrival j); more are walked
+    int n_arr = 0, my_arr = -1, rest = -1;
+    unsigned my_aid = 0;
+    for (int x = a.mv_head[c]; x >= 0; x = a.mv_next[x]) {
+        if (n_arr == LANES) { rest = x; break; }
+        if (lane == n_arr) { my_arr = x; my_aid = a.id_in[x]; }
+        n_arr++;
+    }
+
+    // tombstones: old entries first
+    int doff = 0;
+    if (a.ds_new) {
+        const int ds = a.ds_old[c], de = a.ds_old[c + 1];
+        doff = a.ds_new[c];
+        for (int t = ds + lane; t < de; t += LANES) a.dead_new[doff + (t - ds)] = a.dead_old[t];
+        doff += de - ds;
+    }
+
+    // stayers keep their order; each adds the number of arrivals with a smaller id
+    int run = 0;
+    for (int base = s; base < e; base += LANES) {
+        const int k = base + lane;
+        const int ft = k < e ? a.fate[k] : 255;
+        const unsigned me = k < e ? a.id_in[k] : 0u;
+        const unsigned smask = tile.ballot(ft == FATE_STAY);
+        int before = 0;  // arrivals with a smaller id (shuffles stay outside divergent code)
+        for (int j = 0; j < n_arr; j++) before += tile.shfl(my_aid, j) < me ? 1 : 0;
+        if (ft == FATE_STAY) {
+            int r = run + __popc(smask & lt) + before;
+            for (int x = rest; x >= 0; x = a.mv_next[x]) r += a.id_in[x] < me ? 1 : 0;
+            const int o = ns + r;
+            a.pos_out[o] = a.pos_in[k];
+            a.vel_out[o] = a.vel_in[k];
+            a.m_out[o] = a.m_in[k];
+            a.id_out[o] = me;
+            a.cell_out[o] = c;
+        }
+        run += __popc(smask);
+        if (a.ds_new) {
+            const unsigned dmask = tile.ballot(ft == FATE_DEAD_HERE);
+            if (ft == FATE_DEAD_HERE) a.dead_new[doff + __popc(dmask & lt)] = me;
+            doff += __popc(dmask);
+        }
+    }
+
+    // arrivals: position = stayers with a smaller id + arrivals with a smaller id
+    for (int x = a.mv_head[c]; x >= 0; x = a.mv_next[x]) {
+        const unsigned aid = a.id_in[x];
+        int r = 0;
+        for (int base = s; base < e; base += LANES) {
+            const int k = base + lane;
+            const bool less = k < e && a.fate[k] == FATE_STAY && a.id_in[k] < aid;
+            r += __popc(tile.ballot(less));
+        }
+        for (int y = a.mv_head[c]; y >= 0; y = a.mv_next[y]) r += a.id_in[y] < aid ? 1 : 0;
+        if (lane == 0) {
+            const int o = ns + r;
+            a.pos_out[o] = a.pos_in[x];
+            a.vel_out[o] = a.vel_in[x];
+            a.m_out[o] = a.m_in[x];
+            a.id_out[o] = aid;
+            a.cell_out[o] = c;
+        }
+    }
+    // tombstones of particles that died this step and came to rest in this cell from elsewhere
+    if (a.ds_new && lane == 0)
+        for (int x = a.dm_head[c]; x >= 0; x = a.mv_next[x]) a.dead_new[doff++] = a.id_in[x];
+    tile.sync();
+    if (lane == 0) {
+        a.mv_head[c] = -1;
+        a.dm_head[c] = -1;
+        a.arr_head[c] = -1;
+        a.count[c] = 0;
+    }
+}
+
+}  // namespace parsim

@@ -2,6 +2,7 @@
 #include "parsim_rank.cuh"
 
 #include <math.h>
+#include <stddef.h>
 #include <string.h>
 
 #include <algorithm>
@@ -62,6 +63,11 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     g.ncells = g.rows * g.nc;
     g.cell_base = g.row0 * g.nc;
     c->thr2 = collision_threshold2();
+    {   // |float(x) - x| <= side * 2^-24, so an FP32 coordinate difference is off by < side * 2.5e-7
+        double delta = side * 2.5e-7;
+        double t = (kEpsilon + 1.5 * delta) * (kEpsilon + 1.5 * delta) * (1.0 + 1e-5);
+        c->thrf = nextafterf((float)t, INFINITY);
+    }
     double ppc = (double)n_part / ((double)ncside * (double)ncside);
     c->com_lanes = ppc <= 6 ? 4 : ppc <= 12 ? 8 : ppc <= 24 ? 16 : 32;
 
@@ -86,6 +92,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     const size_t N = (size_t)c->cap, C = (size_t)g.ncells;
     PS_ALLOC(c, c->pos_cur, N, false); PS_ALLOC(c, c->pos_alt, N, false);
     PS_ALLOC(c, c->vel_cur, N, false); PS_ALLOC(c, c->vel_alt, N, false);
+    PS_ALLOC(c, c->posf, N, false);
     PS_ALLOC(c, c->m_cur, N, false);   PS_ALLOC(c, c->m_alt, N, false);
     PS_ALLOC(c, c->id_cur, N, false);  PS_ALLOC(c, c->id_alt, N, false);
     PS_ALLOC(c, c->cell_cur, N, false); PS_ALLOC(c, c->cell_alt, N, false);
@@ -96,13 +103,14 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     PS_ALLOC(c, c->partner, N, false); PS_ALLOC(c, c->tmp_src, N, false);
     PS_ALLOC(c, c->tmp_id, N, false);
     PS_ALLOC(c, c->arr_head, C, false); PS_ALLOC(c, c->arr_next, N, false);
+    PS_ALLOC(c, c->mv_head, C, false); PS_ALLOC(c, c->dm_head, C, false); PS_ALLOC(c, c->mv_next, N, false);
+    PS_ALLOC(c, c->fate, N, true);
     PS_ALLOC(c, c->flags, N, true);
     PS_ALLOC(c, c->com_xy, (size_t)(g.rows + 2) * g.nc, true);
     PS_ALLOC(c, c->com_m, (size_t)(g.rows + 2) * g.nc, true);
     PS_ALLOC(c, c->dead_count, C, true); PS_ALLOC(c, c->dead_new_count, C, true);
     PS_ALLOC(c, c->dead_start_cur, C + 1, true); PS_ALLOC(c, c->dead_start_alt, C + 1, true);
     PS_ALLOC(c, c->dead_id_cur, N, false); PS_ALLOC(c, c->dead_id_alt, N, false);
-    PS_ALLOC(c, c->dead_cell_cur, N, false); PS_ALLOC(c, c->dead_cell_alt, N, false);
     PS_ALLOC(c, c->grave_pos, N, false); PS_ALLOC(c, c->grave_vel, N, false);
     PS_ALLOC(c, c->grave_id, N, false); PS_ALLOC(c, c->grave_cell, N, false);
     PS_ALLOC(c, c->d_ctr, 1, true);
@@ -129,8 +137,8 @@ void rank_destroy(Rank *c) {
                     c->dst, c->newcell, c->partner, c->tmp_src, c->tmp_id, c->arr_head, c->arr_next,
                     c->flags, c->com_xy, c->com_m, c->dbg_acc, c->dead_count, c->dead_new_count,
                     c->dead_start_cur, c->dead_start_alt, c->dead_id_cur, c->dead_id_alt,
-                    c->dead_cell_cur, c->dead_cell_alt, c->grave_pos, c->grave_vel, c->grave_id,
-                    c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->pos0, c->vel0,
+                    c->mv_head, c->dm_head, c->mv_next, c->fate, c->grave_pos, c->grave_vel, c->grave_id,
+                    c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->posf, c->pos0, c->vel0,
                     c->m0, c->id0, c->stage_ids, c->stage[0],
                     c->stage[1], c->stage[2], c->stage[3], c->stage[4]};
     for (void *p : ptrs) if (p) cudaFree(p);
@@ -152,11 +160,17 @@ static int reset_state(Rank *c) {
     c->n_tomb = 0; c->n_grave = 0; c->steps_done = 0; c->collisions_total = 0;
     c->have_newcell = c->have_flags = false;
     c->pos_latest = c->pos_cur;
-    PS_CUDA(c, cudaMemsetAsync(c->d_ctr, 0, sizeof(Counters), c->stream));
+    // everything but the four statistics counters (parsim_stats_reset clears those)
+    PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->collisions, 0, sizeof(unsigned long long), c->stream));
+    PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->deaths_step, 0, sizeof(Counters) - offsetof(Counters, deaths_step),
+                               c->stream));
     PS_CUDA(c, cudaMemsetAsync(c->count, 0, sizeof(int) * C, c->stream));
     PS_CUDA(c, cudaMemsetAsync(c->dead_count, 0, sizeof(int) * C, c->stream));
     PS_CUDA(c, cudaMemsetAsync(c->dead_new_count, 0, sizeof(int) * C, c->stream));
     PS_CUDA(c, cudaMemsetAsync(c->dead_start_cur, 0, sizeof(int) * (C + 1), c->stream));
+    PS_CUDA(c, cudaMemsetAsync(c->arr_head, 0xFF, sizeof(int) * C, c->stream));  // empty bags (-1)
+    PS_CUDA(c, cudaMemsetAsync(c->mv_head, 0xFF, sizeof(int) * C, c->stream));
+    PS_CUDA(c, cudaMemsetAsync(c->dm_head, 0xFF, sizeof(int) * C, c->stream));
     return 0;
 }
 

@@ -9,13 +9,14 @@
 
 #include "../../include/parsim_b200.h"
 #include "parsim_kernels.cuh"
+#include "parsim_merge.cuh"
 #include "parsim_nccl.hpp"
 
 namespace parsim {
 
 enum KernelId {
     K_INGEST = 0, K_BIN_KEYS, K_SCAN, K_REBIN_SCATTER, K_REBIN_GATHER, K_COM, K_GHOST, K_FORCE,
-    K_CLASSIFY, K_COLLIDE, K_RESOLVE, K_TOMBSTONES, K_MIGRATE, K_INIT, K_MISC, K_COUNT_
+    K_CLASSIFY, K_COLLIDE, K_RESOLVE, K_TOMBSTONES, K_MIGRATE, K_INIT, K_MOVE, K_COUNT_
 };
 static_assert(K_COUNT_ <= PARSIM_NKERNELS, "grow PARSIM_NKERNELS");
 
@@ -47,11 +48,15 @@ struct Rank {
     int *cell_cur = nullptr, *cell_alt = nullptr;
     int *cs_cur = nullptr, *cs_alt = nullptr;  // cell_start[ncells+1]
     double2 *pos_latest = nullptr;             // where the newest positions are (dumps)
+    float2 *posf = nullptr;                    // FP32 copy of the post-move positions (collision pre-filter)
+    float thrf = 0;                            // pre-filter threshold on the FP32 squared distance
     bool have_newcell = false, have_flags = false;
 
     int *count = nullptr, *tile_sums = nullptr;
     int *dst = nullptr, *newcell = nullptr, *partner = nullptr, *tmp_src = nullptr;
     int *arr_head = nullptr, *arr_next = nullptr, *guest_src = nullptr;
+    int *mv_head = nullptr, *dm_head = nullptr, *mv_next = nullptr;  // end-of-step move / dead bags
+    unsigned char *fate = nullptr;
     unsigned *tmp_id = nullptr;
     unsigned char *flags = nullptr;
     double2 *com_xy = nullptr;
@@ -62,7 +67,6 @@ struct Rank {
     int *dead_count = nullptr, *dead_new_count = nullptr;
     int *dead_start_cur = nullptr, *dead_start_alt = nullptr;
     unsigned *dead_id_cur = nullptr, *dead_id_alt = nullptr;
-    int *dead_cell_cur = nullptr, *dead_cell_alt = nullptr;
     int n_tomb = 0;  // entries in the dead CSR of this strip
     double2 *grave_pos = nullptr, *grave_vel = nullptr;
     unsigned *grave_id = nullptr;
@@ -97,7 +101,7 @@ struct Rank {
     std::string err;
 
     // options / stats
-    bool opt_stats = false, opt_full_rebin = false, opt_sync_check = false;
+    bool opt_stats = false, opt_sync_check = false;
     double capacity_factor = 1.35;
     parsim_stats_t stats{};
     std::vector<TimedLaunch> pending;

@@ -35,31 +35,51 @@ static int rebin(Rank *c, int n_src, const double2 *pos_src, double2 *pos_out) {
     return 0;
 }
 
-// Merge new tombstones into the dead CSR.  Sources: this step's graveyard slice and (multi
-// strip) the tombstones received from the neighbours; both were already counted into
-// dead_new_count[] for the cells of this strip.
-static int tombstones_update(Rank *c, int grave_first, int grave_cnt, int inbox_cnt) {
+template <int LANES>
+static void launch_move(Rank *c, const MoveArgs &a) {
+    long long threads = (long long)c->g.ncells * LANES;
+    k_move<LANES><<<grid_for(threads), kThreads, 0, c->stream>>>(c->g, a);
+}
+
+// End of step: new cell_start (and tombstone_start) by scan, then the per-cell merge.
+// Sources are entries [0, n_src) of (pos_alt, vel_cur, m_cur, id_cur) with their fate byte.
+static int merge_step(Rank *c, int n_src, int n_surv, bool with_dead) {
     const Geom &g = c->g;
-    int bound_old = c->n_tomb;
-    PS_LAUNCH(c, K_TOMBSTONES, 12.0 * g.ncells, "k_add_counts",
-              k_add_counts<<<grid_for(g.ncells), kThreads, 0, c->stream>>>(g.ncells, c->dead_count,
-                                                                           c->dead_new_count));
-    if (device_scan(c, c->dead_count, g.ncells, c->dead_start_alt, nullptr)) return 1;
-    if (bound_old > 0)
-        PS_LAUNCH(c, K_TOMBSTONES, 16.0 * bound_old, "k_dead_copy_old",
-                  k_dead_copy_old<<<grid_for(bound_old), kThreads, 0, c->stream>>>(
-                      bound_old, c->dead_start_cur, g.ncells, c->dead_start_alt, c->dead_id_cur,
-                      c->dead_cell_cur, c->dead_id_alt, c->dead_cell_alt));
-    if (grave_cnt > 0)
-        PS_LAUNCH(c, K_TOMBSTONES, 16.0 * grave_cnt, "k_dead_append",
-                  k_dead_append<<<grid_for(grave_cnt), kThreads, 0, c->stream>>>(
-                      g, grave_cnt, c->grave_id + grave_first, c->grave_cell + grave_first,
-                      c->dead_start_alt, c->dead_new_count, c->dead_id_alt, c->dead_cell_alt));
-    if (inbox_cnt > 0 && exchange_append_tombstones(c, inbox_cnt)) return 1;
-    std::swap(c->dead_start_cur, c->dead_start_alt);
-    std::swap(c->dead_id_cur, c->dead_id_alt);
-    std::swap(c->dead_cell_cur, c->dead_cell_alt);
-    c->n_tomb = bound_old + grave_cnt + inbox_cnt;  // upper bound; exact total is dead_start[ncells]
+    if (device_scan(c, c->count, g.ncells, c->cs_alt, &c->d_ctr->n_next)) return 1;
+    if (with_dead) {
+        PS_LAUNCH(c, K_TOMBSTONES, 12.0 * g.ncells, "k_add_counts",
+                  k_add_counts<<<grid_for(g.ncells), kThreads, 0, c->stream>>>(g.ncells, c->dead_count,
+                                                                               c->dead_new_count));
+        if (device_scan(c, c->dead_count, g.ncells, c->dead_start_alt, nullptr)) return 1;
+    }
+    MoveArgs a;
+    a.cs_old = c->cs_cur; a.cs_new = c->cs_alt;
+    a.ds_old = c->dead_start_cur; a.ds_new = with_dead ? c->dead_start_alt : nullptr;
+    a.fate = c->fate;
+    a.pos_in = c->pos_alt; a.vel_in = c->vel_cur; a.m_in = c->m_cur; a.id_in = c->id_cur;
+    a.mv_head = c->mv_head; a.dm_head = c->dm_head; a.arr_head = c->arr_head; a.count = c->count;
+    a.mv_next = c->mv_next;
+    a.dead_old = c->dead_id_cur; a.dead_new = c->dead_id_alt;
+    a.pos_out = c->pos_cur; a.vel_out = c->vel_alt; a.m_out = c->m_alt; a.id_out = c->id_alt;
+    a.cell_out = c->cell_alt;
+    // 1 fate + 4 id read per source entry, 40 read + 48 written per survivor, 8 B per tombstone
+    PS_LAUNCH(c, K_MOVE, 5.0 * n_src + 88.0 * n_surv + 16.0 * g.ncells + (with_dead ? 8.0 * c->n_tomb : 0.0), "k_move", {
+        switch (c->com_lanes) {
+        case 4: launch_move<4>(c, a); break;
+        case 8: launch_move<8>(c, a); break;
+        case 16: launch_move<16>(c, a); break;
+        default: launch_move<32>(c, a); break;
+        }
+    });
+    std::swap(c->vel_cur, c->vel_alt);
+    std::swap(c->m_cur, c->m_alt);
+    std::swap(c->id_cur, c->id_alt);
+    std::swap(c->cell_cur, c->cell_alt);
+    std::swap(c->cs_cur, c->cs_alt);
+    if (with_dead) {
+        std::swap(c->dead_start_cur, c->dead_start_alt);
+        std::swap(c->dead_id_cur, c->dead_id_alt);
+    }
     return 0;
 }
 
@@ -106,7 +126,7 @@ static int stage_force(Rank *c) {
     PS_LAUNCH(c, K_FORCE, 80.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate",
               k_force_integrate<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
                   c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,
-                  c->pos_alt, c->vel_cur, c->newcell, c->dbg_acc));
+                  c->pos_alt, c->posf, c->vel_cur, c->newcell, c->dbg_acc));
     c->pos_latest = c->pos_alt;
     c->have_newcell = true;
     return 0;
@@ -115,12 +135,11 @@ static int stage_force(Rank *c) {
 // stage 2: list update (movers / strays), and emigrants to the neighbouring strips
 static int stage_lists(Rank *c) {
     const Geom &g = c->g;
-    PS_CUDA(c, cudaMemsetAsync(c->arr_head, 0xFF, sizeof(int) * (size_t)g.ncells, c->stream));
     PS_LAUNCH(c, K_CLASSIFY, 9.0 * c->n_alive + 4.0 * g.ncells, "k_classify",
               k_classify<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
                   g, c->n_alive, c->cell_cur, c->cs_cur, c->newcell, c->id_cur,
                   c->n_tomb > 0 ? c->dead_start_cur : nullptr, c->dead_id_cur, c->flags, c->arr_head,
-                  c->arr_next, c->d_ctr));
+                  c->arr_next, c->opt_stats ? &c->d_ctr->movers : nullptr, &c->d_ctr->strays));
     c->n_guest = 0;
     if (c->nranks > 1 && exchange_emigrants(c)) return 1;
     c->have_flags = true;
@@ -133,28 +152,27 @@ static int stage_collide(Rank *c) {
     const int n_tot = c->n_alive + c->n_guest;
     PS_LAUNCH(c, K_COLLIDE, 21.0 * n_tot + 8.0 * g.ncells, "k_collide_find",
               k_collide_find<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
-                  g, n_tot, c->n_alive, c->thr2, c->pos_alt, c->cell_cur, c->cs_cur, c->newcell,
+                  g, n_tot, c->n_alive, c->thr2, c->thrf, c->pos_alt, c->posf, c->cell_cur, c->cs_cur, c->newcell,
                   c->id_cur, c->flags, c->arr_head, c->arr_next, c->guest_src, c->partner,
                   c->opt_stats ? &c->d_ctr->collision_pairs : nullptr));
-    PS_LAUNCH(c, K_RESOLVE, 17.0 * n_tot, "k_resolve",
-              k_resolve<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
-                  g, n_tot, c->n_alive, c->partner, c->newcell, c->flags, c->pos_alt, c->vel_cur,
-                  c->id_cur, c->dst, c->count, c->dead_new_count, c->grave_pos, c->grave_vel,
-                  c->grave_id, c->grave_cell, c->d_ctr));
+    PS_LAUNCH(c, K_RESOLVE, 10.0 * n_tot, "k_resolve",
+              k_resolve<<<std::min(grid_for(n_tot, kThreads * kResolveRows), 148 * 8), kThreads, 0, c->stream>>>(
+                  g, n_tot, c->n_alive, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,
+                  c->vel_cur, c->id_cur, c->fate, c->count, c->dead_new_count, c->mv_head, c->dm_head,
+                  c->mv_next, c->grave_pos, c->grave_vel, c->grave_id, c->grave_cell, c->d_ctr));
     PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error));
     const int grave_first = c->n_grave;
     const int deaths = c->h_ctr->grave_count - grave_first;
     c->n_grave = c->h_ctr->grave_count;
-    int n_src = n_tot, inbox = 0, n_next;
+    int n_src = n_tot, tomb_in = 0, n_next;
     if (c->nranks > 1) {
-        if (exchange_late(c, grave_first, deaths, &n_src, &inbox)) return 1;
+        if (exchange_late(c, &n_src, &tomb_in)) return 1;
     }
-    if (deaths > 0 || inbox > 0) {
-        if (tombstones_update(c, grave_first, deaths, inbox)) return 1;
-    }
-    if (rebin(c, n_src, c->pos_alt, c->pos_cur)) return 1;
+    const bool with_dead = c->n_tomb > 0 || deaths > 0 || tomb_in > 0;
+    if (merge_step(c, n_src, n_src - deaths, with_dead)) return 1;
+    c->n_tomb += deaths + tomb_in;  // upper bound; exact total is dead_start[ncells]
     if (c->nranks == 1) {
         n_next = n_tot - deaths;
     } else {
