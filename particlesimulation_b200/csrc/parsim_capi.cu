@@ -230,7 +230,7 @@ int parsim_dump_cells(parsim_ctx *ctx, double *mx, double *my, double *m) {
 
 const char *parsim_kernel_name(int k) {
     static const char *names[K_COUNT_] = {
-        "ingest", "bin_keys", "scan", "rebin_scatter", "rebin_gather", "com", "ghost_rows",
+        "ingest", "bin_keys", "scan", "sort_passes", "sort_gather", "com", "ghost_rows",
         "force_integrate", "classify_movers", "collide_find", "collide_resolve", "tombstones",
         "migrate", "init_particles", "merge_move"};
     return (k >= 0 && k < K_COUNT_) ? names[k] : nullptr;

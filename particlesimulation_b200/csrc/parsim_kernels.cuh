@@ -195,18 +195,6 @@ __global__ void k_fp64_peak(int iters, double *out) {
 }
 
 // ---------------------------------------------------------------------------------------
-// Binning keys for particles in arbitrary order (step 0, or the full_rebin option):
-// dst[i] = local cell of the current position, histogram into count[] (north_star (a)).
-__global__ void k_bin_keys(Geom g, int n, const double2 *__restrict__ pos, int *__restrict__ dst,
-                           int *count) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    int c = global_cell(pos[i], g) - g.cell_base;
-    dst[i] = c;  // uploads are filtered by strip, so 0 <= c < ncells
-    atomicAdd(&count[c], 1);
-}
-
-// ---------------------------------------------------------------------------------------
 // Device-wide exclusive scan of int counts (three small kernels; the data is 4 B per CELL,
 // not per particle).  out has N+1 entries, out[N] = total.
 constexpr int kScanItems = 8;
@@ -293,48 +281,6 @@ __global__ void k_scan_apply(const int *__restrict__ in, const int *__restrict__
         if (k < N) out[k] = ex;
         ex += v[j];
     }
-}
-
-// ---------------------------------------------------------------------------------------
-// Rebin, pass 1: claim a slot inside the destination cell's segment.  The claim order is
-// arbitrary (atomics); pass 2 orders each cell by id, so the final layout is deterministic.
-// count[] is consumed back to zero by the atomicSub, so it needs no memset per step.
-__global__ void k_rebin_scatter(int n_src, const int *__restrict__ dst,
-                                const unsigned *__restrict__ id, const int *__restrict__ start,
-                                int *count, int *__restrict__ tmp_src, unsigned *__restrict__ tmp_id,
-                                int *__restrict__ cell_out) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_src) return;
-    int c = dst[i];
-    if (c < 0) return;  // dead, or emigrated to another strip
-    int slot = start[c + 1] - atomicSub(&count[c], 1);
-    tmp_src[slot] = i;
-    tmp_id[slot] = id[i];
-    cell_out[slot] = c;
-}
-
-// Rebin, pass 2: rank by id inside the cell (the reference's bin-time list order is ascending
-// particle index, serial/parsim.cpp:265,:285) and move the 44-byte state once.
-__global__ void k_rebin_gather(const int *__restrict__ n_out_ptr, const int *__restrict__ cell_out,
-                               const int *__restrict__ start, const int *__restrict__ tmp_src,
-                               const unsigned *__restrict__ tmp_id,
-                               const double2 *__restrict__ pos_in, const double2 *__restrict__ vel_in,
-                               const double *__restrict__ m_in, double2 *__restrict__ pos_out,
-                               double2 *__restrict__ vel_out, double *__restrict__ m_out,
-                               unsigned *__restrict__ id_out) {
-    int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= *n_out_ptr) return;
-    int c = cell_out[p];
-    unsigned me = tmp_id[p];
-    int s = start[c], e = start[c + 1];
-    int rank = 0;
-    for (int q = s; q < e; q++) rank += (tmp_id[q] < me) ? 1 : 0;
-    int o = s + rank;
-    int src = tmp_src[p];
-    pos_out[o] = pos_in[src];
-    vel_out[o] = vel_in[src];
-    m_out[o] = m_in[src];
-    id_out[o] = me;
 }
 
 // ---------------------------------------------------------------------------------------

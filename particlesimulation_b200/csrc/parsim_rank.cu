@@ -98,9 +98,11 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     PS_ALLOC(c, c->cell_cur, N, false); PS_ALLOC(c, c->cell_alt, N, false);
     PS_ALLOC(c, c->cs_cur, C + 1, true); PS_ALLOC(c, c->cs_alt, C + 1, true);
     PS_ALLOC(c, c->count, C, true);
-    PS_ALLOC(c, c->tile_sums, C / kScanTile + 2, true);
-    PS_ALLOC(c, c->dst, N, false); PS_ALLOC(c, c->newcell, N, false);
-    PS_ALLOC(c, c->partner, N, false); PS_ALLOC(c, c->tmp_src, N, false);
+    const size_t H = (size_t)kSortMaxBins * (N / kSortTile + 1);  // radix-sort tile histograms
+    PS_ALLOC(c, c->tile_sums, std::max(C, H) / kScanTile + 2, true);
+    PS_ALLOC(c, c->sort_hist, H, false); PS_ALLOC(c, c->sort_hist_scan, H + 1, false);
+    PS_ALLOC(c, c->newcell, N, false);
+    PS_ALLOC(c, c->partner, N, false);
     PS_ALLOC(c, c->tmp_id, N, false);
     PS_ALLOC(c, c->arr_head, C, false); PS_ALLOC(c, c->arr_next, N, false);
     PS_ALLOC(c, c->mv_head, C, false); PS_ALLOC(c, c->dm_head, C, false); PS_ALLOC(c, c->mv_next, N, false);
@@ -134,7 +136,7 @@ void rank_destroy(Rank *c) {
     exchange_destroy(c);
     void *ptrs[] = {c->pos_cur, c->pos_alt, c->vel_cur, c->vel_alt, c->m_cur, c->m_alt, c->id_cur,
                     c->id_alt, c->cell_cur, c->cell_alt, c->cs_cur, c->cs_alt, c->count, c->tile_sums,
-                    c->dst, c->newcell, c->partner, c->tmp_src, c->tmp_id, c->arr_head, c->arr_next,
+                    c->sort_hist, c->sort_hist_scan, c->newcell, c->partner, c->tmp_id, c->arr_head, c->arr_next,
                     c->flags, c->com_xy, c->com_m, c->dbg_acc, c->dead_count, c->dead_new_count,
                     c->dead_start_cur, c->dead_start_alt, c->dead_id_cur, c->dead_id_alt,
                     c->mv_head, c->dm_head, c->mv_next, c->fate, c->grave_pos, c->grave_vel, c->grave_id,

@@ -10,12 +10,13 @@
 #include "../../include/parsim_b200.h"
 #include "parsim_kernels.cuh"
 #include "parsim_merge.cuh"
+#include "parsim_sort.cuh"
 #include "parsim_nccl.hpp"
 
 namespace parsim {
 
 enum KernelId {
-    K_INGEST = 0, K_BIN_KEYS, K_SCAN, K_REBIN_SCATTER, K_REBIN_GATHER, K_COM, K_GHOST, K_FORCE,
+    K_INGEST = 0, K_BIN_KEYS, K_SCAN, K_SORT_PASS, K_SORT_GATHER, K_COM, K_GHOST, K_FORCE,
     K_CLASSIFY, K_COLLIDE, K_RESOLVE, K_TOMBSTONES, K_MIGRATE, K_INIT, K_MOVE, K_COUNT_
 };
 static_assert(K_COUNT_ <= PARSIM_NKERNELS, "grow PARSIM_NKERNELS");
@@ -53,7 +54,8 @@ struct Rank {
     bool have_newcell = false, have_flags = false;
 
     int *count = nullptr, *tile_sums = nullptr;
-    int *dst = nullptr, *newcell = nullptr, *partner = nullptr, *tmp_src = nullptr;
+    int *newcell = nullptr, *partner = nullptr;
+    int *sort_hist = nullptr, *sort_hist_scan = nullptr;  // radix-sort tile histograms (step 0)
     int *arr_head = nullptr, *arr_next = nullptr, *guest_src = nullptr;
     int *mv_head = nullptr, *dm_head = nullptr, *mv_next = nullptr;  // end-of-step move / dead bags
     unsigned char *fate = nullptr;

@@ -14,19 +14,75 @@ static int device_scan(Rank *c, const int *in, int N, int *out, int *total2) {
     return 0;
 }
 
-// Sort the n_src source entries (state in pos_src, vel_cur, m_cur, id_cur; destination cell in
-// dst[], already histogrammed into count[]) into (cell, id) order.  Output: pos_out, *_alt,
-// cs_alt; then the non-position buffers are swapped.  Entries with dst < 0 are dropped.
-static int rebin(Rank *c, int n_src, const double2 *pos_src, double2 *pos_out) {
+// One stable radix pass over `bits` key bits starting at bit 0 of keyA (digits of <= 8 bits).
+// Entries are (keyA, srcA); srcA == nullptr means source = index.  Results end in (keyA, srcA).
+static int sort_passes(Rank *c, int n, int bits, unsigned *&keyA, unsigned *&keyB, int *&srcA, int *&srcB,
+                       bool src_implicit) {
+    const int passes = (bits + 7) / 8;
+    const int dbits = (bits + passes - 1) / passes;
+    const int ntiles = (n + kSortTile - 1) / kSortTile;
+    for (int p = 0; p < passes; p++) {
+        const int shift = p * dbits;
+        const unsigned mask = (1u << dbits) - 1u;
+        const int nb = (int)mask + 1;
+        PS_LAUNCH(c, K_SORT_PASS, 4.0 * n, "k_sort_hist",
+                  k_sort_hist<<<ntiles, kSortThreads, 0, c->stream>>>(n, keyA, shift, mask, ntiles, c->sort_hist));
+        if (device_scan(c, c->sort_hist, nb * ntiles, c->sort_hist_scan, nullptr)) return 1;
+        PS_LAUNCH(c, K_SORT_PASS, 16.0 * n, "k_sort_scatter",
+                  k_sort_scatter<<<ntiles, kSortThreads, 0, c->stream>>>(
+                      n, keyA, src_implicit ? nullptr : srcA, shift, mask, ntiles, c->sort_hist_scan, keyB, srcB));
+        std::swap(keyA, keyB);
+        std::swap(srcA, srcB);
+        src_implicit = false;
+    }
+    return 0;
+}
+
+static int bits_for(unsigned long long max_value) {
+    int b = 1;
+    while (b < 63 && (max_value >> b)) b++;
+    return b;
+}
+
+// Step 0: bring the uploaded particles (arbitrary slots) into (cell, id) order -- the binning of
+// updateCOM (serial/parsim.cpp:265-285) done once; later steps keep the order by merging.
+static int sort_initial(Rank *c) {
     const Geom &g = c->g;
-    if (device_scan(c, c->count, g.ncells, c->cs_alt, &c->d_ctr->n_next)) return 1;
-    PS_LAUNCH(c, K_REBIN_SCATTER, 20.0 * n_src, "k_rebin_scatter",
-              k_rebin_scatter<<<grid_for(n_src), kThreads, 0, c->stream>>>(
-                  n_src, c->dst, c->id_cur, c->cs_alt, c->count, c->tmp_src, c->tmp_id, c->cell_alt));
-    PS_LAUNCH(c, K_REBIN_GATHER, 100.0 * n_src, "k_rebin_gather",
-              k_rebin_gather<<<grid_for(n_src), kThreads, 0, c->stream>>>(
-                  &c->d_ctr->n_next, c->cell_alt, c->cs_alt, c->tmp_src, c->tmp_id, pos_src,
-                  c->vel_cur, c->m_cur, pos_out, c->vel_alt, c->m_alt, c->id_alt));
+    const int n = c->n_alive;
+    if (n == 0) {
+        PS_CUDA(c, cudaMemsetAsync(c->cs_cur, 0, sizeof(int) * ((size_t)g.ncells + 1), c->stream));
+        return 0;
+    }
+    unsigned *keyA = (unsigned *)c->newcell, *keyB = (unsigned *)c->partner;
+    int *srcA = c->arr_next, *srcB = c->mv_next;
+    PS_CUDA(c, cudaMemsetAsync(c->d_found, 0, sizeof(int), c->stream));
+    k_ids_ascending<<<grid_for(n), kThreads, 0, c->stream>>>(n, c->id_cur, c->d_found);
+    int unordered = 0;
+    PS_CUDA(c, cudaMemcpyAsync(&unordered, c->d_found, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaStreamSynchronize(c->stream));
+    const int cell_bits = bits_for((unsigned long long)std::max(g.ncells - 1, 1));
+    if (!unordered) {
+        PS_LAUNCH(c, K_BIN_KEYS, 20.0 * n, "k_sort_cell_of",
+                  k_sort_cell_of<<<grid_for(n), kThreads, 0, c->stream>>>(g, n, c->pos_cur, keyA));
+        if (sort_passes(c, n, cell_bits, keyA, keyB, srcA, srcB, true)) return 1;
+    } else {
+        // slots are not in id order: sort by id first (LSD), then by cell
+        PS_LAUNCH(c, K_BIN_KEYS, 20.0 * n, "k_sort_cell_of",
+                  k_sort_cell_of<<<grid_for(n), kThreads, 0, c->stream>>>(g, n, c->pos_cur, c->tmp_id));
+        PS_LAUNCH(c, K_SORT_PASS, 8.0 * n, "k_sort_id_keys",
+                  k_sort_id_keys<<<grid_for(n), kThreads, 0, c->stream>>>(n, nullptr, c->id_cur, keyA));
+        if (sort_passes(c, n, bits_for((unsigned long long)std::max<long long>(c->n_part - 1, 1)), keyA, keyB,
+                        srcA, srcB, true))
+            return 1;
+        PS_LAUNCH(c, K_SORT_PASS, 12.0 * n, "k_sort_cell_keys",
+                  k_sort_cell_keys<<<grid_for(n), kThreads, 0, c->stream>>>(n, srcA, c->tmp_id, keyA));
+        if (sort_passes(c, n, cell_bits, keyA, keyB, srcA, srcB, false)) return 1;
+    }
+    PS_LAUNCH(c, K_SORT_GATHER, 100.0 * n + 4.0 * g.ncells, "k_sort_gather",
+              k_sort_gather<<<grid_for(n), kThreads, 0, c->stream>>>(
+                  n, g.ncells, keyA, srcA, c->pos_cur, c->vel_cur, c->m_cur, c->id_cur, c->pos_alt, c->vel_alt,
+                  c->m_alt, c->id_alt, c->cell_alt, c->cs_alt));
+    std::swap(c->pos_cur, c->pos_alt);
     std::swap(c->vel_cur, c->vel_alt);
     std::swap(c->m_cur, c->m_alt);
     std::swap(c->id_cur, c->id_alt);
@@ -95,11 +151,7 @@ static void launch_com(Rank *c) {
 static int stage_bin_com(Rank *c) {
     const Geom &g = c->g;
     if (!c->sorted) {
-        PS_LAUNCH(c, K_BIN_KEYS, 20.0 * c->n_alive, "k_bin_keys",
-                  k_bin_keys<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(g, c->n_alive, c->pos_cur,
-                                                                               c->dst, c->count));
-        if (rebin(c, c->n_alive, c->pos_cur, c->pos_alt)) return 1;
-        std::swap(c->pos_cur, c->pos_alt);
+        if (sort_initial(c)) return 1;
         c->sorted = true;
     }
     PS_LAUNCH(c, K_COM, 24.0 * c->n_alive + 24.0 * g.ncells, "k_com", {
