@@ -232,7 +232,7 @@ const char *parsim_kernel_name(int k) {
     static const char *names[K_COUNT_] = {
         "ingest", "bin_keys", "scan", "sort_passes", "sort_gather", "com", "ghost_rows",
         "force_integrate", "classify_movers", "collide_find", "collide_resolve", "tombstones",
-        "migrate", "init_particles", "merge_move"};
+        "migrate", "init_particles", "merge_move", "collide_big_cells"};
     return (k >= 0 && k < K_COUNT_) ? names[k] : nullptr;
 }
 

@@ -61,7 +61,7 @@ __global__ void k_pack_emigrants(Geom g, int n, int mig_cap, const unsigned char
 __global__ void k_unpack_guests(Geom g, int n_rec, const double *__restrict__ recv, int first_idx,
                                 int guest_first, double2 *pos, float2 *posf, double2 *vel, double *m, unsigned *id,
                                 int *cell, int *newcell, unsigned char *flags, int *guest_src,
-                                int *arr_head, int *arr_next, Counters *ctr) {
+                                int *arr_head, int *arr_next, int *arr_cnt, Counters *ctr) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_rec) return;
     const double *r = recv + (size_t)t * kRec;
@@ -71,7 +71,7 @@ __global__ void k_unpack_guests(Geom g, int n_rec, const double *__restrict__ re
     int dst = dstg - g.cell_base;
     if (dst < 0 || dst >= g.ncells) { ctr->error = DE_LONG_JUMP; return; }
     pos[idx] = make_double2(r[0], r[1]);
-    posf[idx] = make_float2((float)r[0], (float)r[1]);
+    if (posf) posf[idx] = make_float2((float)r[0], (float)r[1]);
     vel[idx] = make_double2(r[2], r[3]);
     m[idx] = r[4];
     id[idx] = (unsigned)(a & 0xffffffffu);
@@ -80,6 +80,7 @@ __global__ void k_unpack_guests(Geom g, int n_rec, const double *__restrict__ re
     flags[idx] = F_MOVER | F_REMOVED | F_GUEST;
     guest_src[guest_first + t] = (int)(unsigned)(a >> 32);
     arr_next[idx] = atomicExch(&arr_head[dst], idx);
+    if (arr_cnt) atomicAdd(&arr_cnt[dst], 1 << 20);  // guests have no arrival record: the bag is walked
 }
 
 // after the collisions: strays that survived but now lie in another strip (kind 0) and
@@ -244,11 +245,11 @@ inline int exchange_emigrants(Rank *c) {
     if (ru)
         k_unpack_guests<<<grid_for(ru), kThreads, 0, c->stream>>>(
             g, ru, c->mig_recv[0], first, 0, c->pos_alt, c->posf, c->vel_cur, c->m_cur, c->id_cur, c->cell_cur,
-            c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->d_ctr);
+            c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->arr_cnt, c->d_ctr);
     if (rd)
         k_unpack_guests<<<grid_for(rd), kThreads, 0, c->stream>>>(
             g, rd, c->mig_recv[1], first + ru, ru, c->pos_alt, c->posf, c->vel_cur, c->m_cur, c->id_cur,
-            c->cell_cur, c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->d_ctr);
+            c->cell_cur, c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->arr_cnt, c->d_ctr);
     timed_end(c);
     c->n_guest = ru + rd;
     return check_launch(c, "exchange_emigrants");

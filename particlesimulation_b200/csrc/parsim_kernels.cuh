@@ -32,6 +32,7 @@ enum : unsigned char {
 struct Geom {
     double side;   // side_length
     double cellw;  // side_length / grid_size, the divisor of serial/parsim.cpp:160-161,:268-269
+    double inv_cellw;  // 1 / cellw (fast path of cell_coord_fast only)
     int nc;        // grid_size (cells per side)
     int row0;      // first global grid row of this strip
     int rows;      // rows in this strip
@@ -54,6 +55,17 @@ struct Counters {  // one per context, device memory, copied to the host once pe
     int n_next;          // alive residents after this step's rebin
     int error;           // sticky device-side error code (capacity overflow, long jump, ...)
     int n_staged;        // upload cursor for multi-rank ingest
+    int pad;
+};
+
+// Arrival record: what the collision search needs to know about a mover that the list update
+// appended to a cell's list, written next to the linked bag so that a cell's first kArrSlots
+// arrivals cost one load instead of a pointer chase.
+constexpr int kArrSlots = 4;
+struct __align__(16) ArrRec {
+    double2 pos;             // post-move position
+    unsigned long long key;  // list key (see list_key)
+    int idx;                 // entry index
     int pad;
 };
 
@@ -347,23 +359,55 @@ __global__ void k_ghost_wrap(Geom g, double2 *com_xy, double *com_m) {
 // rounding sequence exactly (no FMA contraction).
 // Pre-move positions are read from pos_in by every thread of the cell, so post-move
 // positions go to pos_out.
-// 1/sqrt(a) for a normal positive double: MUFU.RSQ64H seed (about 23 good bits) and one
-// third-order correction -> ~1 ulp.  No special-case branch: the caller discards a == 0.
-__device__ __forceinline__ double rsqrt_pos(double a) {
-    double y;
-    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(a));
-    double e = fma(a, -(y * y), 1.0);
-    double p = fma(e, 0.375, 0.5);
-    return fma(p, y * e, y);
-}
+// One source (particle or neighbour centre of mass) acting on a target: a += m_k d / |d|^3.
+// |d|^-3 comes from the MUFU.RSQ64H seed y (rel. error < 2^-21) and ONE third-order correction
+// of the cube: with e = 1 - d2 y^2,  d2^(-3/2) = y^3 (1 + e (3/2 + 15/8 e)) + O(e^3) -- 13 FP64
+// instructions per pair where the reference's sqrt + 3 divisions cost ~60.  kTinyD2 keeps
+// coincident points (d == 0, including k == i) finite: they contribute exactly 0 like the
+// reference's `if (d == 0) return` (:134-137); it is far below the square of any position ulp.
+constexpr double kTinyD2 = 1e-60;
 
 __device__ __forceinline__ void accumulate(double dx, double dy, double mk, double &ax, double &ay) {
-    double d2 = fma(dx, dx, dy * dy);
-    double r = rsqrt_pos(d2);
-    double w = (mk * r) * (r * r);
-    w = d2 > 0.0 ? w : 0.0;  // coincident points (and k == i) contribute nothing, :134-137
+    const double d2 = fma(dx, dx, fma(dy, dy, kTinyD2));
+    double y;
+    asm("rsqrt.approx.ftz.f64 %0, %1;" : "=d"(y) : "d"(d2));
+    const double yy = y * y;
+    const double e = fma(-d2, yy, 1.0);
+    const double p = fma(e, 1.875, 1.5);
+    const double u = (mk * y) * yy;
+    const double w = fma(u * e, p, u);
     ax = fma(w, dx, ax);
     ay = fma(w, dy, ay);
+}
+
+// x = fmod(x + side, side) (:171-172) without the library loop: fmod is exact, and for
+// t = x + side in [side, 4 side) the subtractions below are exact too (Sterbenz), so the
+// result is bit-identical.  Anything else (a jump of more than a box length) takes fmod.
+__device__ __forceinline__ double wrap_coord(double x, double side) {
+    const double t = __dadd_rn(x, side);
+    if (t >= side) {
+        const double r1 = __dadd_rn(t, -side);
+        if (r1 < side) return r1;
+        const double r2 = __dadd_rn(r1, -side);  // r1 in [side, 3 side): exact again
+        if (r2 < side && t < 4.0 * side) return r2;
+        return fmod(t, side);
+    }
+    return t >= 0.0 ? t : fmod(t, side);
+}
+
+// cell_coord without the division: q = v * (1/cellw) differs from the correctly rounded
+// v / cellw by < 4 ulp, so trunc() agrees unless q sits within 1e-12 q of an integer; only
+// then the true division of the reference decides.
+__device__ __forceinline__ int cell_coord_fast(double v, const Geom &g) {
+    const double q = v * g.inv_cellw;
+    int c = __double2int_rz(q);
+    const double fr = q - (double)c;
+    const double tol = q * 1e-12;
+    if (fr < tol || fr > 1.0 - tol || !(q >= 0.0)) c = __double2int_rz(__ddiv_rn(v, g.cellw));
+    return min(max(c, 0), g.nc - 1);
+}
+__device__ __forceinline__ int global_cell_fast(double2 p, const Geom &g) {
+    return cell_coord_fast(p.y, g) * g.nc + cell_coord_fast(p.x, g);
 }
 
 __global__ void __launch_bounds__(kThreads)
@@ -418,13 +462,13 @@ k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
                                         __dmul_rn(__dmul_rn(__dmul_rn(0.5, ay), kDeltaT), kDeltaT)));
     v.x = __dadd_rn(v.x, __dmul_rn(ax, kDeltaT));
     v.y = __dadd_rn(v.y, __dmul_rn(ay, kDeltaT));
-    x = fmod(__dadd_rn(x, g.side), g.side);  // :171-172
-    y = fmod(__dadd_rn(y, g.side), g.side);
+    x = wrap_coord(x, g.side);  // :171-172
+    y = wrap_coord(y, g.side);
     double2 pn = make_double2(x, y);
     pos_out[i] = pn;
-    posf_out[i] = make_float2((float)x, (float)y);  // collision pre-filter, see k_collide_find
+    if (posf_out) posf_out[i] = make_float2((float)x, (float)y);  // pre-filter of k_collide_find
     vel[i] = v;
-    newcell[i] = global_cell(pn, g);          // :174-177
+    newcell[i] = global_cell_fast(pn, g);     // :174-177
 }
 
 // ---------------------------------------------------------------------------------------
@@ -450,6 +494,7 @@ k_classify(Geom g, int n, const int *__restrict__ cell, const int *__restrict__ 
            const int *__restrict__ newcell, const unsigned *__restrict__ id,
            const int *__restrict__ dead_start, const unsigned *__restrict__ dead_id,
            unsigned char *__restrict__ flags, int *arr_head, int *__restrict__ arr_next,
+           const double2 *__restrict__ pos_new, int *arr_cnt, ArrRec *__restrict__ arr_rec,
            unsigned long long *stat_movers, unsigned long long *stat_strays) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long mover = 0, stray = 0;
@@ -474,6 +519,17 @@ k_classify(Geom g, int n, const int *__restrict__ cell, const int *__restrict__ 
                 int dst = dstg - g.cell_base;
                 if (dst >= 0 && dst < g.ncells) {
                     arr_next[i] = atomicExch(&arr_head[dst], i);  // unordered bag; order comes from keys
+                    if (arr_cnt) {
+                        const int sl = atomicAdd(&arr_cnt[dst], 1);
+                        if (sl < kArrSlots) {
+                            ArrRec r;
+                            r.pos = pos_new[i];
+                            r.key = (1ull << 63) | ((unsigned long long)(unsigned)cg << 32) | id[i];
+                            r.idx = i;
+                            r.pad = 0;
+                            arr_rec[(size_t)dst * kArrSlots + sl] = r;
+                        }
+                    }
                 } else {
                     f |= F_EMIGRANT;
                 }

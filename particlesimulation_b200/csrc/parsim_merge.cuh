@@ -139,6 +139,7 @@ struct MoveArgs {
     const double *m_in;
     const unsigned *id_in;
     int *mv_head, *dm_head, *arr_head;   // bags; reset to -1 here for the next step
+    int *arr_cnt;                        // arrival-record counters (nullptr: unused); reset to 0 here
     int *count;                          // per-cell survivor counts; reset to 0 here
     const int *mv_next;
     const unsigned *dead_old;
@@ -231,6 +232,7 @@ __global__ void __launch_bounds__(kThreads) k_move(Geom g, MoveArgs a) {
         a.mv_head[c] = -1;
         a.dm_head[c] = -1;
         a.arr_head[c] = -1;
+        if (a.arr_cnt) a.arr_cnt[c] = 0;
         a.count[c] = 0;
     }
 }

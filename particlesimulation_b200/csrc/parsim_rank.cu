@@ -56,6 +56,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     Geom &g = c->g;
     g.side = side;
     g.cellw = side / (double)ncside;  // side_length / grid_size with grid_size a long, :160
+    g.inv_cellw = 1.0 / g.cellw;
     g.nc = (int)ncside;
     g.row0 = (int)((long long)rank * ncside / nranks);
     int row1 = (int)((long long)(rank + 1) * ncside / nranks);
@@ -71,6 +72,34 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     double ppc = (double)n_part / ((double)ncside * (double)ncside);
     c->com_lanes = ppc <= 6 ? 4 : ppc <= 12 ? 8 : ppc <= 24 ? 16 : 32;
 
+    {   // sub-grid of the collision search: pitch >= EPSILON (with a margin for the binning arithmetic)
+        const double hmin = kEpsilon * (1.0 + 1e-6);
+        const double fit = floor(g.cellw / hmin);
+        const int nb_geom = fit >= 1.0 ? (fit > 1024.0 ? 1024 : (int)fit) : 1;
+        c->grid_nb = std::min(nb_geom, 16);
+        c->big_nb = std::min(nb_geom, 32);
+        // bin-time entries per lane of the warp-per-cell kernel: covers ppc + 6 sigma (Poisson)
+        const double want = ppc + 6.0 * sqrt(ppc) + 8.0;
+        c->grid_it = want <= 64 ? 2 : want <= 128 ? 4 : want <= 192 ? 6 : want <= 256 ? 8 : 12;
+        c->grid_cap = 32 * c->grid_it + 32;
+        c->big_cap = 6400;
+        c->collide_grid = c->grid_nb >= 3 && ppc >= 16.0;
+        if (const char *e = getenv("PARSIM_COLLIDE")) {
+            if (!strcmp(e, "pairs")) c->collide_grid = false;
+            else if (!strcmp(e, "grid")) c->collide_grid = true;
+        }
+        if (c->collide_grid) {
+            const int nbins = c->grid_nb * c->grid_nb;
+#define PS_COLLIDE_ATTR(IT)                                                                              \
+    PS_CUDA(c, cudaFuncSetAttribute(k_collide_cells<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                                    (int)(kCollideWarps * warp_staging_bytes(nbins, 32 * IT + 32))))
+            PS_COLLIDE_ATTR(1); PS_COLLIDE_ATTR(2); PS_COLLIDE_ATTR(3); PS_COLLIDE_ATTR(4);
+            PS_COLLIDE_ATTR(6); PS_COLLIDE_ATTR(8); PS_COLLIDE_ATTR(12);
+#undef PS_COLLIDE_ATTR
+            PS_CUDA(c, cudaFuncSetAttribute(k_collide_big, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)staging_bytes(c->big_nb * c->big_nb, c->big_cap)));
+        }
+    }
     if (const char *e = getenv("PARSIM_CAPACITY_PCT")) {
         double pct = atof(e);
         if (pct >= 100) c->capacity_factor = pct / 100.0;
@@ -92,7 +121,11 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     const size_t N = (size_t)c->cap, C = (size_t)g.ncells;
     PS_ALLOC(c, c->pos_cur, N, false); PS_ALLOC(c, c->pos_alt, N, false);
     PS_ALLOC(c, c->vel_cur, N, false); PS_ALLOC(c, c->vel_alt, N, false);
-    PS_ALLOC(c, c->posf, N, false);
+    if (!c->collide_grid) PS_ALLOC(c, c->posf, N, false);
+    else {
+        PS_ALLOC(c, c->big_cells, C, false); PS_ALLOC(c, c->d_big_count, 1, true);
+        PS_ALLOC(c, c->arr_cnt, C, true); PS_ALLOC(c, c->arr_rec, C * kArrSlots, false);
+    }
     PS_ALLOC(c, c->m_cur, N, false);   PS_ALLOC(c, c->m_alt, N, false);
     PS_ALLOC(c, c->id_cur, N, false);  PS_ALLOC(c, c->id_alt, N, false);
     PS_ALLOC(c, c->cell_cur, N, false); PS_ALLOC(c, c->cell_alt, N, false);
@@ -141,7 +174,7 @@ void rank_destroy(Rank *c) {
                     c->dead_start_cur, c->dead_start_alt, c->dead_id_cur, c->dead_id_alt,
                     c->mv_head, c->dm_head, c->mv_next, c->fate, c->grave_pos, c->grave_vel, c->grave_id,
                     c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->posf, c->pos0, c->vel0,
-                    c->m0, c->id0, c->stage_ids, c->stage[0],
+                    c->m0, c->id0, c->big_cells, c->d_big_count, c->arr_cnt, c->arr_rec, c->stage_ids, c->stage[0],
                     c->stage[1], c->stage[2], c->stage[3], c->stage[4]};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
@@ -171,6 +204,7 @@ static int reset_state(Rank *c) {
     PS_CUDA(c, cudaMemsetAsync(c->dead_new_count, 0, sizeof(int) * C, c->stream));
     PS_CUDA(c, cudaMemsetAsync(c->dead_start_cur, 0, sizeof(int) * (C + 1), c->stream));
     PS_CUDA(c, cudaMemsetAsync(c->arr_head, 0xFF, sizeof(int) * C, c->stream));  // empty bags (-1)
+    if (c->arr_cnt) PS_CUDA(c, cudaMemsetAsync(c->arr_cnt, 0, sizeof(int) * C, c->stream));
     PS_CUDA(c, cudaMemsetAsync(c->mv_head, 0xFF, sizeof(int) * C, c->stream));
     PS_CUDA(c, cudaMemsetAsync(c->dm_head, 0xFF, sizeof(int) * C, c->stream));
     return 0;

@@ -11,13 +11,14 @@
 #include "parsim_kernels.cuh"
 #include "parsim_merge.cuh"
 #include "parsim_sort.cuh"
+#include "parsim_collide.cuh"
 #include "parsim_nccl.hpp"
 
 namespace parsim {
 
 enum KernelId {
     K_INGEST = 0, K_BIN_KEYS, K_SCAN, K_SORT_PASS, K_SORT_GATHER, K_COM, K_GHOST, K_FORCE,
-    K_CLASSIFY, K_COLLIDE, K_RESOLVE, K_TOMBSTONES, K_MIGRATE, K_INIT, K_MOVE, K_COUNT_
+    K_CLASSIFY, K_COLLIDE, K_RESOLVE, K_TOMBSTONES, K_MIGRATE, K_INIT, K_MOVE, K_COLLIDE_BIG, K_COUNT_
 };
 static_assert(K_COUNT_ <= PARSIM_NKERNELS, "grow PARSIM_NKERNELS");
 
@@ -51,6 +52,12 @@ struct Rank {
     double2 *pos_latest = nullptr;             // where the newest positions are (dumps)
     float2 *posf = nullptr;                    // FP32 copy of the post-move positions (collision pre-filter)
     float thrf = 0;                            // pre-filter threshold on the FP32 squared distance
+    // cell-centric collision search (parsim_collide.cuh); off: per-particle all-pairs k_collide_find
+    bool collide_grid = false;
+    int grid_nb = 1, grid_cap = 0, grid_it = 2, big_nb = 1, big_cap = 0;
+    int *big_cells = nullptr, *d_big_count = nullptr;
+    int *arr_cnt = nullptr;
+    ArrRec *arr_rec = nullptr;
     bool have_newcell = false, have_flags = false;
 
     int *count = nullptr, *tile_sums = nullptr;

@@ -113,7 +113,7 @@ static int merge_step(Rank *c, int n_src, int n_surv, bool with_dead) {
     a.ds_old = c->dead_start_cur; a.ds_new = with_dead ? c->dead_start_alt : nullptr;
     a.fate = c->fate;
     a.pos_in = c->pos_alt; a.vel_in = c->vel_cur; a.m_in = c->m_cur; a.id_in = c->id_cur;
-    a.mv_head = c->mv_head; a.dm_head = c->dm_head; a.arr_head = c->arr_head; a.count = c->count;
+    a.mv_head = c->mv_head; a.dm_head = c->dm_head; a.arr_head = c->arr_head; a.arr_cnt = c->arr_cnt; a.count = c->count;
     a.mv_next = c->mv_next;
     a.dead_old = c->dead_id_cur; a.dead_new = c->dead_id_alt;
     a.pos_out = c->pos_cur; a.vel_out = c->vel_alt; a.m_out = c->m_alt; a.id_out = c->id_alt;
@@ -191,22 +191,60 @@ static int stage_lists(Rank *c) {
               k_classify<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
                   g, c->n_alive, c->cell_cur, c->cs_cur, c->newcell, c->id_cur,
                   c->n_tomb > 0 ? c->dead_start_cur : nullptr, c->dead_id_cur, c->flags, c->arr_head,
-                  c->arr_next, c->opt_stats ? &c->d_ctr->movers : nullptr, &c->d_ctr->strays));
+                  c->arr_next, c->pos_alt, c->arr_cnt, c->arr_rec,
+                  c->opt_stats ? &c->d_ctr->movers : nullptr, &c->d_ctr->strays));
     c->n_guest = 0;
     if (c->nranks > 1 && exchange_emigrants(c)) return 1;
     c->have_flags = true;
     return 0;
 }
 
+template <int IT>
+static void launch_collide_cells(Rank *c, const CollideArgs &a) {
+    const size_t sh = kCollideWarps * warp_staging_bytes(a.nb * a.nb, 32 * IT + 32);
+    k_collide_cells<IT><<<grid_for(c->g.ncells, kCollideWarps), kCollideWarps * 32, sh, c->stream>>>(a);
+}
+
 // stage 3: collisions, compaction, and the (cell, id) order for the next step
 static int stage_collide(Rank *c) {
     const Geom &g = c->g;
     const int n_tot = c->n_alive + c->n_guest;
-    PS_LAUNCH(c, K_COLLIDE, 21.0 * n_tot + 8.0 * g.ncells, "k_collide_find",
-              k_collide_find<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
-                  g, n_tot, c->n_alive, c->thr2, c->thrf, c->pos_alt, c->posf, c->cell_cur, c->cs_cur, c->newcell,
-                  c->id_cur, c->flags, c->arr_head, c->arr_next, c->guest_src, c->partner,
-                  c->opt_stats ? &c->d_ctr->collision_pairs : nullptr));
+    if (c->collide_grid) {
+        CollideArgs a;
+        a.g = g; a.n_res = c->n_alive; a.thr2 = c->thr2; a.pos = c->pos_alt;
+        a.cell = c->cell_cur; a.cell_start = c->cs_cur; a.newcell = c->newcell; a.id = c->id_cur;
+        a.flags = c->flags; a.arr_head = c->arr_head; a.arr_next = c->arr_next; a.guest_src = c->guest_src;
+        a.arr_cnt = c->arr_cnt; a.arr_rec = c->arr_rec;
+        a.partner = c->partner;
+        a.collision_pairs = c->opt_stats ? &c->d_ctr->collision_pairs : nullptr;
+        a.worklist = c->big_cells; a.work_count = c->d_big_count;
+        PS_CUDA(c, cudaMemsetAsync(c->d_big_count, 0, sizeof(int), c->stream));
+        a.nb = c->grid_nb; a.inv_h = c->grid_nb / g.cellw; a.cap = c->grid_cap;
+        PS_LAUNCH(c, K_COLLIDE, 29.0 * n_tot + 8.0 * g.ncells, "k_collide_cells", {
+            // entries per lane from the CURRENT occupancy (+2.5 sigma); fuller cells go to k_collide_big
+            const double now = (double)n_tot / std::max(1, g.ncells);
+            const double want = now + 2.5 * sqrt(now) + 4.0;
+            const int it = want <= 32 ? 1 : want <= 64 ? 2 : want <= 96 ? 3 : want <= 128 ? 4 : want <= 192 ? 6 : want <= 256 ? 8 : 12;
+            switch (std::min(it, c->grid_it)) {
+            case 1: launch_collide_cells<1>(c, a); break;
+            case 2: launch_collide_cells<2>(c, a); break;
+            case 3: launch_collide_cells<3>(c, a); break;
+            case 4: launch_collide_cells<4>(c, a); break;
+            case 6: launch_collide_cells<6>(c, a); break;
+            case 8: launch_collide_cells<8>(c, a); break;
+            default: launch_collide_cells<12>(c, a); break;
+            }
+        });
+        a.nb = c->big_nb; a.inv_h = c->big_nb / g.cellw; a.cap = c->big_cap;
+        PS_LAUNCH(c, K_COLLIDE_BIG, 0.0, "k_collide_big",
+                  k_collide_big<<<148, kThreads, staging_bytes(a.nb * a.nb, a.cap), c->stream>>>(a));
+    } else {
+        PS_LAUNCH(c, K_COLLIDE, 21.0 * n_tot + 8.0 * g.ncells, "k_collide_find",
+                  k_collide_find<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
+                      g, n_tot, c->n_alive, c->thr2, c->thrf, c->pos_alt, c->posf, c->cell_cur, c->cs_cur, c->newcell,
+                      c->id_cur, c->flags, c->arr_head, c->arr_next, c->guest_src, c->partner,
+                      c->opt_stats ? &c->d_ctr->collision_pairs : nullptr));
+    }
     PS_LAUNCH(c, K_RESOLVE, 10.0 * n_tot, "k_resolve",
               k_resolve<<<std::min(grid_for(n_tot, kThreads * kResolveRows), 148 * 8), kThreads, 0, c->stream>>>(
                   g, n_tot, c->n_alive, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,

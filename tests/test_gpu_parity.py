@@ -135,6 +135,26 @@ def test_run_is_deterministic_and_matches_staged():
     assert a.result() == b.result() == c.result()
 
 
+@pytest.mark.parametrize("case", [(1, 10, 100, 100000, 5), (5, 1, 20, 20000, 4), (5, 1, 20, 200000, 3),
+                                  (5, 1, 20, 3000000, 2), (-7, 10, 50, 200000, 6), (9, 0.3, 4, 3000, 6),
+                                  (1, 5000, 20, 300000, 3), (3, 100, 1000, 800000, 5)],
+                         ids=lambda c: " ".join(map(str, c)))
+def test_collision_search_paths_agree(case, monkeypatch):
+    """The sub-grid collision search (warp per cell, block per big cell, all-pairs fallback for
+    lists beyond the staging area) must give exactly the result of the per-particle all-pairs sweep."""
+    seed, side, nc, n, steps = case
+    res = {}
+    for mode in ("pairs", "grid"):
+        monkeypatch.setenv("PARSIM_COLLIDE", mode)
+        g = ParticleSimulation(seed, side, nc, n)
+        g.simulate(steps)
+        res[mode] = (g.result(), g.dump())
+        g.close()
+    assert res["pairs"][0] == res["grid"][0]
+    for k in ("x", "y", "vx", "vy", "m", "alive"):
+        assert np.array_equal(res["pairs"][1][k], res["grid"][1][k]), k
+
+
 def test_upload_arrays_path_and_errors():
     arrs = init_particles(1, 2, 3, 10)
     g = ParticleSimulation(0, 2, 3, 10, arrays=arrs)
