@@ -4,6 +4,7 @@ namespace parsim {
 // Particle 0 of THIS strip (alive array first, then the graveyard) and this strip's collisions.
 int rank_result_local(Rank *c, double *x0, double *y0, int *found, long long *collisions) {
     PS_CUDA(c, cudaSetDevice(c->device));
+    if (rank_ensure_sorted(c)) return 1;
     PS_CUDA(c, cudaMemsetAsync(c->d_found, 0, sizeof(int), c->stream));
     if (c->n_alive > 0)
         k_find_id<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(c->n_alive, c->id_cur, c->pos_latest,
@@ -41,6 +42,7 @@ static int fetch(Rank *c, T *host_dst, const T *dev, size_t n, const unsigned ch
 int rank_dump(Rank *c, double *x, double *y, double *vx, double *vy, double *m, int *alive, int *cell,
               int *list_cell, unsigned long long *list_rank, unsigned char *owned) {
     PS_CUDA(c, cudaSetDevice(c->device));
+    if (rank_ensure_sorted(c)) return 1;
     const size_t n = (size_t)c->n_part;
     double *dx, *dy, *dvx, *dvy, *dm;
     int *dalive, *dcell, *dlist;

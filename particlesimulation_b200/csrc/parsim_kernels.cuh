@@ -99,14 +99,33 @@ __device__ __forceinline__ void block_add_u64(unsigned long long v, unsigned lon
 }
 
 // ---------------------------------------------------------------------------------------
-// Upload: interleave host SoA (x,y,vx,vy,m) into the device layout and keep the particles of
-// this strip.  Slot order is irrelevant: the first rebin orders every cell by id.
+// The uploaded (unordered) state: one 64-byte record per particle slot, so that the step-0 sort
+// moves a particle with ONE random 64-byte access instead of four 16-byte ones (DRAM fetches
+// 64 bytes at a time).  The sort never modifies the records, so parsim_reset costs nothing.
+struct __align__(16) InitRec {
+    double2 pos;
+    double2 vel;
+    double m;
+    unsigned id;
+    unsigned pad0;
+    double2 pad1;
+};
+static_assert(sizeof(InitRec) == 64, "InitRec must be one 64-byte line");
+
+__device__ __forceinline__ void store_rec(InitRec *rec, int slot, double2 p, double2 v, double m, unsigned id) {
+    double2 *q = reinterpret_cast<double2 *>(rec + slot);
+    q[0] = p;
+    q[1] = v;
+    q[2] = make_double2(m, __hiloint2double(0, (int)id));  // id in the low word of the 4th double
+}
+
+// Upload: interleave host SoA (x,y,vx,vy,m) into records and keep the particles of this strip.
+// Single strip: slot = id (id order).  Several strips: claimed slots (any order).
 __global__ void k_ingest(Geom g, long long id_base, const unsigned *__restrict__ ids, int count,
                          const double *__restrict__ x,
                          const double *__restrict__ y, const double *__restrict__ vx,
                          const double *__restrict__ vy, const double *__restrict__ m,
-                         int single_rank, int capacity, double2 *pos, double2 *vel, double *mass,
-                         unsigned *id, Counters *ctr) {
+                         int single_rank, int capacity, InitRec *rec, Counters *ctr) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= count) return;
     double2 p = make_double2(x[t], y[t]);
@@ -120,10 +139,7 @@ __global__ void k_ingest(Geom g, long long id_base, const unsigned *__restrict__
         slot = atomicAdd(&ctr->n_staged, 1);
         if (slot >= capacity) { ctr->error = DE_CAPACITY; return; }
     }
-    pos[slot] = p;
-    vel[slot] = make_double2(vx[t], vy[t]);
-    mass[slot] = m[t];
-    id[slot] = pid;
+    store_rec(rec, slot, p, make_double2(vx[t], vy[t]), m[t], pid);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -156,8 +172,7 @@ __device__ __forceinline__ double xs_draw(unsigned &s) {
 }
 
 __global__ void k_init_particles(Geom g, const XsJumpTable *__restrict__ jt, unsigned s0, long long n_part,
-                                 int single_rank, int capacity, double2 *pos, double2 *vel, double *mass,
-                                 unsigned *id, Counters *ctr) {
+                                 int single_rank, int capacity, InitRec *rec, Counters *ctr) {
     const long long T = (long long)gridDim.x * blockDim.x;
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_part) return;
@@ -185,10 +200,7 @@ __global__ void k_init_particles(Geom g, const XsJumpTable *__restrict__ jt, uns
             slot = atomicAdd(&ctr->n_staged, 1);
             if (slot >= capacity) { ctr->error = DE_CAPACITY; continue; }
         }
-        pos[slot] = make_double2(x, y);
-        vel[slot] = make_double2(vx, vy);
-        mass[slot] = m;
-        id[slot] = (unsigned)i;
+        store_rec(rec, slot, make_double2(x, y), make_double2(vx, vy), m, (unsigned)i);
     }
 }
 
@@ -410,24 +422,57 @@ __device__ __forceinline__ int global_cell_fast(double2 p, const Geom &g) {
     return cell_coord_fast(p.y, g) * g.nc + cell_coord_fast(p.x, g);
 }
 
-__global__ void __launch_bounds__(kThreads)
+// A block of TB consecutive particles touches the segments of the cells from its first to its
+// last particle's cell: one contiguous range of the (cell, id)-ordered arrays.  The range is
+// staged in shared memory with coalesced loads (24 B per source), and the pair loop reads it
+// from there: no global load -- and no load latency -- inside the FP64-bound loop.  Ranges
+// longer than kForceTile sources (very full cells) are read through L1 instead.
+constexpr int kForceTile = 1280;
+
+template <int TB, int UNROLL>
+__global__ void __launch_bounds__(TB)
 k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
                   const double *__restrict__ m, const int *__restrict__ cell,
                   const int *__restrict__ cell_start, const double2 *__restrict__ com_xy,
                   const double *__restrict__ com_m, double2 *__restrict__ pos_out,
                   float2 *__restrict__ posf_out, double2 *__restrict__ vel, int *__restrict__ newcell,
                   double2 *__restrict__ dbg_acc) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    __shared__ double2 s_pos[kForceTile];
+    __shared__ double s_m[kForceTile];
+    const int b0 = blockIdx.x * TB;
+    const int i = b0 + threadIdx.x;
+    const int last = min(b0 + TB, n) - 1;
+    const int r0 = cell_start[cell[b0]], r1 = cell_start[cell[last] + 1];
+    const bool staged = r1 - r0 <= kForceTile;  // block-uniform
+    int c = 0, s = 0, e = 0;
+    double2 p = make_double2(0.0, 0.0);
+    if (i < n) {
+        c = cell[i];
+        p = pos_in[i];
+        s = cell_start[c];
+        e = cell_start[c + 1];
+    }
+    if (staged) {
+        for (int k = r0 + threadIdx.x; k < r1; k += TB) {
+            s_pos[k - r0] = pos_in[k];
+            s_m[k - r0] = m[k];
+        }
+        __syncthreads();
+    }
     if (i >= n) return;
-    const int c = cell[i];
-    const double2 p = pos_in[i];
-    const int s = cell_start[c], e = cell_start[c + 1];
     double ax = 0.0, ay = 0.0;
+    if (staged) {
+#pragma unroll UNROLL
+        for (int k = s - r0; k < e - r0; k++) {
+            const double2 q = s_pos[k];
+            accumulate(q.x - p.x, q.y - p.y, s_m[k], ax, ay);
+        }
+    } else {
 #pragma unroll 4
-    for (int k = s; k < e; k++) {
-        double2 q = __ldg(&pos_in[k]);
-        double mk = __ldg(&m[k]);
-        accumulate(q.x - p.x, q.y - p.y, mk, ax, ay);
+        for (int k = s; k < e; k++) {
+            const double2 q = __ldg(&pos_in[k]);
+            accumulate(q.x - p.x, q.y - p.y, __ldg(&m[k]), ax, ay);
+        }
     }
     const int lrow = c / g.nc;
     const int gx = c - lrow * g.nc;

@@ -100,6 +100,8 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
                                             (int)staging_bytes(c->big_nb * c->big_nb, c->big_cap)));
         }
     }
+    if (const char *e = getenv("PARSIM_FORCE_TB")) c->force_tb = atoi(e) == 128 ? 128 : 256;
+    if (const char *e = getenv("PARSIM_FORCE_UNROLL")) c->force_unroll = atoi(e);
     if (const char *e = getenv("PARSIM_CAPACITY_PCT")) {
         double pct = atof(e);
         if (pct >= 100) c->capacity_factor = pct / 100.0;
@@ -119,6 +121,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     c->cap = (int)cap;
 
     const size_t N = (size_t)c->cap, C = (size_t)g.ncells;
+    PS_ALLOC(c, c->rec0, N, false);
     PS_ALLOC(c, c->pos_cur, N, false); PS_ALLOC(c, c->pos_alt, N, false);
     PS_ALLOC(c, c->vel_cur, N, false); PS_ALLOC(c, c->vel_alt, N, false);
     if (!c->collide_grid) PS_ALLOC(c, c->posf, N, false);
@@ -173,8 +176,8 @@ void rank_destroy(Rank *c) {
                     c->flags, c->com_xy, c->com_m, c->dbg_acc, c->dead_count, c->dead_new_count,
                     c->dead_start_cur, c->dead_start_alt, c->dead_id_cur, c->dead_id_alt,
                     c->mv_head, c->dm_head, c->mv_next, c->fate, c->grave_pos, c->grave_vel, c->grave_id,
-                    c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->posf, c->pos0, c->vel0,
-                    c->m0, c->id0, c->big_cells, c->d_big_count, c->arr_cnt, c->arr_rec, c->stage_ids, c->stage[0],
+                    c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->posf, c->rec0,
+                    c->big_cells, c->d_big_count, c->arr_cnt, c->arr_rec, c->stage_ids, c->stage[0],
                     c->stage[1], c->stage[2], c->stage[3], c->stage[4]};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
@@ -186,7 +189,6 @@ void rank_destroy(Rank *c) {
 }
 
 // ---- upload -------------------------------------------------------------------------------
-static int keep_initial(Rank *c);
 
 static int reset_state(Rank *c) {
     c->n_uploaded = 0;
@@ -241,8 +243,7 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
         PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest",
                   k_ingest<<<grid_for(cnt), kThreads, 0, c->stream>>>(
                       c->g, id_base + off, ids ? c->stage_ids : nullptr, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
-                      c->stage[4], c->nranks == 1, c->cap - 2 * c->mig_cap, c->pos_cur, c->vel_cur,
-                      c->m_cur, c->id_cur, c->d_ctr));
+                      c->stage[4], c->nranks == 1, c->cap - 2 * c->mig_cap, c->rec0, c->d_ctr));
         // the staging buffers are reused by the next piece
         PS_CUDA(c, cudaStreamSynchronize(c->stream));
     }
@@ -263,38 +264,19 @@ int rank_upload_end(Rank *c) {
     else if (c->n_uploaded != c->n_part) return c->fail("upload did not cover all n_part particles");
     else c->n_alive = (int)c->n_part;
     c->pos_latest = c->pos_cur;
-    return keep_initial(c);
-}
-
-// option "keep_initial": a device-resident copy of the uploaded state, so that parsim_reset can
-// restart the same problem without touching the host (bench: inputs already in HBM).
-static int keep_initial(Rank *c) {
-    if (!c->opt_keep_initial) return 0;
-    const size_t N = (size_t)c->cap;
-    if (!c->pos0) {
-        PS_ALLOC(c, c->pos0, N, false); PS_ALLOC(c, c->vel0, N, false);
-        PS_ALLOC(c, c->m0, N, false); PS_ALLOC(c, c->id0, N, false);
-    }
-    const size_t n = (size_t)c->n_alive;
-    PS_CUDA(c, cudaMemcpyAsync(c->pos0, c->pos_cur, sizeof(double2) * n, cudaMemcpyDeviceToDevice, c->stream));
-    PS_CUDA(c, cudaMemcpyAsync(c->vel0, c->vel_cur, sizeof(double2) * n, cudaMemcpyDeviceToDevice, c->stream));
-    PS_CUDA(c, cudaMemcpyAsync(c->m0, c->m_cur, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
-    PS_CUDA(c, cudaMemcpyAsync(c->id0, c->id_cur, sizeof(unsigned) * n, cudaMemcpyDeviceToDevice, c->stream));
-    PS_CUDA(c, cudaStreamSynchronize(c->stream));
     c->n0 = c->n_alive;
+    c->slots_id_ordered = c->nranks == 1;
     return 0;
 }
 
+// Restart from the uploaded state: the records in rec0 are untouched by the step loop.
 int rank_reset(Rank *c) {
     PS_CUDA(c, cudaSetDevice(c->device));
-    if (!c->pos0 || c->n0 <= 0) return c->fail("parsim_reset: set option keep_initial=1 before uploading");
+    if (c->n0 <= 0 || c->uploading) return c->fail("parsim_reset: nothing uploaded yet");
+    const int n0 = c->n0;
     if (reset_state(c)) return 1;
-    const size_t n = (size_t)c->n0;
-    PS_CUDA(c, cudaMemcpyAsync(c->pos_cur, c->pos0, sizeof(double2) * n, cudaMemcpyDeviceToDevice, c->stream));
-    PS_CUDA(c, cudaMemcpyAsync(c->vel_cur, c->vel0, sizeof(double2) * n, cudaMemcpyDeviceToDevice, c->stream));
-    PS_CUDA(c, cudaMemcpyAsync(c->m_cur, c->m0, sizeof(double) * n, cudaMemcpyDeviceToDevice, c->stream));
-    PS_CUDA(c, cudaMemcpyAsync(c->id_cur, c->id0, sizeof(unsigned) * n, cudaMemcpyDeviceToDevice, c->stream));
-    c->n_alive = c->n0;
+    c->n_alive = c->n0 = n0;
+    c->n_uploaded = c->n_part;
     c->pos_latest = c->pos_cur;
     return 0;
 }
@@ -307,6 +289,20 @@ int rank_download(Rank *c, long long capacity, unsigned *ids, double *x, double 
     const size_t n = (size_t)c->n_alive;
     *count_out = (long long)n;
     if ((long long)n > capacity) return c->fail("parsim_download: host arrays too small");
+    if (!c->sorted) {  // still the uploaded records, slot order
+        const size_t piece = 1 << 22;
+        std::vector<InitRec> tmp(std::min(n, piece));
+        for (size_t off = 0; off < n; off += piece) {
+            const size_t cnt = std::min(piece, n - off);
+            PS_CUDA(c, cudaMemcpy(tmp.data(), c->rec0 + off, sizeof(InitRec) * cnt, cudaMemcpyDeviceToHost));
+            for (size_t i = 0; i < cnt; i++) {
+                const InitRec &r = tmp[i];
+                x[off + i] = r.pos.x; y[off + i] = r.pos.y; vx[off + i] = r.vel.x; vy[off + i] = r.vel.y;
+                m[off + i] = r.m; ids[off + i] = r.id;
+            }
+        }
+        return 0;
+    }
     std::vector<double2> tmp(n);
     PS_CUDA(c, cudaMemcpy(tmp.data(), c->pos_latest, sizeof(double2) * n, cudaMemcpyDeviceToHost));
     for (size_t i = 0; i < n; i++) { x[i] = tmp[i].x; y[i] = tmp[i].y; }
@@ -353,8 +349,7 @@ int rank_init_device(Rank *c, long seed) {
     const unsigned s0 = (unsigned)abs(iseed) + 987654321u;  // :24
     PS_LAUNCH(c, K_INIT, 44.0 * c->n_part, "k_init_particles",
               k_init_particles<<<blocks, kThreads, 0, c->stream>>>(
-                  c->g, d_jt, s0, c->n_part, c->nranks == 1, c->cap - 2 * c->mig_cap, c->pos_cur,
-                  c->vel_cur, c->m_cur, c->id_cur, c->d_ctr));
+                  c->g, d_jt, s0, c->n_part, c->nranks == 1, c->cap - 2 * c->mig_cap, c->rec0, c->d_ctr));
     c->uploading = true;
     c->n_uploaded = c->n_part;
     int rc = rank_upload_end(c);

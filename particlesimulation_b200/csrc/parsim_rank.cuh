@@ -36,6 +36,8 @@ struct Rank {
     Geom g{};
     double thr2 = 0;    // collision threshold on the squared distance (see k_collide_find)
     int com_lanes = 32; // lanes per cell in k_com, from the GLOBAL particles-per-cell
+    int force_unroll = 4;
+    int force_tb = 256; // block size of k_force_integrate (PARSIM_FORCE_TB: 128 | 256)
 
     // particle storage: alive residents [0, n_alive), guests after them until the rebin
     int cap = 0;
@@ -91,12 +93,12 @@ struct Rank {
     unsigned *stage_ids = nullptr;
     int stage_cap = 0;
     long long n_uploaded = 0;
-    // option keep_initial: device copy of the uploaded state for parsim_reset
-    bool opt_keep_initial = false;
-    double2 *pos0 = nullptr, *vel0 = nullptr;
-    double *m0 = nullptr;
-    unsigned *id0 = nullptr;
-    int n0 = 0;
+    // the uploaded state (one 64-byte record per slot, parsim_kernels.cuh); the step-0 sort reads
+    // it and never modifies it, so parsim_reset only rewinds the bookkeeping
+    InitRec *rec0 = nullptr;
+    int n0 = 0;                 // records in rec0
+    bool slots_id_ordered = true;  // slot order == id order (single strip); else ids are sorted too
+    bool opt_keep_initial = false; // accepted for compatibility: reset is always possible now
     bool uploading = false;
 
     // multi-strip exchange (parsim_exchange.cuh)
@@ -199,6 +201,7 @@ int rank_fp64_peak(Rank *c, double *tflops);
 int rank_upload_end(Rank *c);
 int rank_init_device(Rank *c, long seed);
 int rank_stage(Rank *c, int stage);
+int rank_ensure_sorted(Rank *c);
 int rank_run(Rank *c, long n_steps);
 int rank_result_local(Rank *c, double *x0, double *y0, int *found, long long *collisions);
 int rank_dump(Rank *c, double *x, double *y, double *vx, double *vy, double *m, int *alive, int *cell,

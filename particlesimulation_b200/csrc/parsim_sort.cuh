@@ -136,10 +136,10 @@ k_sort_scatter(int n, const unsigned *__restrict__ keys_in, const int *__restric
 }
 
 // keys for an id pass: the id of the source of entry i (src_in == nullptr: source = i)
-__global__ void k_sort_id_keys(int n, const int *__restrict__ src_in, const unsigned *__restrict__ id,
+__global__ void k_sort_id_keys(int n, const int *__restrict__ src_in, const InitRec *__restrict__ rec,
                                unsigned *__restrict__ keys) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) keys[i] = id[src_in ? src_in[i] : i];
+    if (i < n) keys[i] = rec[src_in ? src_in[i] : i].id;
 }
 // keys for the first cell pass after id passes: the cell of the source of entry i
 __global__ void k_sort_cell_keys(int n, const int *__restrict__ src_in, const unsigned *__restrict__ cellkey,
@@ -148,33 +148,28 @@ __global__ void k_sort_cell_keys(int n, const int *__restrict__ src_in, const un
     if (i < n) keys[i] = cellkey[src_in[i]];
 }
 
-// are the ids ascending in slot order?  (*flag is set to 1 when they are not)
-__global__ void k_ids_ascending(int n, const unsigned *__restrict__ id, int *flag) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i + 1 < n && id[i] >= id[i + 1]) *flag = 1;
-}
-
 // cell key of every slot (the reference's binning arithmetic, :268-272)
-__global__ void k_sort_cell_of(Geom g, int n, const double2 *__restrict__ pos, unsigned *__restrict__ key) {
+__global__ void k_sort_cell_of(Geom g, int n, const InitRec *__restrict__ rec, unsigned *__restrict__ key) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) key[i] = (unsigned)(global_cell(pos[i], g) - g.cell_base);
+    if (i < n) key[i] = (unsigned)(global_cell(rec[i].pos, g) - g.cell_base);
 }
 
-// final permutation: one move of the 44-byte state; cell_start from the sorted keys
+// final permutation: one 64-byte read per particle, SoA written in (cell, id) order;
+// cell_start from the sorted keys
 __global__ void __launch_bounds__(kThreads)
 k_sort_gather(int n, int ncells, const unsigned *__restrict__ keys, const int *__restrict__ src,
-              const double2 *__restrict__ pos_in, const double2 *__restrict__ vel_in,
-              const double *__restrict__ m_in, const unsigned *__restrict__ id_in,
-              double2 *__restrict__ pos_out, double2 *__restrict__ vel_out, double *__restrict__ m_out,
-              unsigned *__restrict__ id_out, int *__restrict__ cell_out, int *__restrict__ cell_start) {
+              const InitRec *__restrict__ rec, double2 *__restrict__ pos_out, double2 *__restrict__ vel_out,
+              double *__restrict__ m_out, unsigned *__restrict__ id_out, int *__restrict__ cell_out,
+              int *__restrict__ cell_start) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
-    const int s = src[p];
     const int c = (int)keys[p];
-    pos_out[p] = pos_in[s];
-    vel_out[p] = vel_in[s];
-    m_out[p] = m_in[s];
-    id_out[p] = id_in[s];
+    const double2 *q = reinterpret_cast<const double2 *>(rec + src[p]);
+    const double2 a = __ldg(q), v = __ldg(q + 1), mi = __ldg(q + 2);
+    pos_out[p] = a;
+    vel_out[p] = v;
+    m_out[p] = mi.x;
+    id_out[p] = (unsigned)__double2loint(mi.y);
     cell_out[p] = c;
     const int prev = p > 0 ? (int)keys[p - 1] : -1;
     for (int k = prev + 1; k <= c; k++) cell_start[k] = p;

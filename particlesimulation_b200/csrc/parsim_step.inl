@@ -55,22 +55,17 @@ static int sort_initial(Rank *c) {
     }
     unsigned *keyA = (unsigned *)c->newcell, *keyB = (unsigned *)c->partner;
     int *srcA = c->arr_next, *srcB = c->mv_next;
-    PS_CUDA(c, cudaMemsetAsync(c->d_found, 0, sizeof(int), c->stream));
-    k_ids_ascending<<<grid_for(n), kThreads, 0, c->stream>>>(n, c->id_cur, c->d_found);
-    int unordered = 0;
-    PS_CUDA(c, cudaMemcpyAsync(&unordered, c->d_found, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    PS_CUDA(c, cudaStreamSynchronize(c->stream));
     const int cell_bits = bits_for((unsigned long long)std::max(g.ncells - 1, 1));
-    if (!unordered) {
-        PS_LAUNCH(c, K_BIN_KEYS, 20.0 * n, "k_sort_cell_of",
-                  k_sort_cell_of<<<grid_for(n), kThreads, 0, c->stream>>>(g, n, c->pos_cur, keyA));
+    if (c->slots_id_ordered) {
+        PS_LAUNCH(c, K_BIN_KEYS, 68.0 * n, "k_sort_cell_of",
+                  k_sort_cell_of<<<grid_for(n), kThreads, 0, c->stream>>>(g, n, c->rec0, keyA));
         if (sort_passes(c, n, cell_bits, keyA, keyB, srcA, srcB, true)) return 1;
     } else {
         // slots are not in id order: sort by id first (LSD), then by cell
-        PS_LAUNCH(c, K_BIN_KEYS, 20.0 * n, "k_sort_cell_of",
-                  k_sort_cell_of<<<grid_for(n), kThreads, 0, c->stream>>>(g, n, c->pos_cur, c->tmp_id));
-        PS_LAUNCH(c, K_SORT_PASS, 8.0 * n, "k_sort_id_keys",
-                  k_sort_id_keys<<<grid_for(n), kThreads, 0, c->stream>>>(n, nullptr, c->id_cur, keyA));
+        PS_LAUNCH(c, K_BIN_KEYS, 68.0 * n, "k_sort_cell_of",
+                  k_sort_cell_of<<<grid_for(n), kThreads, 0, c->stream>>>(g, n, c->rec0, c->tmp_id));
+        PS_LAUNCH(c, K_SORT_PASS, 68.0 * n, "k_sort_id_keys",
+                  k_sort_id_keys<<<grid_for(n), kThreads, 0, c->stream>>>(n, nullptr, c->rec0, keyA));
         if (sort_passes(c, n, bits_for((unsigned long long)std::max<long long>(c->n_part - 1, 1)), keyA, keyB,
                         srcA, srcB, true))
             return 1;
@@ -78,10 +73,10 @@ static int sort_initial(Rank *c) {
                   k_sort_cell_keys<<<grid_for(n), kThreads, 0, c->stream>>>(n, srcA, c->tmp_id, keyA));
         if (sort_passes(c, n, cell_bits, keyA, keyB, srcA, srcB, false)) return 1;
     }
-    PS_LAUNCH(c, K_SORT_GATHER, 100.0 * n + 4.0 * g.ncells, "k_sort_gather",
+    PS_LAUNCH(c, K_SORT_GATHER, 120.0 * n + 4.0 * g.ncells, "k_sort_gather",
               k_sort_gather<<<grid_for(n), kThreads, 0, c->stream>>>(
-                  n, g.ncells, keyA, srcA, c->pos_cur, c->vel_cur, c->m_cur, c->id_cur, c->pos_alt, c->vel_alt,
-                  c->m_alt, c->id_alt, c->cell_alt, c->cs_alt));
+                  n, g.ncells, keyA, srcA, c->rec0, c->pos_alt, c->vel_alt, c->m_alt, c->id_alt, c->cell_alt,
+                  c->cs_alt));
     std::swap(c->pos_cur, c->pos_alt);
     std::swap(c->vel_cur, c->vel_alt);
     std::swap(c->m_cur, c->m_alt);
@@ -175,10 +170,22 @@ static int stage_bin_com(Rank *c) {
 
 // stage 1: forces + integration
 static int stage_force(Rank *c) {
-    PS_LAUNCH(c, K_FORCE, 80.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate",
-              k_force_integrate<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
-                  c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,
-                  c->pos_alt, c->posf, c->vel_cur, c->newcell, c->dbg_acc));
+#define PS_FORCE(TB, UN)                                                                            \
+    k_force_integrate<TB, UN><<<grid_for(c->n_alive, TB), TB, 0, c->stream>>>(                      \
+        c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,        \
+        c->pos_alt, c->posf, c->vel_cur, c->newcell, c->dbg_acc)
+    PS_LAUNCH(c, K_FORCE, 80.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate", {
+        const int v = c->force_tb * 100 + c->force_unroll;
+        switch (v) {
+        case 12802: PS_FORCE(128, 2); break;
+        case 12804: PS_FORCE(128, 4); break;
+        case 12808: PS_FORCE(128, 8); break;
+        case 25602: PS_FORCE(256, 2); break;
+        case 25608: PS_FORCE(256, 8); break;
+        default: PS_FORCE(256, 4); break;
+        }
+    });
+#undef PS_FORCE
     c->pos_latest = c->pos_alt;
     c->have_newcell = true;
     return 0;
@@ -278,6 +285,17 @@ static int stage_collide(Rank *c) {
     c->have_newcell = c->have_flags = false;
     c->steps_done++;
     c->stats.steps++;
+    return 0;
+}
+
+// dumps / downloads / results asked for before the first step: bring the uploaded records into
+// the ordered layout now (stage 0 then skips its sort)
+int rank_ensure_sorted(Rank *c) {
+    PS_CUDA(c, cudaSetDevice(c->device));
+    if (c->sorted || c->uploading) return 0;
+    if (sort_initial(c)) return 1;
+    c->sorted = true;
+    c->pos_latest = c->pos_cur;
     return 0;
 }
 
