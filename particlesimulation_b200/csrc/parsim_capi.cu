@@ -247,7 +247,7 @@ int parsim_stats(parsim_ctx *ctx, parsim_stats_t *out) {
         out->alive_particle_steps += s.alive_particle_steps;
         out->force_pairs += (long long)c->h_ctr->force_pairs;
         out->collision_pairs += (long long)c->h_ctr->collision_pairs;
-        out->movers += (long long)c->h_ctr->movers;
+        out->movers += s.movers;
         out->strays += (long long)c->h_ctr->strays;
         out->deaths += s.deaths;
         out->migrants += s.migrants;

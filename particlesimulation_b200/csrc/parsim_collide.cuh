@@ -232,29 +232,30 @@ __device__ long long collide_cell_allpairs(const CollideArgs &a, int L, int t) {
 
 constexpr int kCollideWarps = 8;  // cells per block in k_collide_cells
 
-// Warp-per-cell staging area: start[nbins + 1], arr_idx[32], spos[cap], sord[cap], best[cap]
-__host__ __device__ inline size_t warp_staging_bytes(int nbins, int cap) {
-    size_t b = (sizeof(int) * (size_t)(nbins + 1 + 32) + 15) & ~(size_t)15;
-    return b + (size_t)cap * (16 + 4 + 4);
+// Warp-per-cell staging area: start[256 + 8] (always 16 x 16 bins worth), arr_idx[32], spos[cap],
+// sord[cap], best[cap]
+constexpr int kWarpBins = 256;
+__host__ __device__ inline size_t warp_staging_bytes(int cap) {
+    return sizeof(int) * (size_t)(kWarpBins + 8 + 32) + (size_t)cap * (16 + 4 + 4);
 }
 
-// exclusive scan of cnt[0..nbins) in place by one warp, bank-conflict free (lane-strided rounds);
-// cnt[nbins] = total
-__device__ __forceinline__ void warp_scan_bins(int *cnt, int nbins, int lane) {
-    int carry = 0;
-    for (int base = 0; base < nbins; base += 32) {
-        const int b = base + lane;
-        const int v = b < nbins ? cnt[b] : 0;
-        int inc = v;
+// exclusive scan of cnt[0..256) in place by one warp; cnt[256] = total.  Lane l owns the eight
+// consecutive bins 8l..8l+7 (two 16-byte accesses each way).
+__device__ __forceinline__ void warp_scan_bins(int *cnt, int lane) {
+    int4 *v = reinterpret_cast<int4 *>(cnt) + 2 * lane;
+    int4 a = v[0], b = v[1];
+    const int s0 = a.x, s1 = s0 + a.y, s2 = s1 + a.z, s3 = s2 + a.w;
+    const int s4 = s3 + b.x, s5 = s4 + b.y, s6 = s5 + b.z, s7 = s6 + b.w;
+    int inc = s7;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            int u = __shfl_up_sync(0xffffffffu, inc, o);
-            if (lane >= o) inc += u;
-        }
-        if (b < nbins) cnt[b] = carry + inc - v;
-        carry += __shfl_sync(0xffffffffu, inc, 31);
+    for (int o = 1; o < 32; o <<= 1) {
+        int u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += u;
     }
-    if (lane == 0) cnt[nbins] = carry;
+    const int base = inc - s7;
+    v[0] = make_int4(base, base + s0, base + s1, base + s2);
+    v[1] = make_int4(base + s3, base + s4, base + s5, base + s6);
+    if (lane == 31) cnt[kWarpBins] = inc;
     __syncwarp();
 }
 
@@ -273,11 +274,10 @@ k_collide_cells(CollideArgs a) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int L = blockIdx.x * kCollideWarps + warp;
     constexpr int cap = 32 * IT + 32;
-    const int nbins = a.nb * a.nb;
-    unsigned char *raw = smem_raw + (size_t)warp * warp_staging_bytes(nbins, cap);
+    unsigned char *raw = smem_raw + (size_t)warp * warp_staging_bytes(cap);
     int *start = (int *)raw;
-    int *arr_idx = start + nbins + 1;
-    double2 *spos = (double2 *)(raw + ((sizeof(int) * (size_t)(nbins + 1 + 32) + 15) & ~(size_t)15));
+    int *arr_idx = start + kWarpBins + 8;
+    double2 *spos = (double2 *)(raw + sizeof(int) * (size_t)(kWarpBins + 8 + 32));
     unsigned *sord = (unsigned *)(spos + cap);
     unsigned *best = sord + cap;
     long long tested = 0;
@@ -316,7 +316,8 @@ k_collide_cells(CollideArgs a) {
                 n_arr = -1;
             }
             if (n_arr >= 0) {
-            for (int b = lane; b <= nbins; b += 32) start[b] = 0;
+            reinterpret_cast<int4 *>(start)[2 * lane] = make_int4(0, 0, 0, 0);
+            reinterpret_cast<int4 *>(start)[2 * lane + 1] = make_int4(0, 0, 0, 0);
             for (int o = lane; o < cap; o += 32) best[o] = 0xffffffffu;
             // order of the arrivals among themselves
             unsigned aord = 0;
@@ -342,7 +343,7 @@ k_collide_cells(CollideArgs a) {
                 br[IT] = (b << 16) | atomicAdd(&start[b], 1);
             }
             __syncwarp();
-            warp_scan_bins(start, nbins, lane);
+            warp_scan_bins(start, lane);
 #pragma unroll
             for (int j = 0; j <= IT; j++) {
                 if (br[j] >= 0) {

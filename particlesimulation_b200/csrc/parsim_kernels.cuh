@@ -55,7 +55,7 @@ struct Counters {  // one per context, device memory, copied to the host once pe
     int n_next;          // alive residents after this step's rebin
     int error;           // sticky device-side error code (capacity overflow, long jump, ...)
     int n_staged;        // upload cursor for multi-rank ingest
-    int pad;
+    int n_movers;        // particles that changed cell in this step (length of the mover list)
 };
 
 // Arrival record: what the collision search needs to know about a mover that the list update
@@ -313,36 +313,65 @@ __global__ void k_scan_apply(const int *__restrict__ in, const int *__restrict__
 // strided subsequence, then a fixed xor-shuffle tree: the order of additions depends only on
 // the cell's (id-sorted) contents, never on scheduling or on the number of GPUs.
 // com_xy / com_m carry one ghost row above and below the strip: index = (local_row+1)*nc + gx.
+constexpr int kComCells = 2;  // consecutive cells per lane group
+constexpr int kComAhead = 4;  // rounds of every cell whose loads are issued before any is used
+
 template <int LANES>
 __global__ void k_com(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
                       const int *__restrict__ cell_start, double2 *__restrict__ com_xy,
                       double *__restrict__ com_m, unsigned long long *force_pairs) {
-    int t = blockIdx.x * blockDim.x + threadIdx.x;
-    int c = t / LANES, lane = t % LANES;
-    int s = 0, e = 0;
-    if (c < g.ncells) { s = cell_start[c]; e = cell_start[c + 1]; }
-    double M = 0, Mx = 0, My = 0;
-    for (int k = s + lane; k < e; k += LANES) {
-        double mk = m[k];
-        double2 p = pos[k];
-        M += mk;
-        Mx = fma(mk, p.x, Mx);
-        My = fma(mk, p.y, My);
-    }
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c0 = (t / LANES) * kComCells, lane = t % LANES;
+    // Each lane group takes kComCells consecutive cells and has the first kComAhead rounds of all of
+    // them in flight at once (memory-level parallelism: a cell is only ~2.4 KB).  Out-of-range
+    // slots add exact zeros, so the order of additions is that of the plain strided loop.
+    int b[kComCells + 1];
 #pragma unroll
-    for (int o = LANES / 2; o > 0; o >>= 1) {
-        M += __shfl_xor_sync(0xffffffffu, M, o);
-        Mx += __shfl_xor_sync(0xffffffffu, Mx, o);
-        My += __shfl_xor_sync(0xffffffffu, My, o);
+    for (int q = 0; q <= kComCells; q++) b[q] = cell_start[min(c0 + q, g.ncells)];
+    double mk[kComCells][kComAhead];
+    double2 pk[kComCells][kComAhead];
+#pragma unroll
+    for (int q = 0; q < kComCells; q++) {
+#pragma unroll
+        for (int j = 0; j < kComAhead; j++) {
+            const int k = b[q] + lane + j * LANES;
+            const bool in = k < b[q + 1];
+            mk[q][j] = in ? m[k] : 0.0;
+            pk[q][j] = in ? pos[k] : make_double2(0.0, 0.0);
+        }
     }
     unsigned long long pairs = 0;
-    if (lane == 0 && c < g.ncells) {
-        double2 r = make_double2(0.0, 0.0);
-        if (M > 0) r = make_double2(Mx / M, My / M);
-        com_xy[c + g.nc] = r;
-        com_m[c + g.nc] = M;
-        unsigned long long a = (unsigned long long)(e - s);
-        pairs = a * (a - 1);
+#pragma unroll
+    for (int q = 0; q < kComCells; q++) {
+        const int c = c0 + q, s = b[q], e = b[q + 1];
+        double M = 0, Mx = 0, My = 0;
+#pragma unroll
+        for (int j = 0; j < kComAhead; j++) {
+            M += mk[q][j];
+            Mx = fma(mk[q][j], pk[q][j].x, Mx);
+            My = fma(mk[q][j], pk[q][j].y, My);
+        }
+        for (int k = s + lane + kComAhead * LANES; k < e; k += LANES) {
+            double mv = m[k];
+            double2 p = pos[k];
+            M += mv;
+            Mx = fma(mv, p.x, Mx);
+            My = fma(mv, p.y, My);
+        }
+#pragma unroll
+        for (int o = LANES / 2; o > 0; o >>= 1) {
+            M += __shfl_xor_sync(0xffffffffu, M, o);
+            Mx += __shfl_xor_sync(0xffffffffu, Mx, o);
+            My += __shfl_xor_sync(0xffffffffu, My, o);
+        }
+        if (lane == 0 && c < g.ncells) {
+            double2 r = make_double2(0.0, 0.0);
+            if (M > 0) r = make_double2(Mx / M, My / M);
+            com_xy[c + g.nc] = r;
+            com_m[c + g.nc] = M;
+            unsigned long long a = (unsigned long long)(e - s);
+            pairs += a * (a - 1);
+        }
     }
     if (force_pairs) block_add_u64(pairs, force_pairs);  // stats only (uniform branch)
 }
@@ -436,6 +465,7 @@ k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
                   const int *__restrict__ cell_start, const double2 *__restrict__ com_xy,
                   const double *__restrict__ com_m, double2 *__restrict__ pos_out,
                   float2 *__restrict__ posf_out, double2 *__restrict__ vel, int *__restrict__ newcell,
+                  unsigned char *__restrict__ flags, int *__restrict__ mover_list, int *n_movers,
                   double2 *__restrict__ dbg_acc) {
     __shared__ double2 s_pos[kForceTile];
     __shared__ double s_m[kForceTile];
@@ -513,7 +543,19 @@ k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
     pos_out[i] = pn;
     if (posf_out) posf_out[i] = make_float2((float)x, (float)y);  // pre-filter of k_collide_find
     vel[i] = v;
-    newcell[i] = global_cell_fast(pn, g);     // :174-177
+    const int cnew = global_cell_fast(pn, g);  // :174-177
+    newcell[i] = cnew;
+    // movers (:183-190) are rare: they go on a list for k_classify, everybody else is done here
+    const bool mover = cnew != c + g.cell_base;
+    flags[i] = mover ? (unsigned char)F_MOVER : (unsigned char)0;
+    if (mover) {
+        const unsigned mm = __activemask();
+        const int lane = threadIdx.x & 31, leader = __ffs(mm) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(n_movers, __popc(mm));
+        base = __shfl_sync(mm, base, leader);
+        mover_list[base + __popc(mm & ((1u << lane) - 1u))] = i;
+    }
 }
 
 // ---------------------------------------------------------------------------------------
@@ -535,58 +577,51 @@ __device__ __forceinline__ bool tombstone_between(const int *__restrict__ dead_s
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_classify(Geom g, int n, const int *__restrict__ cell, const int *__restrict__ cell_start,
+k_classify(Geom g, const int *__restrict__ mover_list, const int *__restrict__ n_movers,
+           const int *__restrict__ cell, const int *__restrict__ cell_start,
            const int *__restrict__ newcell, const unsigned *__restrict__ id,
            const int *__restrict__ dead_start, const unsigned *__restrict__ dead_id,
            unsigned char *__restrict__ flags, int *arr_head, int *__restrict__ arr_next,
            const double2 *__restrict__ pos_new, int *arr_cnt, ArrRec *__restrict__ arr_rec,
-           unsigned long long *stat_movers, unsigned long long *stat_strays) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    unsigned long long mover = 0, stray = 0;
-    if (i < n) {
+           unsigned long long *stat_strays) {
+    const int nm = *n_movers;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nm; t += gridDim.x * blockDim.x) {
+        const int i = mover_list[t];
         const int c = cell[i];
         const int cg = c + g.cell_base;
         const int dstg = newcell[i];
-        unsigned char f = 0;
-        if (dstg != cg) {
-            // length of the run of consecutive leavers that ends just before i
-            int run = 0;
-            const int s = cell_start[c];
-            for (int t = i - 1; t >= s; t--) {
-                if (newcell[t] == cg) break;
-                if (tombstone_between(dead_start, dead_id, c, id[t], id[t + 1])) break;
-                run++;
-            }
-            f = F_MOVER;
-            mover = 1;
-            if ((run & 1) == 0) {
-                f |= F_REMOVED;
-                int dst = dstg - g.cell_base;
-                if (dst >= 0 && dst < g.ncells) {
-                    arr_next[i] = atomicExch(&arr_head[dst], i);  // unordered bag; order comes from keys
-                    if (arr_cnt) {
-                        const int sl = atomicAdd(&arr_cnt[dst], 1);
-                        if (sl < kArrSlots) {
-                            ArrRec r;
-                            r.pos = pos_new[i];
-                            r.key = (1ull << 63) | ((unsigned long long)(unsigned)cg << 32) | id[i];
-                            r.idx = i;
-                            r.pad = 0;
-                            arr_rec[(size_t)dst * kArrSlots + sl] = r;
-                        }
+        // length of the run of consecutive leavers that ends just before i
+        int run = 0;
+        const int s = cell_start[c];
+        for (int u = i - 1; u >= s; u--) {
+            if (newcell[u] == cg) break;
+            if (tombstone_between(dead_start, dead_id, c, id[u], id[u + 1])) break;
+            run++;
+        }
+        unsigned char f = F_MOVER;
+        if ((run & 1) == 0) {
+            f |= F_REMOVED;
+            int dst = dstg - g.cell_base;
+            if (dst >= 0 && dst < g.ncells) {
+                arr_next[i] = atomicExch(&arr_head[dst], i);  // unordered bag; order comes from keys
+                if (arr_cnt) {
+                    const int sl = atomicAdd(&arr_cnt[dst], 1);
+                    if (sl < kArrSlots) {
+                        ArrRec r;
+                        r.pos = pos_new[i];
+                        r.key = (1ull << 63) | ((unsigned long long)(unsigned)cg << 32) | id[i];
+                        r.idx = i;
+                        r.pad = 0;
+                        arr_rec[(size_t)dst * kArrSlots + sl] = r;
                     }
-                } else {
-                    f |= F_EMIGRANT;
                 }
             } else {
-                stray = 1;
+                f |= F_EMIGRANT;
             }
+        } else {
+            atomicAdd(stat_strays, 1ull);  // rare
         }
         flags[i] = f;
-    }
-    if (stat_movers) {  // stats only (uniform branch)
-        block_add_u64(mover, stat_movers);
-        block_add_u64(stray, stat_strays);
     }
 }
 

@@ -53,6 +53,22 @@ k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner, const int *
     for (long long t0 = (long long)blockIdx.x * tile_len; t0 < n; t0 += (long long)gridDim.x * tile_len) {
         unsigned char fts[kResolveRows];
         unsigned dying_mask[kResolveRows];
+        // all loads of the tile are issued before the first one is needed, in two waves
+        // (partner[partner[i]] depends on the first wave)
+        int cc[kResolveRows], nn[kResolveRows], pp[kResolveRows], qq[kResolveRows];
+        unsigned char ff[kResolveRows];
+#pragma unroll
+        for (int r = 0; r < kResolveRows; r++) {
+            const long long ii = t0 + (long long)r * kThreads + threadIdx.x;
+            const bool in = ii < n;
+            const int i = (int)ii;
+            cc[r] = in && i < n_res ? cell[i] : -1;
+            nn[r] = in ? newcell[i] : 0;
+            ff[r] = in ? flags[i] : (unsigned char)0;
+            pp[r] = in ? partner[i] : -1;
+        }
+#pragma unroll
+        for (int r = 0; r < kResolveRows; r++) qq[r] = pp[r] >= 0 ? partner[pp[r]] : -1;
 #pragma unroll
         for (int r = 0; r < kResolveRows; r++) {
             const long long ii = t0 + (long long)r * kThreads + threadIdx.x;
@@ -60,15 +76,15 @@ k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner, const int *
             int c = -2 - lane;  // lanes past the end match nobody
             int ft = 255, nl = -1;
             if (ii < n) {
-                c = i < n_res ? cell[i] : -40 - lane;  // guests have no bin-time cell
-                nl = newcell[i] - g.cell_base;
+                c = i < n_res ? cc[r] : -40 - lane;  // guests have no bin-time cell
+                nl = nn[r] - g.cell_base;
                 const bool in_strip = nl >= 0 && nl < g.ncells;
-                if (flags[i] & F_EMIGRANT) {
+                if (ff[r] & F_EMIGRANT) {
                     ft = FATE_EMIGRATED;
                 } else {
-                    const int p = partner[i];
+                    const int p = pp[r];
                     const bool dead = p >= 0;
-                    if (dead && partner[p] == i && i < p) mine++;  // mutual-first pair, counted once
+                    if (dead && qq[r] == i && i < p) mine++;  // mutual-first pair, counted once
                     if (!in_strip) ft = dead ? FATE_LEFT_DEAD : FATE_LEFT_ALIVE;
                     else if (nl == c) ft = dead ? FATE_DEAD_HERE : FATE_STAY;
                     else ft = dead ? FATE_DEAD_MOVED : FATE_MOVE;

@@ -89,10 +89,9 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
             else if (!strcmp(e, "grid")) c->collide_grid = true;
         }
         if (c->collide_grid) {
-            const int nbins = c->grid_nb * c->grid_nb;
 #define PS_COLLIDE_ATTR(IT)                                                                              \
     PS_CUDA(c, cudaFuncSetAttribute(k_collide_cells<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
-                                    (int)(kCollideWarps * warp_staging_bytes(nbins, 32 * IT + 32))))
+                                    (int)(kCollideWarps * warp_staging_bytes(32 * IT + 32))))
             PS_COLLIDE_ATTR(1); PS_COLLIDE_ATTR(2); PS_COLLIDE_ATTR(3); PS_COLLIDE_ATTR(4);
             PS_COLLIDE_ATTR(6); PS_COLLIDE_ATTR(8); PS_COLLIDE_ATTR(12);
 #undef PS_COLLIDE_ATTR

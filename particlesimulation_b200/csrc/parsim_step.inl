@@ -136,7 +136,7 @@ static int merge_step(Rank *c, int n_src, int n_surv, bool with_dead) {
 
 template <int LANES>
 static void launch_com(Rank *c) {
-    long long threads = (long long)c->g.ncells * LANES;
+    long long threads = ((long long)c->g.ncells + kComCells - 1) / kComCells * LANES;
     k_com<LANES><<<grid_for(threads), kThreads, 0, c->stream>>>(
         c->g, c->pos_cur, c->m_cur, c->cs_cur, c->com_xy, c->com_m,
         c->opt_stats ? &c->d_ctr->force_pairs : nullptr);
@@ -173,8 +173,10 @@ static int stage_force(Rank *c) {
 #define PS_FORCE(TB, UN)                                                                            \
     k_force_integrate<TB, UN><<<grid_for(c->n_alive, TB), TB, 0, c->stream>>>(                      \
         c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,        \
-        c->pos_alt, c->posf, c->vel_cur, c->newcell, c->dbg_acc)
-    PS_LAUNCH(c, K_FORCE, 80.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate", {
+        c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
+        c->dbg_acc)
+    PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->n_movers, 0, sizeof(int), c->stream));
+    PS_LAUNCH(c, K_FORCE, 81.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate", {
         const int v = c->force_tb * 100 + c->force_unroll;
         switch (v) {
         case 12802: PS_FORCE(128, 2); break;
@@ -194,12 +196,13 @@ static int stage_force(Rank *c) {
 // stage 2: list update (movers / strays), and emigrants to the neighbouring strips
 static int stage_lists(Rank *c) {
     const Geom &g = c->g;
-    PS_LAUNCH(c, K_CLASSIFY, 9.0 * c->n_alive + 4.0 * g.ncells, "k_classify",
-              k_classify<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
-                  g, c->n_alive, c->cell_cur, c->cs_cur, c->newcell, c->id_cur,
+    // the mover list (written by k_force_integrate) lives in `partner`, which is free until the
+    // collision search; about 1-5 % of the particles are on it
+    PS_LAUNCH(c, K_CLASSIFY, 0.5 * c->n_alive, "k_classify",
+              k_classify<<<148 * 4, kThreads, 0, c->stream>>>(
+                  g, c->partner, &c->d_ctr->n_movers, c->cell_cur, c->cs_cur, c->newcell, c->id_cur,
                   c->n_tomb > 0 ? c->dead_start_cur : nullptr, c->dead_id_cur, c->flags, c->arr_head,
-                  c->arr_next, c->pos_alt, c->arr_cnt, c->arr_rec,
-                  c->opt_stats ? &c->d_ctr->movers : nullptr, &c->d_ctr->strays));
+                  c->arr_next, c->pos_alt, c->arr_cnt, c->arr_rec, &c->d_ctr->strays));
     c->n_guest = 0;
     if (c->nranks > 1 && exchange_emigrants(c)) return 1;
     c->have_flags = true;
@@ -208,7 +211,7 @@ static int stage_lists(Rank *c) {
 
 template <int IT>
 static void launch_collide_cells(Rank *c, const CollideArgs &a) {
-    const size_t sh = kCollideWarps * warp_staging_bytes(a.nb * a.nb, 32 * IT + 32);
+    const size_t sh = kCollideWarps * warp_staging_bytes(32 * IT + 32);
     k_collide_cells<IT><<<grid_for(c->g.ncells, kCollideWarps), kCollideWarps * 32, sh, c->stream>>>(a);
 }
 
@@ -228,9 +231,9 @@ static int stage_collide(Rank *c) {
         PS_CUDA(c, cudaMemsetAsync(c->d_big_count, 0, sizeof(int), c->stream));
         a.nb = c->grid_nb; a.inv_h = c->grid_nb / g.cellw; a.cap = c->grid_cap;
         PS_LAUNCH(c, K_COLLIDE, 29.0 * n_tot + 8.0 * g.ncells, "k_collide_cells", {
-            // entries per lane from the CURRENT occupancy (+2.5 sigma); fuller cells go to k_collide_big
+            // entries per lane from the CURRENT occupancy (+2 sigma); fuller cells go to k_collide_big
             const double now = (double)n_tot / std::max(1, g.ncells);
-            const double want = now + 2.5 * sqrt(now) + 4.0;
+            const double want = now + 2.0 * sqrt(now) + 4.0;
             const int it = want <= 32 ? 1 : want <= 64 ? 2 : want <= 96 ? 3 : want <= 128 ? 4 : want <= 192 ? 6 : want <= 256 ? 8 : 12;
             switch (std::min(it, c->grid_it)) {
             case 1: launch_collide_cells<1>(c, a); break;
@@ -278,6 +281,7 @@ static int stage_collide(Rank *c) {
         n_next = c->h_ctr->n_next;
     }
     c->stats.alive_particle_steps += c->n_alive;
+    c->stats.movers += c->h_ctr->n_movers;
     c->stats.deaths += deaths;
     c->n_alive = n_next;
     c->n_guest = 0;
