@@ -10,14 +10,19 @@
 //   emigrants after the list update:    removed movers whose new cell is in the other strip
 //   late      after the collisions:     surviving strays that left the strip + tombstones
 // Payloads are KB-scale; a record is 8 doubles.
+// A close encounter (two particles a few 1e-6 apart) throws both many cells away in one step,
+// exactly as in the reference; such "far" records (anything that is not the adjacent row of a
+// neighbouring strip) are all-gathered and every strip keeps the ones that landed in its rows.
 #pragma once
 #include <limits.h>
+#include <stdio.h>
 
 #include "parsim_rank.cuh"
 #include "parsim_merge.cuh"
 
 namespace parsim {
 
+constexpr int kFarCap = 4096;  // far records per strip per exchange (see exchange_records)
 constexpr int kRec = 8;  // doubles per migrant record: x y vx vy m (id|src<<32) (cell|kind<<32) pad
 
 __device__ __forceinline__ double pack_u64(unsigned long long v) { return __longlong_as_double((long long)v); }
@@ -45,15 +50,16 @@ __global__ void k_pack_emigrants(Geom g, int n, int mig_cap, const unsigned char
                                  const double2 *__restrict__ pos, const double2 *__restrict__ vel,
                                  const double *__restrict__ m, const unsigned *__restrict__ id,
                                  const int *__restrict__ cell, const int *__restrict__ newcell,
-                                 double *send_up, double *send_dn, int *hdr, Counters *ctr) {
+                                 double *send_up, double *send_dn, double *send_far, int *hdr,
+                                 Counters *ctr) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n || !(flags[i] & F_EMIGRANT)) return;
     int dir = strip_dir(g, newcell[i]);
-    if (dir < 0) { ctr->error = DE_LONG_JUMP; return; }
+    if (dir < 0) dir = 2;  // far
     int slot = atomicAdd(&hdr[dir], 1);
-    if (slot >= mig_cap) { ctr->error = DE_MIGRANT_OVERFLOW; return; }
-    write_record(dir ? send_dn : send_up, slot, pos[i], vel[i], m[i], id[i], cell[i] + g.cell_base,
-                 newcell[i], 0);
+    if (slot >= (dir == 2 ? kFarCap : mig_cap)) { ctr->error = DE_MIGRANT_OVERFLOW; return; }
+    write_record(dir == 2 ? send_far : dir ? send_dn : send_up, slot, pos[i], vel[i], m[i], id[i],
+                 cell[i] + g.cell_base, newcell[i], 0);
 }
 
 // guests: removed movers that arrived from the neighbouring strips; they sit behind the
@@ -61,7 +67,8 @@ __global__ void k_pack_emigrants(Geom g, int n, int mig_cap, const unsigned char
 __global__ void k_unpack_guests(Geom g, int n_rec, const double *__restrict__ recv, int first_idx,
                                 int guest_first, double2 *pos, float2 *posf, double2 *vel, double *m, unsigned *id,
                                 int *cell, int *newcell, unsigned char *flags, int *guest_src,
-                                int *arr_head, int *arr_next, int *arr_cnt, Counters *ctr) {
+                                int *arr_head, int *arr_next, int *arr_cnt, int *partner, int filter,
+                                Counters *ctr) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_rec) return;
     const double *r = recv + (size_t)t * kRec;
@@ -69,7 +76,15 @@ __global__ void k_unpack_guests(Geom g, int n_rec, const double *__restrict__ re
     int idx = first_idx + t;
     int dstg = (int)(unsigned)(b & 0xffffffffu);
     int dst = dstg - g.cell_base;
-    if (dst < 0 || dst >= g.ncells) { ctr->error = DE_LONG_JUMP; return; }
+    if (dst < 0 || dst >= g.ncells) {
+        if (!filter) { ctr->error = 22; return; }
+        // a far record that landed on another strip: a void entry that every kernel skips
+        cell[idx] = -1;
+        newcell[idx] = dstg;
+        flags[idx] = F_MOVER | F_REMOVED | F_EMIGRANT | F_GUEST;
+        partner[idx] = -1;
+        return;
+    }
     pos[idx] = make_double2(r[0], r[1]);
     if (posf) posf[idx] = make_float2((float)r[0], (float)r[1]);
     vel[idx] = make_double2(r[2], r[3]);
@@ -89,16 +104,16 @@ __global__ void k_pack_late(Geom g, int n, int mig_cap, const unsigned char *__r
                             const double2 *__restrict__ pos,
                             const double2 *__restrict__ vel, const double *__restrict__ m,
                             const unsigned *__restrict__ id, const int *__restrict__ newcell,
-                            double *send_up, double *send_dn, int *hdr, Counters *ctr) {
+                            double *send_up, double *send_dn, double *send_far, int *hdr, Counters *ctr) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const int ft = fate[i];
     if (ft != FATE_LEFT_ALIVE && ft != FATE_LEFT_DEAD) return;
     int dir = strip_dir(g, newcell[i]);
-    if (dir < 0) { ctr->error = DE_LONG_JUMP; return; }
+    if (dir < 0) dir = 2;  // far
     int slot = atomicAdd(&hdr[dir], 1);
-    if (slot >= mig_cap) { ctr->error = DE_MIGRANT_OVERFLOW; return; }
-    write_record(dir ? send_dn : send_up, slot, pos[i], vel[i], m[i], id[i], 0, newcell[i],
+    if (slot >= (dir == 2 ? kFarCap : mig_cap)) { ctr->error = DE_MIGRANT_OVERFLOW; return; }
+    write_record(dir == 2 ? send_far : dir ? send_dn : send_up, slot, pos[i], vel[i], m[i], id[i], 0, newcell[i],
                  ft == FATE_LEFT_DEAD ? 1 : 0);
 }
 
@@ -107,7 +122,7 @@ __global__ void k_pack_late(Geom g, int n, int mig_cap, const unsigned char *__r
 __global__ void k_unpack_late(Geom g, int n_rec, const double *__restrict__ recv, int first_idx,
                               double2 *pos, double2 *vel, double *m, unsigned *id, unsigned char *fate,
                               int *count, int *dead_new_count, int *mv_head, int *dm_head, int *mv_next,
-                              Counters *ctr) {
+                              int filter, Counters *ctr) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_rec) return;
     const double *r = recv + (size_t)t * kRec;
@@ -116,7 +131,11 @@ __global__ void k_unpack_late(Geom g, int n_rec, const double *__restrict__ recv
     int cg = (int)(unsigned)(b & 0xffffffffu);
     int kind = (int)(b >> 32);
     int c = cg - g.cell_base;
-    if (c < 0 || c >= g.ncells) { ctr->error = DE_LONG_JUMP; return; }
+    if (c < 0 || c >= g.ncells) {
+        if (!filter) { ctr->error = 24; return; }
+        fate[idx] = FATE_EMIGRATED;  // landed on another strip: skipped by the merge
+        return;
+    }
     id[idx] = (unsigned)(a & 0xffffffffu);
     if (kind == 0) {
         pos[idx] = make_double2(r[0], r[1]);
@@ -155,13 +174,18 @@ inline int exchange_create(Rank *c, const unsigned char *nccl_id) {
             cudaMalloc((void **)&c->mig_recv[d], rec * sizeof(double)) != cudaSuccess)
             return c->fail("cudaMalloc of migrant buffers failed");
     }
-    // hdr_send[0..1], hdr_recv[0..1]
-    if (cudaMalloc((void **)&c->mig_hdr_send, 4 * sizeof(int)) != cudaSuccess)
+    // hdr_send[0..2] = records for the strip above / below / far; hdr_recv[0..1]
+    if (cudaMalloc((void **)&c->mig_hdr_send, 8 * sizeof(int)) != cudaSuccess)
         return c->fail("cudaMalloc failed");
-    c->mig_hdr_recv = c->mig_hdr_send + 2;
-    if (cudaMalloc((void **)&c->guest_src, sizeof(int) * 2 * (size_t)c->mig_cap) != cudaSuccess)
+    c->mig_hdr_recv = c->mig_hdr_send + 4;
+    const size_t far = (size_t)kFarCap * kRec;
+    if (cudaMalloc((void **)&c->far_send, far * sizeof(double)) != cudaSuccess ||
+        cudaMalloc((void **)&c->far_recv, far * c->nranks * sizeof(double)) != cudaSuccess ||
+        cudaMalloc((void **)&c->far_cnt_recv, c->nranks * sizeof(int)) != cudaSuccess)
+        return c->fail("cudaMalloc of far-record buffers failed");
+    if (cudaMalloc((void **)&c->guest_src, sizeof(int) * (2 * (size_t)c->mig_cap + (size_t)c->nranks * kFarCap)) != cudaSuccess)
         return c->fail("cudaMalloc failed");
-    if (cudaMallocHost((void **)&c->h_mig_hdr, 4 * sizeof(int)) != cudaSuccess)
+    if (cudaMallocHost((void **)&c->h_mig_hdr, (8 + c->nranks) * sizeof(int)) != cudaSuccess)
         return c->fail("cudaMallocHost failed");
     return 0;
 }
@@ -174,6 +198,9 @@ inline void exchange_destroy(Rank *c) {
         if (c->mig_recv[d]) cudaFree(c->mig_recv[d]);
     }
     if (c->mig_hdr_send) cudaFree(c->mig_hdr_send);
+    if (c->far_send) cudaFree(c->far_send);
+    if (c->far_recv) cudaFree(c->far_recv);
+    if (c->far_cnt_recv) cudaFree(c->far_cnt_recv);
     if (c->h_mig_hdr) cudaFreeHost(c->h_mig_hdr);
 }
 
@@ -199,59 +226,75 @@ inline int exchange_halo(Rank *c) {
     return 0;
 }
 
-// Ship hdr_send[0] records up and hdr_send[1] records down; learn how many arrive.
-// recv[1] holds what came from below, recv[0] what came from above.
-inline int exchange_records(Rank *c, int *from_up, int *from_dn) {
+// Ship hdr_send[0] records up, hdr_send[1] down and all-gather the hdr_send[2] far records; learn
+// how many arrive.  recv[1] holds what came from below, recv[0] what came from above, far_recv the
+// far records of every strip (stride *far_stride records per strip, far_cnt[r] of them valid).
+// h_mig_hdr: [0..2] sent up / down / far, [4..5] received from up / down, [8..8+nranks) far counts.
+inline int exchange_records(Rank *c, int *from_up, int *from_dn, int *far_stride) {
     NcclApi &api = nccl_api();
-    PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr, c->mig_hdr_send, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr, c->mig_hdr_send, 3 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     PS_NCCL(c, api.GroupStart());
     PS_NCCL(c, api.Send(c->mig_hdr_send + 0, 1, kNcclInt32, c->up, c->comm.comm, c->stream));
     PS_NCCL(c, api.Send(c->mig_hdr_send + 1, 1, kNcclInt32, c->dn, c->comm.comm, c->stream));
     PS_NCCL(c, api.Recv(c->mig_hdr_recv + 1, 1, kNcclInt32, c->dn, c->comm.comm, c->stream));
     PS_NCCL(c, api.Recv(c->mig_hdr_recv + 0, 1, kNcclInt32, c->up, c->comm.comm, c->stream));
+    PS_NCCL(c, api.AllGather(c->mig_hdr_send + 2, c->far_cnt_recv, 1, kNcclInt32, c->comm.comm, c->stream));
     PS_NCCL(c, api.GroupEnd());
-    PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr + 2, c->mig_hdr_recv, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr + 4, c->mig_hdr_recv, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr + 8, c->far_cnt_recv, c->nranks * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error) +
-                                        " (2 = particle jumped past the neighbouring strip, 3 = migrant buffer overflow)");
-    const int su = c->h_mig_hdr[0], sd = c->h_mig_hdr[1], ru = c->h_mig_hdr[2], rd = c->h_mig_hdr[3];
+                                        " (3 = migrant buffer overflow; 22 / 24 = a record for another strip arrived)");
+    const int su = c->h_mig_hdr[0], sd = c->h_mig_hdr[1], ru = c->h_mig_hdr[4], rd = c->h_mig_hdr[5];
     if (ru > c->mig_cap || rd > c->mig_cap) return c->fail("migrant buffer overflow on receive");
-    c->stats.migrants += su + sd;
-    if (su + sd + ru + rd > 0) {
+    int far_max = 0;  // the same on every strip: everybody sees all the counts
+    for (int r = 0; r < c->nranks; r++) far_max = std::max(far_max, c->h_mig_hdr[8 + r]);
+    if (far_max > kFarCap) return c->fail("far-record buffer overflow");
+    c->stats.migrants += su + sd + c->h_mig_hdr[2];
+    if (su + sd + ru + rd + far_max > 0) {
         PS_NCCL(c, api.GroupStart());
         if (su) PS_NCCL(c, api.Send(c->mig_send[0], (size_t)su * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
         if (sd) PS_NCCL(c, api.Send(c->mig_send[1], (size_t)sd * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));
         if (rd) PS_NCCL(c, api.Recv(c->mig_recv[1], (size_t)rd * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));
         if (ru) PS_NCCL(c, api.Recv(c->mig_recv[0], (size_t)ru * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
+        if (far_max)
+            PS_NCCL(c, api.AllGather(c->far_send, c->far_recv, (size_t)far_max * kRec, kNcclFloat64, c->comm.comm, c->stream));
         PS_NCCL(c, api.GroupEnd());
     }
     *from_up = ru;
     *from_dn = rd;
+    *far_stride = far_max;
     return 0;
 }
 
 inline int exchange_emigrants(Rank *c) {
     const Geom &g = c->g;
     timed_begin(c, K_MIGRATE, 0);
-    PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 2 * sizeof(int), c->stream));
+    PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 3 * sizeof(int), c->stream));
     k_pack_emigrants<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
         g, c->n_alive, c->mig_cap, c->flags, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->cell_cur,
-        c->newcell, c->mig_send[0], c->mig_send[1], c->mig_hdr_send, c->d_ctr);
-    int ru = 0, rd = 0;
-    if (exchange_records(c, &ru, &rd)) return 1;
-    if (c->n_alive + ru + rd > c->cap) return c->fail("strip capacity exceeded by arriving particles");
-    int first = c->n_alive;
-    if (ru)
-        k_unpack_guests<<<grid_for(ru), kThreads, 0, c->stream>>>(
-            g, ru, c->mig_recv[0], first, 0, c->pos_alt, c->posf, c->vel_cur, c->m_cur, c->id_cur, c->cell_cur,
-            c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->arr_cnt, c->d_ctr);
-    if (rd)
-        k_unpack_guests<<<grid_for(rd), kThreads, 0, c->stream>>>(
-            g, rd, c->mig_recv[1], first + ru, ru, c->pos_alt, c->posf, c->vel_cur, c->m_cur, c->id_cur,
-            c->cell_cur, c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->arr_cnt, c->d_ctr);
+        c->newcell, c->mig_send[0], c->mig_send[1], c->far_send, c->mig_hdr_send, c->d_ctr);
+    int ru = 0, rd = 0, far_stride = 0;
+    if (exchange_records(c, &ru, &rd, &far_stride)) return 1;
+    int n_far = 0;
+    for (int r = 0; r < c->nranks; r++) if (r != c->rank) n_far += c->h_mig_hdr[8 + r];
+    if (c->n_alive + ru + rd + n_far > c->cap) return c->fail("strip capacity exceeded by arriving particles");
+    int first = c->n_alive, gfirst = 0;
+    auto unpack = [&](int cnt, const double *buf, int filter) {
+        if (!cnt) return;
+        k_unpack_guests<<<grid_for(cnt), kThreads, 0, c->stream>>>(
+            g, cnt, buf, first, gfirst, c->pos_alt, c->posf, c->vel_cur, c->m_cur, c->id_cur, c->cell_cur,
+            c->newcell, c->flags, c->guest_src, c->arr_head, c->arr_next, c->arr_cnt, c->partner, filter, c->d_ctr);
+        first += cnt;
+        gfirst += cnt;
+    };
+    unpack(ru, c->mig_recv[0], 0);
+    unpack(rd, c->mig_recv[1], 0);
+    for (int r = 0; r < c->nranks; r++)
+        if (r != c->rank) unpack(c->h_mig_hdr[8 + r], c->far_recv + (size_t)r * far_stride * kRec, 1);
     timed_end(c);
-    c->n_guest = ru + rd;
+    c->n_guest = ru + rd + n_far;
     return check_launch(c, "exchange_emigrants");
 }
 
@@ -259,24 +302,30 @@ inline int exchange_late(Rank *c, int *n_src, int *n_tombstones_in) {
     const Geom &g = c->g;
     const int n_tot = c->n_alive + c->n_guest;
     timed_begin(c, K_MIGRATE, 0);
-    PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 2 * sizeof(int), c->stream));
+    PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 3 * sizeof(int), c->stream));
     k_pack_late<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
         g, n_tot, c->mig_cap, c->fate, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->newcell,
-        c->mig_send[0], c->mig_send[1], c->mig_hdr_send, c->d_ctr);
-    int ru = 0, rd = 0;
-    if (exchange_records(c, &ru, &rd)) return 1;
-    if (n_tot + ru + rd > c->cap) return c->fail("strip capacity exceeded by arriving particles");
-    if (ru)
-        k_unpack_late<<<grid_for(ru), kThreads, 0, c->stream>>>(
-            g, ru, c->mig_recv[0], n_tot, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->fate, c->count,
-            c->dead_new_count, c->mv_head, c->dm_head, c->mv_next, c->d_ctr);
-    if (rd)
-        k_unpack_late<<<grid_for(rd), kThreads, 0, c->stream>>>(
-            g, rd, c->mig_recv[1], n_tot + ru, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->fate,
-            c->count, c->dead_new_count, c->mv_head, c->dm_head, c->mv_next, c->d_ctr);
+        c->mig_send[0], c->mig_send[1], c->far_send, c->mig_hdr_send, c->d_ctr);
+    int ru = 0, rd = 0, far_stride = 0;
+    if (exchange_records(c, &ru, &rd, &far_stride)) return 1;
+    int n_far = 0;
+    for (int r = 0; r < c->nranks; r++) if (r != c->rank) n_far += c->h_mig_hdr[8 + r];
+    if (n_tot + ru + rd + n_far > c->cap) return c->fail("strip capacity exceeded by arriving particles");
+    int first = n_tot;
+    auto unpack = [&](int cnt, const double *buf, int filter) {
+        if (!cnt) return;
+        k_unpack_late<<<grid_for(cnt), kThreads, 0, c->stream>>>(
+            g, cnt, buf, first, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->fate, c->count,
+            c->dead_new_count, c->mv_head, c->dm_head, c->mv_next, filter, c->d_ctr);
+        first += cnt;
+    };
+    unpack(ru, c->mig_recv[0], 0);
+    unpack(rd, c->mig_recv[1], 0);
+    for (int r = 0; r < c->nranks; r++)
+        if (r != c->rank) unpack(c->h_mig_hdr[8 + r], c->far_recv + (size_t)r * far_stride * kRec, 1);
     timed_end(c);
-    *n_src = n_tot + ru + rd;
-    *n_tombstones_in = ru + rd;  // upper bound
+    *n_src = first;
+    *n_tombstones_in = ru + rd + n_far;  // upper bound
     return check_launch(c, "exchange_late");
 }
 

@@ -308,6 +308,98 @@ __global__ void k_scan_apply(const int *__restrict__ in, const int *__restrict__
 }
 
 // ---------------------------------------------------------------------------------------
+// Row strips (several GPUs): every strip sees the whole particle stream and keeps the particles
+// whose row it owns -- a STABLE compaction (count per block, scan, write), so the kept records
+// stay in id order and the step-0 sort needs no id passes.
+//   PHASE 0: blk_cnt[block] = particles kept by the block
+//   PHASE 1: records written at base + blk_off[block] + (rank inside the block)
+constexpr int kInitPer = 32;  // particles per thread in k_init_strip (block = kThreads * kInitPer ids)
+
+template <int PHASE>
+__global__ void __launch_bounds__(kThreads)
+k_ingest_strip(Geom g, long long id_base, const unsigned *__restrict__ ids, int count,
+               const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ vx,
+               const double *__restrict__ vy, const double *__restrict__ m, int capacity,
+               int *__restrict__ blk, InitRec *rec, Counters *ctr) {
+    __shared__ int ws[33];
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    bool keep = false;
+    double py = 0.0;
+    if (t < count) {
+        py = y[t];
+        const int row = cell_coord(py, g);
+        keep = row >= g.row0 && row < g.row0 + g.rows;
+    }
+    int tot;
+    const int rank = block_exclusive_scan(keep ? 1 : 0, ws, tot);
+    if (PHASE == 0) {
+        if (threadIdx.x == 0) blk[blockIdx.x] = tot;
+        return;
+    }
+    if (!keep) return;
+    const int slot = ctr->n_staged + blk[blockIdx.x] + rank;
+    if (slot >= capacity) { ctr->error = DE_CAPACITY; return; }
+    const unsigned pid = ids ? ids[t] : (unsigned)(id_base + t);
+    store_rec(rec, slot, make_double2(x[t], py), make_double2(vx[t], vy[t]), m[t], pid);
+}
+
+__global__ void k_advance_staged(Counters *ctr, const int *total) { ctr->n_staged += *total; }
+
+__device__ __forceinline__ void xs_step(unsigned &s) {
+    s ^= s << 13;
+    s ^= s >> 17;
+    s ^= s << 5;
+}
+
+// jt->stride must be M^(5 * kThreads - 5) here: a thread's particles are kThreads ids apart.
+template <int PHASE>
+__global__ void __launch_bounds__(kThreads)
+k_init_strip(Geom g, const XsJumpTable *__restrict__ jt, unsigned s0, long long n_part, int capacity,
+             int *__restrict__ blk, InitRec *rec, Counters *ctr) {
+    __shared__ int ws[33];
+    const long long first = (long long)blockIdx.x * (kThreads * kInitPer) + threadIdx.x;
+    unsigned s = s0;
+    unsigned long long jump = 5ull * (unsigned long long)first;
+    for (int j = 0; jump; j++, jump >>= 1)
+        if (jump & 1ull) s = xs_apply(jt->pow2[j], s);
+    const double ncd = (double)g.nc;
+    const double cc = (double)((long long)g.nc * g.nc);
+    const double nd = (double)n_part;
+    int running = PHASE == 1 ? ctr->n_staged + blk[blockIdx.x] : 0;
+    int kept = 0;
+    for (int r = 0; r < kInitPer; r++) {
+        const long long i = first + (long long)r * kThreads;
+        const double x = __dmul_rn(xs_draw(s), g.side);
+        const double y = __dmul_rn(xs_draw(s), g.side);
+        const int row = cell_coord(y, g);
+        const bool keep = i < n_part && row >= g.row0 && row < g.row0 + g.rows;
+        if (PHASE == 0) {
+            xs_step(s); xs_step(s); xs_step(s);
+            kept += keep ? 1 : 0;
+        } else {
+            const double vx = __ddiv_rn(__ddiv_rn(__dmul_rn(__dadd_rn(xs_draw(s), -0.5), g.side), ncd), 5.0);
+            const double vy = __ddiv_rn(__ddiv_rn(__dmul_rn(__dadd_rn(xs_draw(s), -0.5), g.side), ncd), 5.0);
+            const double m = __dmul_rn(__ddiv_rn(__ddiv_rn(__dmul_rn(__dmul_rn(xs_draw(s), 0.01), cc), nd), kG),
+                                       0.005 * 0.005);
+            int tot;
+            const int rank = block_exclusive_scan(keep ? 1 : 0, ws, tot);
+            if (keep) {
+                const int slot = running + rank;
+                if (slot >= capacity) ctr->error = DE_CAPACITY;
+                else store_rec(rec, slot, make_double2(x, y), make_double2(vx, vy), m, (unsigned)i);
+            }
+            running += tot;
+        }
+        s = xs_apply(jt->stride, s);
+    }
+    if (PHASE == 0) {
+        int tot;
+        block_exclusive_scan(kept, ws, tot);
+        if (threadIdx.x == 0) blk[blockIdx.x] = tot;
+    }
+}
+
+// ---------------------------------------------------------------------------------------
 // Centre of mass per cell (north_star (b); Cell::addParticle, serial/parsim.cpp:93-106 computes
 // the same weighted mean as a running average).  LANES lanes per cell, each lane sums a fixed
 // strided subsequence, then a fixed xor-shuffle tree: the order of additions depends only on

@@ -22,6 +22,7 @@ struct NcclApi {
     int (*Send)(const void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*Recv)(void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
     int (*GroupStart)() = nullptr;
     int (*GroupEnd)() = nullptr;
     const char *(*GetErrorString)(int) = nullptr;
@@ -44,6 +45,7 @@ struct NcclApi {
         PS_SYM(Send, "ncclSend");
         PS_SYM(Recv, "ncclRecv");
         PS_SYM(AllReduce, "ncclAllReduce");
+        PS_SYM(AllGather, "ncclAllGather");
         PS_SYM(GroupStart, "ncclGroupStart");
         PS_SYM(GroupEnd, "ncclGroupEnd");
         PS_SYM(GetErrorString, "ncclGetErrorString");

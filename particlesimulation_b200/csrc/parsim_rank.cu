@@ -11,6 +11,8 @@
 
 namespace parsim {
 
+static int device_scan(Rank *c, const int *in, int N, int *out, int *total2);  // parsim_step.inl
+
 template <typename T>
 static int dev_alloc(Rank *c, T **p, size_t count, bool zero = false) {
     size_t bytes = sizeof(T) * (count ? count : 1);
@@ -113,8 +115,9 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
         long long per_row = n_part / ncside + 1;
         long long mc = std::max<long long>(65536, 2 * per_row);
         c->mig_cap = (int)std::min<long long>(mc, n_part);
-        cap = (long long)((double)n_part / nranks * c->capacity_factor) + 4LL * c->mig_cap + 1024;
-        cap = std::min<long long>(cap, n_part + 2LL * c->mig_cap);
+        cap = (long long)((double)n_part / nranks * c->capacity_factor) + 4LL * c->mig_cap + 1024 +
+              2LL * nranks * kFarCap;
+        cap = std::min<long long>(cap, n_part + 2LL * c->mig_cap + 2LL * nranks * kFarCap);
     }
     if (cap > 2147480000LL) return c->fail("strip too large for 32-bit indices: use more GPUs");
     c->cap = (int)cap;
@@ -239,10 +242,25 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
         if (ids)
             PS_CUDA(c, cudaMemcpyAsync(c->stage_ids, ids + off, sizeof(unsigned) * cnt,
                                        cudaMemcpyHostToDevice, c->stream));
-        PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest",
-                  k_ingest<<<grid_for(cnt), kThreads, 0, c->stream>>>(
-                      c->g, id_base + off, ids ? c->stage_ids : nullptr, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
-                      c->stage[4], c->nranks == 1, c->cap - 2 * c->mig_cap, c->rec0, c->d_ctr));
+        const unsigned *dids = ids ? c->stage_ids : nullptr;
+        if (c->nranks == 1) {
+            PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest",
+                      k_ingest<<<grid_for(cnt), kThreads, 0, c->stream>>>(
+                          c->g, id_base + off, dids, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
+                          c->stage[4], 1, c->cap, c->rec0, c->d_ctr));
+        } else {  // stable compaction of this strip's particles: count, scan, write
+            const int nb = grid_for(cnt);
+            PS_LAUNCH(c, K_INGEST, 8.0 * cnt, "k_ingest_strip<0>",
+                      k_ingest_strip<0><<<nb, kThreads, 0, c->stream>>>(
+                          c->g, id_base + off, dids, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
+                          c->stage[4], c->cap - 2 * c->mig_cap, c->sort_hist, c->rec0, c->d_ctr));
+            if (device_scan(c, c->sort_hist, nb, c->sort_hist_scan, nullptr)) return 1;
+            PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest_strip<1>",
+                      k_ingest_strip<1><<<nb, kThreads, 0, c->stream>>>(
+                          c->g, id_base + off, dids, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
+                          c->stage[4], c->cap - 2 * c->mig_cap, c->sort_hist_scan, c->rec0, c->d_ctr));
+            k_advance_staged<<<1, 1, 0, c->stream>>>(c->d_ctr, c->sort_hist_scan + nb);
+        }
         // the staging buffers are reused by the next piece
         PS_CUDA(c, cudaStreamSynchronize(c->stream));
     }
@@ -264,7 +282,15 @@ int rank_upload_end(Rank *c) {
     else c->n_alive = (int)c->n_part;
     c->pos_latest = c->pos_cur;
     c->n0 = c->n_alive;
-    c->slots_id_ordered = c->nranks == 1;
+    c->slots_id_ordered = true;
+    if (c->nranks > 1 && c->n_alive > 1) {  // explicit-id uploads may come in any order
+        PS_CUDA(c, cudaMemsetAsync(c->d_found, 0, sizeof(int), c->stream));
+        k_rec_ids_ascending<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(c->n_alive, c->rec0, c->d_found);
+        int unordered = 0;
+        PS_CUDA(c, cudaMemcpyAsync(&unordered, c->d_found, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->slots_id_ordered = !unordered;
+    }
     return 0;
 }
 
@@ -332,8 +358,10 @@ int rank_init_device(Rank *c, long seed) {
         return c->fail("parsim_init_device: negative seeds use rejection sampling (serial/parsim.cpp:34-43);"
                        " generate on the host and upload");
     if (reset_state(c)) return 1;
+    const bool strips = c->nranks > 1;
     const int blocks = 148 * 8;
-    const unsigned long long T = (unsigned long long)blocks * kThreads;
+    // ids a thread generates are T apart: the whole grid (one strip) or one block (several strips)
+    const unsigned long long T = strips ? (unsigned long long)kThreads : (unsigned long long)blocks * kThreads;
     XsJumpTable jt;
     for (int b = 0; b < 32; b++) jt.pow2[0].col[b] = xs_step_host(1u << b);
     for (int j = 1; j < 34; j++) jt.pow2[j] = xs_mul_host(jt.pow2[j - 1], jt.pow2[j - 1]);
@@ -346,9 +374,21 @@ int rank_init_device(Rank *c, long seed) {
     PS_ALLOC(c, d_jt, 1, false);
     PS_CUDA(c, cudaMemcpyAsync(d_jt, &jt, sizeof(jt), cudaMemcpyHostToDevice, c->stream));
     const unsigned s0 = (unsigned)abs(iseed) + 987654321u;  // :24
-    PS_LAUNCH(c, K_INIT, 44.0 * c->n_part, "k_init_particles",
-              k_init_particles<<<blocks, kThreads, 0, c->stream>>>(
-                  c->g, d_jt, s0, c->n_part, c->nranks == 1, c->cap - 2 * c->mig_cap, c->rec0, c->d_ctr));
+    if (!strips) {
+        PS_LAUNCH(c, K_INIT, 44.0 * c->n_part, "k_init_particles",
+                  k_init_particles<<<blocks, kThreads, 0, c->stream>>>(
+                      c->g, d_jt, s0, c->n_part, 1, c->cap, c->rec0, c->d_ctr));
+    } else {  // every strip walks the whole stream and keeps its rows, in id order
+        const int nb = grid_for(c->n_part, kThreads * kInitPer);
+        PS_LAUNCH(c, K_INIT, 0.0, "k_init_strip<0>",
+                  k_init_strip<0><<<nb, kThreads, 0, c->stream>>>(c->g, d_jt, s0, c->n_part, c->cap - 2 * c->mig_cap,
+                                                                 c->sort_hist, c->rec0, c->d_ctr));
+        if (device_scan(c, c->sort_hist, nb, c->sort_hist_scan, nullptr)) return 1;
+        PS_LAUNCH(c, K_INIT, 64.0 * c->n_part / c->nranks, "k_init_strip<1>",
+                  k_init_strip<1><<<nb, kThreads, 0, c->stream>>>(c->g, d_jt, s0, c->n_part, c->cap - 2 * c->mig_cap,
+                                                                 c->sort_hist_scan, c->rec0, c->d_ctr));
+        k_advance_staged<<<1, 1, 0, c->stream>>>(c->d_ctr, c->sort_hist_scan + nb);
+    }
     c->uploading = true;
     c->n_uploaded = c->n_part;
     int rc = rank_upload_end(c);

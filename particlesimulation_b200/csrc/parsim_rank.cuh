@@ -107,6 +107,9 @@ struct Rank {
     int mig_cap = 0;             // records per direction
     double *mig_send[2] = {nullptr, nullptr}, *mig_recv[2] = {nullptr, nullptr};
     int *mig_hdr_send = nullptr, *mig_hdr_recv = nullptr, *h_mig_hdr = nullptr;
+    // far records: particles that a close encounter threw beyond the neighbouring row (any strip)
+    double *far_send = nullptr, *far_recv = nullptr;
+    int *far_cnt_recv = nullptr;
 
     cudaStream_t stream = nullptr;
     std::string err;

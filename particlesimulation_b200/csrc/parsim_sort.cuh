@@ -148,6 +148,12 @@ __global__ void k_sort_cell_keys(int n, const int *__restrict__ src_in, const un
     if (i < n) keys[i] = cellkey[src_in[i]];
 }
 
+// are the record ids ascending in slot order?  (*flag is set to 1 when they are not)
+__global__ void k_rec_ids_ascending(int n, const InitRec *__restrict__ rec, int *flag) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i + 1 < n && rec[i].id >= rec[i + 1].id) *flag = 1;
+}
+
 // cell key of every slot (the reference's binning arithmetic, :268-272)
 __global__ void k_sort_cell_of(Geom g, int n, const InitRec *__restrict__ rec, unsigned *__restrict__ key) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;

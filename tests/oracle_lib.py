@@ -161,3 +161,26 @@ def oracle_draws(seed, count):
     out = np.zeros(count)
     oracle_lib().po_draws(int(seed), count, _d(out))
     return out
+
+
+def far_jump_case(n=4000, pairs=40, side=100.0, ncside=40, seed=11):
+    """A hand-made initial condition with `pairs` close encounters (separations of a few 1e-6):
+    their mutual force throws both partners tens of cells away in ONE step -- the reference just
+    re-bins them wherever they land (serial/parsim.cpp:171-190).  Exercises the fmod / division
+    slow paths and, on several GPUs, the far-record exchange."""
+    rng = np.random.default_rng(seed)
+    G, eps2 = 6.67408e-11, 0.005 * 0.005
+    x = rng.random(n) * side
+    y = rng.random(n) * side
+    vx = (rng.random(n) - 0.5) * side / ncside / 5.0
+    vy = (rng.random(n) - 0.5) * side / ncside / 5.0
+    m = (0.25 + 0.5 * rng.random(n)) * 0.01 * (ncside * ncside) / n / G * eps2
+    for k in range(pairs):
+        a, b = 2 * k, 2 * k + 1
+        d = 2.5e-6 + 4.5e-6 * rng.random()
+        ang = 2 * np.pi * rng.random()
+        x[b] = x[a] + d * np.cos(ang)
+        y[b] = y[a] + d * np.sin(ang)
+    x = np.clip(x, 0.0, np.nextafter(side, 0.0))
+    y = np.clip(y, 0.0, np.nextafter(side, 0.0))
+    return side, ncside, tuple(np.ascontiguousarray(v) for v in (x, y, vx, vy, m))

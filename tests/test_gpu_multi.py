@@ -46,6 +46,30 @@ def test_strips_match_single_gpu(case, n_gpus):
     one.close(); many.close()
 
 
+@pytest.mark.parametrize("n_gpus", [2, 3, 4, 8])
+def test_far_jumps_cross_strips(n_gpus):
+    """Close encounters throw particles many rows away (any strip, not just the neighbour): the
+    far-record exchange must keep N strips bitwise equal to one GPU."""
+    import oracle_lib as ol
+    if ngpu() < n_gpus:
+        pytest.skip(f"needs {n_gpus} GPUs")
+    os.environ["PARSIM_CAPACITY_PCT"] = "400"
+    side, nc, arrs = ol.far_jump_case()
+    n = len(arrs[0])
+    one = ParticleSimulation(0, side, nc, n, arrays=arrs)
+    many = ParticleSimulation(0, side, nc, n, arrays=arrs, n_gpus=n_gpus)
+    for t in range(4):
+        one.simulate(1)
+        many.simulate(1)
+        assert one.result() == many.result(), f"step {t}"
+    a, b = one.dump(), many.dump()
+    assert b["owned"].all()
+    for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+        assert np.array_equal(a[k], b[k]), k
+    assert many.stats()["migrants"] > 0
+    one.close(); many.close()
+
+
 @pytest.mark.parametrize("n_gpus", [2, 4, 8])
 def test_bench_under_torchrun(n_gpus):
     if ngpu() < n_gpus:

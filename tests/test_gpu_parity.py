@@ -155,6 +155,29 @@ def test_collision_search_paths_agree(case, monkeypatch):
         assert np.array_equal(res["pairs"][1][k], res["grid"][1][k]), k
 
 
+def test_close_encounters_throw_particles_far():
+    """Two particles a few 1e-6 apart fly tens of cells in one step; the result must still be the
+    reference's (alive flags and collision count exact, positions to 1e-9 of the box side)."""
+    side, nc, arrs = ol.far_jump_case()
+    n = len(arrs[0])
+    o = ol.oracle_sim_from(side, nc, *arrs)
+    g = ParticleSimulation(0, side, nc, n, arrays=arrs)
+    x_before = arrs[0].copy()
+    for t in range(4):
+        o.step()
+        g.simulate(1)
+        d, p = g.dump(), o.particles()
+        assert g.result()[2] == o.collisions, t
+        assert np.array_equal(d["alive"], p["alive"]), t
+        for k in ("x", "y", "vx", "vy"):
+            assert np.allclose(d[k], p[k], rtol=1e-12, atol=1e-9 * side), (t, k, np.abs(d[k] - p[k]).max())
+        if t == 0:  # the case does what it is meant to: long jumps happened
+            jump = np.abs(d["x"] - x_before)
+            jump = np.minimum(jump, side - jump)
+            assert (jump > 3 * side / nc).sum() >= 20
+    g.close()
+
+
 def test_upload_arrays_path_and_errors():
     arrs = init_particles(1, 2, 3, 10)
     g = ParticleSimulation(0, 2, 3, 10, arrays=arrs)
