@@ -86,6 +86,10 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append([c.strip() for c in line.split(",")])
 
+    def mark(self):
+        """The timed region starts here: earlier samples (warm-up) are dropped if later ones exist."""
+        self.first = len(self.rows)
+
     def stop(self):
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
@@ -93,7 +97,8 @@ class ClockSampler:
         self.proc.terminate()
         self.t.join(timeout=2)
         sm, mx, pw, reasons = [], [], [], set()
-        for r in self.rows:
+        rows = self.rows[getattr(self, "first", 0):] or self.rows
+        for r in rows:
             try:
                 sm.append(float(r[1])); mx.append(float(r[2])); pw.append(float(r[3]))
             except Exception:
@@ -231,13 +236,14 @@ def main_ours(a):
         sim.simulate(nstep)
 
     # ---- device-resident leg: `value` -----------------------------------------------------
+    clocks = ClockSampler(local)
+    clocks.start()  # before the warm-up: nvidia-smi takes a while to come up on an 8-GPU box
     for _ in range(a.warmup):
         one_run()
     sim.set_option("stats", 1)
     sim.stats_reset()
-    clocks = ClockSampler(local)
     barrier()
-    clocks.start()
+    clocks.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(stream)
     for _ in range(a.steps):
