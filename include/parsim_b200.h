@@ -138,6 +138,9 @@ int parsim_stats_reset(parsim_ctx *ctx);
 
 /* FP64 FMA-chain microbenchmark on this context's GPU (the FP64 roofline denominator). */
 int parsim_fp64_peak(parsim_ctx *ctx, double *tflops);
+/* Pair interactions per second of the force loop's own instruction mix (13 FP64 + 1 MUFU per
+ * pair) on register operands: the ceiling the force kernel's inner loop is compared against. */
+int parsim_pair_peak(parsim_ctx *ctx, double *pairs_per_s);
 
 /* options: "keep_initial" (0/1, see parsim_reset), "stats" (0/1), "sync_check" (0/1: synchronise + check after every kernel). */
 int parsim_set_option(parsim_ctx *ctx, const char *name, long long value);

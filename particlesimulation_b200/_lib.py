@@ -44,6 +44,7 @@ SIGNATURES = {
                                   C.POINTER(C.c_longlong)]),
     "parsim_reset": (C.c_int, [_ctx]),
     "parsim_fp64_peak": (C.c_int, [_ctx, _dp]),
+    "parsim_pair_peak": (C.c_int, [_ctx, _dp]),
     "parsim_host_init_particles": (C.c_int, [C.c_long, C.c_double, C.c_long, C.c_longlong, C.c_longlong,
                                              C.c_longlong, _dp, _dp, _dp, _dp, _dp]),
     "parsim_init_device": (C.c_int, [_ctx, C.c_long]),

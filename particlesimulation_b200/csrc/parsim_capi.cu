@@ -146,6 +146,13 @@ int parsim_fp64_peak(parsim_ctx *ctx, double *tflops) {
     return 0;
 }
 
+int parsim_pair_peak(parsim_ctx *ctx, double *pairs_per_s) {
+    Rank *c = ctx->ranks[0].get();
+    if (!pairs_per_s) return ctx_fail(ctx, "pairs_per_s is NULL");
+    if (rank_pair_peak(c, pairs_per_s)) return ctx_fail(ctx, c->err);
+    return 0;
+}
+
 int parsim_upload_end(parsim_ctx *ctx) { return for_ranks(ctx, rank_upload_end); }
 
 int parsim_upload(parsim_ctx *ctx, const double *x, const double *y, const double *vx,

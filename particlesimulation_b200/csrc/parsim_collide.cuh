@@ -190,44 +190,56 @@ __device__ long long collide_cell(const CollideArgs &a, int L, int t, Staging sm
     return tested;
 }
 
-// all-pairs sweep of one list by a group (lists that fit no staging area)
-template <int G>
-__device__ long long collide_cell_allpairs(const CollideArgs &a, int L, int t) {
-    const int s = a.cell_start[L], e = a.cell_start[L + 1];
-    const int head = a.arr_head[L];
-    long long tested = 0;
-    auto sweep = [&](int i) {
-        const double2 p = a.pos[i];
-        unsigned long long best = ~0ull;
-        int best_idx = -1;
-        for (int k = s; k < e; k++) {
-            if (k != i && !(a.flags[k] & F_REMOVED) && is_close(p, a.pos[k], a.thr2)) {
-                const unsigned long long key = a.id[k];
-                if (key < best) { best = key; best_idx = k; }
-            }
+// All-pairs sweep for lists that fit no staging area (tens of thousands of entries per cell).
+// Such a cell is cut into slices of kThreads bin-time entries (+ one slice for the arrivals bag),
+// and k_collide_huge spreads the slices of all such cells over the whole GPU.
+__device__ __forceinline__ long long sweep_allpairs(const CollideArgs &a, int i, int s, int e, int head) {
+    const double2 p = a.pos[i];
+    unsigned long long best = ~0ull;
+    int best_idx = -1;
+#pragma unroll 4
+    for (int k = s; k < e; k++) {
+        if (is_close(p, __ldg(&a.pos[k]), a.thr2) && k != i && !(a.flags[k] & F_REMOVED)) {
+            const unsigned long long key = a.id[k];
+            if (key < best) { best = key; best_idx = k; }
         }
-        int walked = 0;
-        for (int k = head; k >= 0; k = a.arr_next[k], walked++) {
-            if (k != i && is_close(p, a.pos[k], a.thr2)) {
-                const unsigned long long key = entry_key(a, k);
-                if (key < best) { best = key; best_idx = k; }
-            }
-        }
-        tested += e - s + walked;
-        a.partner[i] = best_idx;
-    };
-    for (int k = s + t; k < e; k += G) {
-        const unsigned char f = a.flags[k];
-        if (f & F_REMOVED) {
-            if (f & F_EMIGRANT) a.partner[k] = -1;
-            continue;
-        }
-        sweep(k);
     }
-    int j = 0;
-    for (int x = head; x >= 0; x = a.arr_next[x], j++)
-        if ((j % G) == t) sweep(x);
-    return tested;
+    int walked = 0;
+    for (int k = head; k >= 0; k = a.arr_next[k], walked++) {
+        if (k != i && is_close(p, a.pos[k], a.thr2)) {
+            const unsigned long long key = entry_key(a, k);
+            if (key < best) { best = key; best_idx = k; }
+        }
+    }
+    a.partner[i] = best_idx;
+    return e - s + walked;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_collide_huge(CollideArgs a, const int2 *__restrict__ items, const int *__restrict__ n_items) {
+    long long tested = 0;
+    const int n = *n_items;
+    for (int w = blockIdx.x; w < n; w += gridDim.x) {
+        const int L = items[w].x, slice = items[w].y;
+        const int s = a.cell_start[L], e = a.cell_start[L + 1];
+        const int head = a.arr_head[L];
+        if (slice >= 0) {  // kThreads bin-time entries
+            const int k = s + slice * kThreads + threadIdx.x;
+            if (k < e) {
+                const unsigned char f = a.flags[k];
+                if (f & F_REMOVED) {
+                    if (f & F_EMIGRANT) a.partner[k] = -1;
+                } else {
+                    tested += sweep_allpairs(a, k, s, e, head);
+                }
+            }
+        } else {  // the arrivals bag
+            int j = 0;
+            for (int x = head; x >= 0; x = a.arr_next[x], j++)
+                if ((j % kThreads) == threadIdx.x) tested += sweep_allpairs(a, x, s, e, head);
+        }
+    }
+    if (a.collision_pairs) block_add_u64((unsigned long long)tested, a.collision_pairs);
 }
 
 constexpr int kCollideWarps = 8;  // cells per block in k_collide_cells
@@ -392,7 +404,7 @@ k_collide_cells(CollideArgs a) {
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_collide_big(CollideArgs a) {
+k_collide_big(CollideArgs a, int2 *__restrict__ huge_items, int *huge_count) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ int scratch[kThreads / 32];
     const int nbins = a.nb * a.nb;
@@ -402,10 +414,14 @@ k_collide_big(CollideArgs a) {
     for (int w = blockIdx.x; w < nwork; w += gridDim.x) {
         const int L = a.worklist[w];
         long long r = collide_cell<kThreads>(a, L, threadIdx.x, sm, scratch);
-        if (r < 0) {
-            __syncthreads();
-            r = collide_cell_allpairs<kThreads>(a, L, threadIdx.x);
-            __syncthreads();
+        if (r < 0) {  // fits no staging area: slices for k_collide_huge
+            if (threadIdx.x == 0) {
+                const int nsl = (a.cell_start[L + 1] - a.cell_start[L] + kThreads - 1) / kThreads;
+                const int base = atomicAdd(huge_count, nsl + 1);
+                for (int j = 0; j < nsl; j++) huge_items[base + j] = make_int2(L, j);
+                huge_items[base + nsl] = make_int2(L, -1);
+            }
+            r = 0;
         }
         tested += r;
     }

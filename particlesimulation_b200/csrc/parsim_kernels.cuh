@@ -543,15 +543,37 @@ __device__ __forceinline__ int global_cell_fast(double2 p, const Geom &g) {
     return cell_coord_fast(p.y, g) * g.nc + cell_coord_fast(p.x, g);
 }
 
+// Pair-interaction microbenchmark: accumulate() on register operands only (no memory traffic),
+// four independent targets per thread.  Its rate is the ceiling of the force kernel's inner loop
+// for THIS instruction mix (13 FP64 + 1 MUFU.RSQ64H per pair), which is lower than the FMA-chain
+// peak because the MUFU shares the issue port of the FP64 pipe.
+__global__ void k_pair_peak(int iters, double *out) {
+    double ax0 = 0, ay0 = 0, ax1 = 0, ay1 = 0, ax2 = 0, ay2 = 0, ax3 = 0, ay3 = 0;
+    double qx = 1.0 + threadIdx.x * 1e-3, qy = 2.0 + blockIdx.x * 1e-6;
+    const double px0 = 0.1, px1 = 0.2, px2 = 0.3, px3 = 0.4, py = 0.5, m = 1.25;
+    for (int i = 0; i < iters; i++) {
+        accumulate(qx - px0, qy - py, m, ax0, ay0);
+        accumulate(qx - px1, qy - py, m, ax1, ay1);
+        accumulate(qx - px2, qy - py, m, ax2, ay2);
+        accumulate(qx - px3, qy - py, m, ax3, ay3);
+        qx += 1e-3;  // a new source every iteration
+        qy -= 1e-3;
+    }
+    const double r = ax0 + ay0 + ax1 + ay1 + ax2 + ay2 + ax3 + ay3;
+    if (r == 123.456) out[0] = r;
+}
+
 // A block of TB consecutive particles touches the segments of the cells from its first to its
 // last particle's cell: one contiguous range of the (cell, id)-ordered arrays.  The range is
 // staged in shared memory with coalesced loads (24 B per source), and the pair loop reads it
 // from there: no global load -- and no load latency -- inside the FP64-bound loop.  Ranges
-// longer than kForceTile sources (very full cells) are read through L1 instead.
-constexpr int kForceTile = 1280;
-
-template <int TB, int UNROLL>
-__global__ void __launch_bounds__(TB)
+// longer than TILE sources (very full cells) are read through L1 instead.
+// TILE = staged sources per block, CELLS = cells per block whose 8 neighbour centres of mass are
+// staged (0: read through L1 per particle), MINB = resident blocks per SM the register budget is
+// set for: full cells want the deep unrolled pair loop (many registers), sparse cells want
+// occupancy (the kernel is then a chain of dependent loads per particle).
+template <int TB, int UNROLL, int TILE, int CELLS, int MINB>
+__global__ void __launch_bounds__(TB, MINB)
 k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
                   const double *__restrict__ m, const int *__restrict__ cell,
                   const int *__restrict__ cell_start, const double2 *__restrict__ com_xy,
@@ -559,13 +581,15 @@ k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
                   float2 *__restrict__ posf_out, double2 *__restrict__ vel, int *__restrict__ newcell,
                   unsigned char *__restrict__ flags, int *__restrict__ mover_list, int *n_movers,
                   double2 *__restrict__ dbg_acc) {
-    __shared__ double2 s_pos[kForceTile];
-    __shared__ double s_m[kForceTile];
+    __shared__ double2 s_pos[TILE];
+    __shared__ double s_m[TILE];
+    __shared__ double2 s_nxy[CELLS > 0 ? CELLS * 8 : 1];
+    __shared__ double s_nm[CELLS > 0 ? CELLS * 8 : 1];
     const int b0 = blockIdx.x * TB;
     const int i = b0 + threadIdx.x;
     const int last = min(b0 + TB, n) - 1;
     const int r0 = cell_start[cell[b0]], r1 = cell_start[cell[last] + 1];
-    const bool staged = r1 - r0 <= kForceTile;  // block-uniform
+    const bool staged = r1 - r0 <= TILE;  // block-uniform
     int c = 0, s = 0, e = 0;
     double2 p = make_double2(0.0, 0.0);
     if (i < n) {
@@ -579,10 +603,64 @@ k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
             s_pos[k - r0] = pos_in[k];
             s_m[k - r0] = m[k];
         }
-        __syncthreads();
     }
-    if (i >= n) return;
+    // The 3 x 3 neighbourhood (north_star (c)): the 8 neighbour centres of mass of every cell this
+    // block touches are staged in shared memory ONCE per cell, already shifted by +-side across
+    // the periodic border (:314-329) -- the wrap arithmetic is per (cell, neighbour), not per
+    // (particle, neighbour), and the particles of a cell read the same 8 entries (broadcast).
+    const int cf = cell[b0], ncb = cell[last] - cf + 1;
+    const bool nb_staged = CELLS > 0 && ncb <= CELLS;  // block-uniform
+    if (nb_staged) {
+        for (int idx = threadIdx.x; idx < ncb * 8; idx += TB) {
+            const int cc = cf + (idx >> 3), j = idx & 7;
+            const int dxn = j < 3 ? -1 : j < 5 ? 0 : 1;
+            const int dyn = j < 3 ? j - 1 : j == 3 ? -1 : j == 4 ? 1 : j - 6;
+            const int lrow = cc / g.nc;
+            int nx = cc - lrow * g.nc + dxn;
+            double sx = 0.0, sy = 0.0;
+            if (nx >= g.nc) { sx = g.side; nx -= g.nc; } else if (nx < 0) { sx = -g.side; nx += g.nc; }
+            const int ny = g.row0 + lrow + dyn;
+            if (ny >= g.nc) sy = g.side; else if (ny < 0) sy = -g.side;
+            const int q = (lrow + dyn + 1) * g.nc + nx;
+            const double2 cm = __ldg(&com_xy[q]);
+            s_nxy[idx] = make_double2(sx + cm.x, sy + cm.y);
+            s_nm[idx] = __ldg(&com_m[q]);
+        }
+    }
     double ax = 0.0, ay = 0.0;
+    double2 v = make_double2(0.0, 0.0);
+    if (i < n) v = vel[i];
+    if (staged || nb_staged) __syncthreads();
+    if (i >= n) return;
+    if (nb_staged) {
+        const int base = (c - cf) * 8;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const double2 cm = s_nxy[base + j];
+            accumulate(cm.x - p.x, cm.y - p.y, s_nm[base + j], ax, ay);
+        }
+    } else {
+        const int lrow = c / g.nc;
+        const int gx = c - lrow * g.nc;
+        const int grow = g.row0 + lrow;
+#pragma unroll
+        for (int dxn = -1; dxn <= 1; dxn++) {
+            int nx = gx + dxn;
+            double sx = 0.0;
+            if (nx >= g.nc) { sx = g.side; nx -= g.nc; } else if (nx < 0) { sx = -g.side; nx += g.nc; }
+#pragma unroll
+            for (int dyn = -1; dyn <= 1; dyn++) {
+                if (dxn == 0 && dyn == 0) continue;
+                const int ny = grow + dyn;
+                double sy = 0.0;
+                if (ny >= g.nc) sy = g.side; else if (ny < 0) sy = -g.side;
+                const int q = (lrow + dyn + 1) * g.nc + nx;
+                const double2 cm = __ldg(&com_xy[q]);
+                const double M = __ldg(&com_m[q]);
+                accumulate((sx + cm.x) - p.x, (sy + cm.y) - p.y, M, ax, ay);
+            }
+        }
+    }
     if (staged) {
 #pragma unroll UNROLL
         for (int k = s - r0; k < e - r0; k++) {
@@ -596,33 +674,11 @@ k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
             accumulate(q.x - p.x, q.y - p.y, __ldg(&m[k]), ax, ay);
         }
     }
-    const int lrow = c / g.nc;
-    const int gx = c - lrow * g.nc;
-    const int grow = g.row0 + lrow;
-#pragma unroll
-    for (int dxn = -1; dxn <= 1; dxn++) {
-        int nx = gx + dxn;
-        double sx = 0.0;
-        if (nx >= g.nc) sx = g.side; else if (nx < 0) sx = -g.side;
-        nx = (nx + g.nc) % g.nc;
-#pragma unroll
-        for (int dyn = -1; dyn <= 1; dyn++) {
-            if (dxn == 0 && dyn == 0) continue;
-            int ny = grow + dyn;
-            double sy = 0.0;
-            if (ny >= g.nc) sy = g.side; else if (ny < 0) sy = -g.side;
-            int q = (lrow + dyn + 1) * g.nc + nx;
-            double2 cm = __ldg(&com_xy[q]);
-            double M = __ldg(&com_m[q]);
-            accumulate((sx + cm.x) - p.x, (sy + cm.y) - p.y, M, ax, ay);
-        }
-    }
     ax *= kG;
     ay *= kG;
     if (dbg_acc) dbg_acc[i] = make_double2(ax, ay);
 
     // Particle::updatePositionAndVelocity, serial/parsim.cpp:54-60, same rounding sequence
-    double2 v = vel[i];
     double x = __dadd_rn(p.x, __dadd_rn(__dmul_rn(v.x, kDeltaT),
                                         __dmul_rn(__dmul_rn(__dmul_rn(0.5, ax), kDeltaT), kDeltaT)));
     double y = __dadd_rn(p.y, __dadd_rn(__dmul_rn(v.y, kDeltaT),

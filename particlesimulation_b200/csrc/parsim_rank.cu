@@ -2,6 +2,7 @@
 #include "parsim_rank.cuh"
 
 #include <math.h>
+#include <stdio.h>
 #include <stddef.h>
 #include <string.h>
 
@@ -101,8 +102,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
                                             (int)staging_bytes(c->big_nb * c->big_nb, c->big_cap)));
         }
     }
-    if (const char *e = getenv("PARSIM_FORCE_TB")) c->force_tb = atoi(e) == 128 ? 128 : 256;
-    if (const char *e = getenv("PARSIM_FORCE_UNROLL")) c->force_unroll = atoi(e);
+    if (const char *e = getenv("PARSIM_FORCE_VARIANT")) c->force_variant = atoi(e);
     if (const char *e = getenv("PARSIM_CAPACITY_PCT")) {
         double pct = atof(e);
         if (pct >= 100) c->capacity_factor = pct / 100.0;
@@ -128,7 +128,8 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     PS_ALLOC(c, c->vel_cur, N, false); PS_ALLOC(c, c->vel_alt, N, false);
     if (!c->collide_grid) PS_ALLOC(c, c->posf, N, false);
     else {
-        PS_ALLOC(c, c->big_cells, C, false); PS_ALLOC(c, c->d_big_count, 1, true);
+        PS_ALLOC(c, c->big_cells, C, false); PS_ALLOC(c, c->d_big_count, 2, true);
+        PS_ALLOC(c, c->huge_items, N / kThreads + 2 * C + 16, false);
         PS_ALLOC(c, c->arr_cnt, C, true); PS_ALLOC(c, c->arr_rec, C * kArrSlots, false);
     }
     PS_ALLOC(c, c->m_cur, N, false);   PS_ALLOC(c, c->m_alt, N, false);
@@ -179,7 +180,7 @@ void rank_destroy(Rank *c) {
                     c->dead_start_cur, c->dead_start_alt, c->dead_id_cur, c->dead_id_alt,
                     c->mv_head, c->dm_head, c->mv_next, c->fate, c->grave_pos, c->grave_vel, c->grave_id,
                     c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->posf, c->rec0,
-                    c->big_cells, c->d_big_count, c->arr_cnt, c->arr_rec, c->stage_ids, c->stage[0],
+                    c->big_cells, c->d_big_count, c->huge_items, c->arr_cnt, c->arr_rec, c->stage_ids, c->stage[0],
                     c->stage[1], c->stage[2], c->stage[3], c->stage[4]};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
@@ -415,6 +416,29 @@ int rank_fp64_peak(Rank *c, double *tflops) {
     }
     cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(d);
     *tflops = 2.0 * 8.0 * iters * (double)blocks * kThreads / (best * 1e-3) / 1e12;
+    return 0;
+}
+
+// pair interactions per second of k_pair_peak (the force loop's own instruction mix, no memory)
+int rank_pair_peak(Rank *c, double *pairs_per_s) {
+    PS_CUDA(c, cudaSetDevice(c->device));
+    const int iters = 1 << 13, blocks = 148 * 8;
+    double *d = nullptr;
+    PS_ALLOC(c, d, 1, true);
+    cudaEvent_t a, b;
+    cudaEventCreate(&a); cudaEventCreate(&b);
+    float best = 1e30f;
+    for (int rep = 0; rep < 4; rep++) {
+        cudaEventRecord(a, c->stream);
+        k_pair_peak<<<blocks, kThreads, 0, c->stream>>>(iters, d);
+        cudaEventRecord(b, c->stream);
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));
+        float ms = 0;
+        cudaEventElapsedTime(&ms, a, b);
+        if (rep > 0 && ms < best) best = ms;
+    }
+    *pairs_per_s = 4.0 * iters * (double)blocks * kThreads / (best * 1e-3);
+    cudaEventDestroy(a); cudaEventDestroy(b); cudaFree(d);
     return 0;
 }
 

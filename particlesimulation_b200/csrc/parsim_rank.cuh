@@ -36,8 +36,7 @@ struct Rank {
     Geom g{};
     double thr2 = 0;    // collision threshold on the squared distance (see k_collide_find)
     int com_lanes = 32; // lanes per cell in k_com, from the GLOBAL particles-per-cell
-    int force_unroll = 4;
-    int force_tb = 256; // block size of k_force_integrate (PARSIM_FORCE_TB: 128 | 256)
+    int force_variant = 0; // k_force_integrate instantiation (PARSIM_FORCE_VARIANT; 0: by occupancy)
 
     // particle storage: alive residents [0, n_alive), guests after them until the rebin
     int cap = 0;
@@ -57,7 +56,8 @@ struct Rank {
     // cell-centric collision search (parsim_collide.cuh); off: per-particle all-pairs k_collide_find
     bool collide_grid = false;
     int grid_nb = 1, grid_cap = 0, grid_it = 2, big_nb = 1, big_cap = 0;
-    int *big_cells = nullptr, *d_big_count = nullptr;
+    int *big_cells = nullptr, *d_big_count = nullptr;  // d_big_count[0]: big cells, [1]: huge-cell slices
+    int2 *huge_items = nullptr;
     int *arr_cnt = nullptr;
     ArrRec *arr_rec = nullptr;
     bool have_newcell = false, have_flags = false;
@@ -201,6 +201,7 @@ int rank_reset(Rank *c);
 int rank_download(Rank *c, long long capacity, unsigned *ids, double *x, double *y, double *vx,
                   double *vy, double *m, long long *count_out);
 int rank_fp64_peak(Rank *c, double *tflops);
+int rank_pair_peak(Rank *c, double *pairs_per_s);
 int rank_upload_end(Rank *c);
 int rank_init_device(Rank *c, long seed);
 int rank_stage(Rank *c, int stage);

@@ -115,7 +115,10 @@ static int merge_step(Rank *c, int n_src, int n_surv, bool with_dead) {
     a.cell_out = c->cell_alt;
     // 1 fate + 4 id read per source entry, 40 read + 48 written per survivor, 8 B per tombstone
     PS_LAUNCH(c, K_MOVE, 5.0 * n_src + 88.0 * n_surv + 16.0 * g.ncells + (with_dead ? 8.0 * c->n_tomb : 0.0), "k_move", {
-        switch (c->com_lanes) {
+        // lanes per cell from the CURRENT occupancy (the result does not depend on it)
+        const double occ = (double)n_src / std::max(1, g.ncells);
+        const int lanes = occ <= 6 ? 4 : occ <= 12 ? 8 : occ <= 24 ? 16 : 32;
+        switch (lanes) {
         case 4: launch_move<4>(c, a); break;
         case 8: launch_move<8>(c, a); break;
         case 16: launch_move<16>(c, a); break;
@@ -170,21 +173,21 @@ static int stage_bin_com(Rank *c) {
 
 // stage 1: forces + integration
 static int stage_force(Rank *c) {
-#define PS_FORCE(TB, UN)                                                                            \
-    k_force_integrate<TB, UN><<<grid_for(c->n_alive, TB), TB, 0, c->stream>>>(                      \
+#define PS_FORCE(UN, TILE, CELLS, MINB)                                                             \
+    k_force_integrate<128, UN, TILE, CELLS, MINB><<<grid_for(c->n_alive, 128), 128, 0, c->stream>>>( \
         c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,        \
         c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
         c->dbg_acc)
     PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->n_movers, 0, sizeof(int), c->stream));
+    // variant by current occupancy (cells fill up or empty out as the run goes on)
+    int v = c->force_variant;
+    if (v <= 0) v = (double)c->n_alive < 12.0 * c->g.ncells ? 1 : 2;
     PS_LAUNCH(c, K_FORCE, 81.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate", {
-        const int v = c->force_tb * 100 + c->force_unroll;
         switch (v) {
-        case 12802: PS_FORCE(128, 2); break;
-        case 12804: PS_FORCE(128, 4); break;
-        case 12808: PS_FORCE(128, 8); break;
-        case 25602: PS_FORCE(256, 2); break;
-        case 25608: PS_FORCE(256, 8); break;
-        default: PS_FORCE(256, 4); break;
+        case 1: PS_FORCE(2, 256, 0, 8); break;    // sparse cells: neighbourhood through L1
+        case 3: PS_FORCE(8, 1280, 16, 5); break;  // deep unroll, 96 registers (comparison)
+        case 4: PS_FORCE(4, 256, 0, 8); break;
+        default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
         }
     });
 #undef PS_FORCE
@@ -228,7 +231,7 @@ static int stage_collide(Rank *c) {
         a.partner = c->partner;
         a.collision_pairs = c->opt_stats ? &c->d_ctr->collision_pairs : nullptr;
         a.worklist = c->big_cells; a.work_count = c->d_big_count;
-        PS_CUDA(c, cudaMemsetAsync(c->d_big_count, 0, sizeof(int), c->stream));
+        PS_CUDA(c, cudaMemsetAsync(c->d_big_count, 0, 2 * sizeof(int), c->stream));
         a.nb = c->grid_nb; a.inv_h = c->grid_nb / g.cellw; a.cap = c->grid_cap;
         PS_LAUNCH(c, K_COLLIDE, 29.0 * n_tot + 8.0 * g.ncells, "k_collide_cells", {
             // entries per lane from the CURRENT occupancy (+2 sigma); fuller cells go to k_collide_big
@@ -247,7 +250,10 @@ static int stage_collide(Rank *c) {
         });
         a.nb = c->big_nb; a.inv_h = c->big_nb / g.cellw; a.cap = c->big_cap;
         PS_LAUNCH(c, K_COLLIDE_BIG, 0.0, "k_collide_big",
-                  k_collide_big<<<148, kThreads, staging_bytes(a.nb * a.nb, a.cap), c->stream>>>(a));
+                  k_collide_big<<<148, kThreads, staging_bytes(a.nb * a.nb, a.cap), c->stream>>>(
+                      a, c->huge_items, c->d_big_count + 1));
+        PS_LAUNCH(c, K_COLLIDE_BIG, 0.0, "k_collide_huge",
+                  k_collide_huge<<<148 * 8, kThreads, 0, c->stream>>>(a, c->huge_items, c->d_big_count + 1));
     } else {
         PS_LAUNCH(c, K_COLLIDE, 21.0 * n_tot + 8.0 * g.ncells, "k_collide_find",
                   k_collide_find<<<grid_for(n_tot), kThreads, 0, c->stream>>>(

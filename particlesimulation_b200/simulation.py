@@ -171,6 +171,11 @@ class ParticleSimulation:
         self._check(self.lib.parsim_fp64_peak(self._ctx, C.byref(v)))
         return v.value
 
+    def pair_peak(self):
+        v = C.c_double()
+        self._check(self.lib.parsim_pair_peak(self._ctx, C.byref(v)))
+        return v.value
+
     def simulate(self, n_time_steps):  # serial/parsim.cpp:422
         self._check(self.lib.parsim_run(self._ctx, int(n_time_steps)))
 

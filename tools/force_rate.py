@@ -14,6 +14,8 @@ k = s["kernels"]["force_integrate"]
 ops = 13.0 * s["force_pairs"] + 130.0 * s["alive_particle_steps"]
 print(f"{sys.argv[1:]}: force {k['ms']:.3f} ms, pairs {s['force_pairs']:.3e}, alive-steps {s['alive_particle_steps']:.3e}, "
       f"fp64 lane-ops/s {ops / (k['ms'] * 1e-3):.3e} = {ops / (k['ms'] * 1e-3) / peak:.3f} of FMA-chain peak")
+pp = g.pair_peak()
+print(f"   pair-mix peak {pp:.3e} pairs/s; force kernel {s['force_pairs'] / (k['ms'] * 1e-3):.3e} pairs/s (+ epilogue) = {s['force_pairs'] / (k['ms'] * 1e-3) / pp:.3f}")
 for name, v in s["kernels"].items():
     if v["launches"]:
         print(f"   {name:18s} {v['ms']:9.3f} ms")
