@@ -180,42 +180,24 @@ def main_ours(a):
 
     import numpy as np
     import torch
-    import torch.distributed as dist
 
     from particlesimulation_b200 import ParticleSimulation, _lib
+    from particlesimulation_b200.strips import RankGroup
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
     if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
         os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout (one JSON line only)
-    if world != a.gpus:
-        raise SystemExit(f"--gpus {a.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run")
-    torch.cuda.set_device(local)
+    grp = RankGroup(backend="nccl", expect_world=a.gpus)  # one process per GPU (tests: gloo, tests/test_multi_cpu.py)
+    rank, world, local = grp.rank, grp.world, grp.local
     nccl_id = None
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-        box = [None]
+        blob = None
         if rank == 0:
             buf = (C.c_ubyte * 128)()
             if _lib.load().parsim_nccl_unique_id(buf):
                 raise SystemExit("parsim_nccl_unique_id failed")
-            box[0] = bytes(buf)
-        dist.broadcast_object_list(box, src=0)
-        nccl_id = box[0]
-
-    def barrier():
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-            torch.cuda.synchronize()
-
-    def max_over_ranks(v):
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+            blob = bytes(buf)
+        nccl_id = grp.broadcast_bytes(blob)
+    barrier, max_over_ranks = grp.barrier, grp.max_over_ranks
 
     seed, side, nc, n, nstep, expect = workload_for(a.workload, a.gpus, a.scale)
     kw = dict(rank=rank, nranks=world, device=local, nccl_id=nccl_id) if world > 1 else {}

@@ -74,6 +74,10 @@ int parsim_reset(parsim_ctx *ctx);
 int parsim_host_init_particles(long seed, double side, long ncside, long long n_part,
                                long long first, long long count, double *x, double *y,
                                double *vx, double *vy, double *m);
+/* Row strips (mpi/parsim-mpi.cpp:338-342 splits the grid rows the same way): rank r of nranks
+ * owns grid rows [first_row, first_row + n_rows).  Host arithmetic only, needs no GPU; what
+ * parsim_create / parsim_create_rank use. */
+int parsim_strip_rows(long ncside, int nranks, int rank, long *first_row, long *n_rows);
 /* Device-side restatement of init_particles for seeds >= 0 (uniform stream; xorshift32
  * jump-ahead, bit-identical to serial/parsim.cpp:26-32,:220-232).  Negative seeds
  * (rejection sampling, :34-43) return an error: generate on the host and upload. */

@@ -174,6 +174,15 @@ int parsim_host_init_particles(long seed, double side, long ncside, long long n_
     return 0;
 }
 
+int parsim_strip_rows(long ncside, int nranks, int rank, long *first_row, long *n_rows) {
+    if (ncside < 1 || nranks < 1 || rank < 0 || rank >= nranks || nranks > ncside || !first_row || !n_rows) {
+        g_create_error = "parsim_strip_rows: bad arguments";
+        return 1;
+    }
+    parsim::strip_rows(ncside, nranks, rank, first_row, n_rows);
+    return 0;
+}
+
 int parsim_init_device(parsim_ctx *ctx, long seed) {
     return for_ranks(ctx, [&](Rank *c) { return rank_init_device(c, seed); });
 }

@@ -61,9 +61,10 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     g.cellw = side / (double)ncside;  // side_length / grid_size with grid_size a long, :160
     g.inv_cellw = 1.0 / g.cellw;
     g.nc = (int)ncside;
-    g.row0 = (int)((long long)rank * ncside / nranks);
-    int row1 = (int)((long long)(rank + 1) * ncside / nranks);
-    g.rows = row1 - g.row0;
+    long first_row, n_rows;
+    strip_rows(ncside, nranks, rank, &first_row, &n_rows);
+    g.row0 = (int)first_row;
+    g.rows = (int)n_rows;
     g.ncells = g.rows * g.nc;
     g.cell_base = g.row0 * g.nc;
     c->thr2 = collision_threshold2();

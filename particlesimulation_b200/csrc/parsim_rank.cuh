@@ -191,6 +191,14 @@ inline int check_launch(Rank *c, const char *name) {
         if (check_launch(c, name)) return 1;       \
     } while (0)
 
+// rank r of nranks owns grid rows [r*nc/R, (r+1)*nc/R)
+inline void strip_rows(long ncside, int nranks, int rank, long *first_row, long *n_rows) {
+    const long r0 = (long)((long long)rank * ncside / nranks);
+    const long r1 = (long)((long long)(rank + 1) * ncside / nranks);
+    *first_row = r0;
+    *n_rows = r1 - r0;
+}
+
 int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, int nranks,
                 int device, const unsigned char *nccl_id);
 void rank_destroy(Rank *c);
