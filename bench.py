@@ -33,6 +33,7 @@ WORKLOADS = {
     "config2": (1, 10.0, 100, 1_000_000, 20, 331425),
     "config4w": (3, 354.0, 3536, 100_000_000, 10, 6103556),  # config 4 density, 1e8 per GPU
 }
+CONFIG4_SERIES = {2: (500.0, 5000, 200_000_000), 4: (707.0, 7071, 400_000_000), 8: (1000.0, 10000, 800_000_000)}
 # bounded CPU sample of the same density (ppc = 100, cell = 0.1): config 3 at 1/100 size
 CPU_SAMPLE = {"config3": "7 10 100 1000000 10", "config2": "1 10 100 1000000 20",
               "config4w": "3 35.4 354 1000000 10"}
@@ -46,7 +47,11 @@ def workload_for(name, n_gpus, scale):
         side = side / WORKLOADS[name][2] * nc
         n = max(10, int(n * scale))
         expect = None
-    if n_gpus > 1:
+    if n_gpus > 1 and name == "config4w" and scale == 1.0 and n_gpus in CONFIG4_SERIES:
+        # SURVEY 8(d)'s weak-scaling series; at 8 GPUs it IS BASELINE configs[3]
+        side, nc, n = CONFIG4_SERIES[n_gpus]
+        expect = None
+    elif n_gpus > 1:
         cellw = side / nc
         nc = round(nc * math.sqrt(n_gpus))
         side = nc * cellw

@@ -41,6 +41,22 @@ int parsim_nccl_unique_id(unsigned char id_out[128]);
 int parsim_create_rank(parsim_ctx **out, double side, long ncside, long long n_part,
                        int rank, int nranks, int device, const unsigned char *nccl_unique_id);
 
+/* Explicit strips (equal-PARTICLE strips for clustered inputs -- the case the
+ * reference's report calls "Uneven"): strip r owns grid rows [first_rows[r], first_rows[r+1]),
+ * first_rows[0] = 0, first_rows[nranks] = ncside, strictly increasing.  NULL = equal-row strips.
+ * parsim_balance_rows derives such boundaries from per-row particle counts (prefix sum; every
+ * strip keeps >= 1 row); parsim_host_row_counts ADDS the rows of `count` y coordinates to
+ * row_counts[ncside] with the reference's binning arithmetic (serial/parsim.cpp:268-272).  The
+ * last two are host arithmetic and need no GPU. */
+int parsim_create_rows(parsim_ctx **out, double side, long ncside, long long n_part, int n_gpus,
+                       const long *first_rows);
+int parsim_create_rank_rows(parsim_ctx **out, double side, long ncside, long long n_part,
+                            int rank, int nranks, int device, const unsigned char *nccl_unique_id,
+                            const long *first_rows);
+int parsim_balance_rows(long ncside, int nranks, const long long *row_counts, long *first_rows);
+int parsim_host_row_counts(double side, long ncside, long long count, const double *y,
+                           long long *row_counts);
+
 void parsim_destroy(parsim_ctx *ctx);
 const char *parsim_last_error(const parsim_ctx *ctx); /* ctx may be NULL: last create error */
 
@@ -146,7 +162,12 @@ int parsim_fp64_peak(parsim_ctx *ctx, double *tflops);
  * pair) on register operands: the ceiling the force kernel's inner loop is compared against. */
 int parsim_pair_peak(parsim_ctx *ctx, double *pairs_per_s);
 
-/* options: "keep_initial" (0/1, see parsim_reset), "stats" (0/1), "sync_check" (0/1: synchronise + check after every kernel). */
+/* options: "keep_initial" (0/1, see parsim_reset), "stats" (0/1), "sync_check" (0/1: synchronise +
+ * check after every kernel), "semantics" (0 = the serial program, the default and the parity
+ * target; 1 = the OpenMP variant's list update, openMP/parsim-omp.cpp:248-278, which moves every
+ * leaver -- no strays -- and is otherwise identical; pinned against parsim-omp run with ONE
+ * thread, whose list order is deterministic.  The MPI variant's predicate d^2 <= EPSILON2,
+ * mpi/parsim-mpi.cpp:1015, is not offered: it cannot be built here, so it could not be pinned). */
 int parsim_set_option(parsim_ctx *ctx, const char *name, long long value);
 
 /* Raw device pointer of the CUDA stream the kernels run on (cudaStream_t), for callers that

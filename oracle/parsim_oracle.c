@@ -109,6 +109,7 @@ typedef struct po_sim {
     unsigned char *change_flag;
     /* cellParticles, :201 */
     po_list *lists;
+    int semantics; /* 0 = serial/parsim.cpp (default), 1 = the OpenMP variant's list update */
     long long collisions;
     long long panics;
     /* scratch for checkCollisions */
@@ -145,6 +146,9 @@ po_sim *po_create_empty(double side, long ncside, long long n) {
 }
 
 /* ParticleSimulation ctor, :209-218 */
+/* which variant's list update (phase 3) to restate: 0 = serial (the parity target), 1 = OpenMP */
+void po_set_semantics(struct po_sim *s, int semantics);
+
 po_sim *po_create(long seed, double side, long ncside, long long n) {
     po_sim *s = po_create_empty(side, ncside, n);
     po_init_particles(seed, side, ncside, n, s->x, s->y, s->vx, s->vy, s->m);
@@ -295,10 +299,26 @@ static void po_apply_forces(po_sim *s) {
  * The reference erases at the loop position and then still advances it (:251-253), so the
  * element that slides into the hole is never examined: of a run of consecutive leavers only
  * every other one is moved; the rest stay listed in their old cell for this step. */
+void po_set_semantics(po_sim *s, int semantics) { s->semantics = semantics; }
+
 static void po_update_cell_particles(po_sim *s) {
     for (long long c = 0; c < s->ncells; c++) {
         if (!s->change_flag[c]) continue;
         po_list *l = &s->lists[c];
+        if (s->semantics == 1) {
+            /* openMP/parsim-omp.cpp:248-278 with one thread: collect the leavers in list order,
+             * append them to their new cells, then remove_if every leaver -- no strays */
+            int w = 0;
+            for (int k = 0; k < l->len; k++) {
+                int p = l->items[k];
+                if (s->cell_index[p] != c) po_list_push(&s->lists[s->cell_index[p]], p);
+            }
+            for (int k = 0; k < l->len; k++)
+                if (s->cell_index[l->items[k]] == c) l->items[w++] = l->items[k];
+            l->len = w;
+            s->change_flag[c] = 0;
+            continue;
+        }
         for (int k = 0; k < l->len; k++) {
             int p = l->items[k];
             if (s->cell_index[p] != c) {
@@ -428,6 +448,8 @@ int main(int argc, char **argv) {
     long long n = strtoll(argv[4], NULL, 10);
     long steps = strtol(argv[5], NULL, 10);
     po_sim *s = po_create(seed, side, nc, n);
+    const char *sem = getenv("PARSIM_SEMANTICS");
+    if (sem && strcmp(sem, "omp") == 0) po_set_semantics(s, 1);
     struct timespec t0, t1;
     clock_gettime(CLOCK_MONOTONIC, &t0);
     po_run(s, steps);

@@ -47,6 +47,11 @@ SIGNATURES = {
     "parsim_pair_peak": (C.c_int, [_ctx, _dp]),
     "parsim_host_init_particles": (C.c_int, [C.c_long, C.c_double, C.c_long, C.c_longlong, C.c_longlong,
                                              C.c_longlong, _dp, _dp, _dp, _dp, _dp]),
+    "parsim_create_rows": (C.c_int, [C.POINTER(_ctx), C.c_double, C.c_long, C.c_longlong, C.c_int, C.POINTER(C.c_long)]),
+    "parsim_create_rank_rows": (C.c_int, [C.POINTER(_ctx), C.c_double, C.c_long, C.c_longlong, C.c_int, C.c_int,
+                                          C.c_int, C.POINTER(C.c_ubyte), C.POINTER(C.c_long)]),
+    "parsim_balance_rows": (C.c_int, [C.c_long, C.c_int, C.POINTER(C.c_longlong), C.POINTER(C.c_long)]),
+    "parsim_host_row_counts": (C.c_int, [C.c_double, C.c_long, C.c_longlong, _dp, C.POINTER(C.c_longlong)]),
     "parsim_strip_rows": (C.c_int, [C.c_long, C.c_int, C.c_int, C.POINTER(C.c_long), C.POINTER(C.c_long)]),
     "parsim_init_device": (C.c_int, [_ctx, C.c_long]),
     "parsim_run": (C.c_int, [_ctx, C.c_long]),

@@ -69,13 +69,14 @@ int parsim_nccl_unique_id(unsigned char id_out[128]) {
     return 0;
 }
 
-int parsim_create_rank(parsim_ctx **out, double side, long ncside, long long n_part, int rank,
-                       int nranks, int device, const unsigned char *nccl_unique_id) {
+int parsim_create_rank_rows(parsim_ctx **out, double side, long ncside, long long n_part, int rank,
+                            int nranks, int device, const unsigned char *nccl_unique_id,
+                            const long *first_rows) {
     if (!out) { g_create_error = "out is NULL"; return 1; }
     *out = nullptr;
     std::unique_ptr<parsim_ctx> ctx(new parsim_ctx);
     ctx->ranks.emplace_back(new Rank);
-    if (rank_create(ctx->ranks[0].get(), side, ncside, n_part, rank, nranks, device, nccl_unique_id)) {
+    if (rank_create(ctx->ranks[0].get(), side, ncside, n_part, rank, nranks, device, nccl_unique_id, first_rows)) {
         g_create_error = ctx->ranks[0]->err;
         rank_destroy(ctx->ranks[0].get());
         return 1;
@@ -84,11 +85,17 @@ int parsim_create_rank(parsim_ctx **out, double side, long ncside, long long n_p
     return 0;
 }
 
-int parsim_create(parsim_ctx **out, double side, long ncside, long long n_part, int n_gpus) {
+int parsim_create_rank(parsim_ctx **out, double side, long ncside, long long n_part, int rank,
+                       int nranks, int device, const unsigned char *nccl_unique_id) {
+    return parsim_create_rank_rows(out, side, ncside, n_part, rank, nranks, device, nccl_unique_id, nullptr);
+}
+
+int parsim_create_rows(parsim_ctx **out, double side, long ncside, long long n_part, int n_gpus,
+                       const long *first_rows) {
     if (!out) { g_create_error = "out is NULL"; return 1; }
     *out = nullptr;
     if (n_gpus < 1) { g_create_error = "n_gpus must be >= 1"; return 1; }
-    if (n_gpus == 1) return parsim_create_rank(out, side, ncside, n_part, 0, 1, 0, nullptr);
+    if (n_gpus == 1) return parsim_create_rank_rows(out, side, ncside, n_part, 0, 1, 0, nullptr, first_rows);
     unsigned char id[128];
     if (parsim_nccl_unique_id(id)) return 1;
     std::unique_ptr<parsim_ctx> ctx(new parsim_ctx);
@@ -97,7 +104,7 @@ int parsim_create(parsim_ctx **out, double side, long ncside, long long n_part, 
     int rc = for_ranks(ctx.get(), [&](Rank *c) {
         int r = 0;
         while (ctx->ranks[r].get() != c) r++;
-        return rank_create(c, side, ncside, n_part, r, n_gpus, r, id);
+        return rank_create(c, side, ncside, n_part, r, n_gpus, r, id, first_rows);
     });
     if (rc) {
         g_create_error = ctx->err;
@@ -105,6 +112,35 @@ int parsim_create(parsim_ctx **out, double side, long ncside, long long n_part, 
         return 1;
     }
     *out = ctx.release();
+    return 0;
+}
+
+int parsim_create(parsim_ctx **out, double side, long ncside, long long n_part, int n_gpus) {
+    return parsim_create_rows(out, side, ncside, n_part, n_gpus, nullptr);
+}
+
+int parsim_balance_rows(long ncside, int nranks, const long long *row_counts, long *first_rows) {
+    if (ncside < 1 || nranks < 1 || nranks > ncside || !row_counts || !first_rows) {
+        g_create_error = "parsim_balance_rows: bad arguments";
+        return 1;
+    }
+    for (long r = 0; r < ncside; r++)
+        if (row_counts[r] < 0) { g_create_error = "parsim_balance_rows: negative count"; return 1; }
+    parsim::balance_rows(ncside, nranks, row_counts, first_rows);
+    return 0;
+}
+
+int parsim_host_row_counts(double side, long ncside, long long count, const double *y, long long *row_counts) {
+    if (!(side > 0) || ncside < 1 || count < 0 || !y || !row_counts) {
+        g_create_error = "parsim_host_row_counts: bad arguments";
+        return 1;
+    }
+    const double cellw = side / (double)ncside;  // serial/parsim.cpp:268-272
+    for (long long i = 0; i < count; i++) {
+        long r = (long)(int)(y[i] / cellw);
+        r = r < 0 ? 0 : r >= ncside ? ncside - 1 : r;
+        row_counts[r]++;
+    }
     return 0;
 }
 
@@ -296,6 +332,11 @@ int parsim_set_option(parsim_ctx *ctx, const char *name, long long value) {
         if (n == "stats") c->opt_stats = value != 0;
         else if (n == "sync_check") c->opt_sync_check = value != 0;
         else if (n == "keep_initial") c->opt_keep_initial = value != 0;
+        else if (n == "semantics") {
+            if (value != 0 && value != 1) return ctx_fail(ctx, "semantics: 0 = serial (default), 1 = omp");
+            if (c->next_stage != 0) return ctx_fail(ctx, "semantics cannot change in the middle of a step");
+            c->g.no_strays = (int)value;
+        }
         else if (n == "debug_acc") {
             if (value && !c->dbg_acc) {
                 cudaSetDevice(c->device);

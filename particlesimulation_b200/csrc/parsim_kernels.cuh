@@ -38,6 +38,8 @@ struct Geom {
     int rows;      // rows in this strip
     int ncells;    // rows * nc
     int cell_base; // row0 * nc : global cell index = local + cell_base
+    int no_strays; // 1 = list update of the OpenMP variant (openMP/parsim-omp.cpp:248-278): every
+                   // leaver is moved; 0 = the serial erase-then-increment behaviour (:234-259)
 };
 
 struct Counters {  // one per context, device memory, copied to the host once per step
@@ -740,7 +742,7 @@ k_classify(Geom g, const int *__restrict__ mover_list, const int *__restrict__ n
         const int dstg = newcell[i];
         // length of the run of consecutive leavers that ends just before i
         int run = 0;
-        const int s = cell_start[c];
+        const int s = g.no_strays ? i : cell_start[c];
         for (int u = i - 1; u >= s; u--) {
             if (newcell[u] == cg) break;
             if (tombstone_between(dead_start, dead_id, c, id[u], id[u + 1])) break;

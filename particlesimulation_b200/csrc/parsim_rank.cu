@@ -39,7 +39,7 @@ static double collision_threshold2() {
 }
 
 int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, int nranks,
-                int device, const unsigned char *nccl_id) {
+                int device, const unsigned char *nccl_id, const long *first_rows) {
     if (!(side > 0)) return c->fail("side_length must be > 0");
     if (ncside < 1) return c->fail("grid_size must be >= 1");
     if (n_part < 1) return c->fail("n_particles must be >= 1");
@@ -58,11 +58,20 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
 
     Geom &g = c->g;
     g.side = side;
+    g.no_strays = 0;
     g.cellw = side / (double)ncside;  // side_length / grid_size with grid_size a long, :160
     g.inv_cellw = 1.0 / g.cellw;
     g.nc = (int)ncside;
     long first_row, n_rows;
-    strip_rows(ncside, nranks, rank, &first_row, &n_rows);
+    if (first_rows) {
+        if (first_rows[0] != 0 || first_rows[nranks] != ncside) return c->fail("strip rows must cover [0, grid_size)");
+        for (int r = 0; r < nranks; r++)
+            if (first_rows[r + 1] <= first_rows[r]) return c->fail("every strip needs at least one row, in rank order");
+        first_row = first_rows[rank];
+        n_rows = first_rows[rank + 1] - first_row;
+    } else {
+        strip_rows(ncside, nranks, rank, &first_row, &n_rows);
+    }
     g.row0 = (int)first_row;
     g.rows = (int)n_rows;
     g.ncells = g.rows * g.nc;

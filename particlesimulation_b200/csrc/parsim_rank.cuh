@@ -199,8 +199,34 @@ inline void strip_rows(long ncside, int nranks, int rank, long *first_row, long 
     *n_rows = r1 - r0;
 }
 
+// Equal-PARTICLE strips: strip boundaries from the prefix sum of the per-row
+// particle counts, so that clustered inputs (negative seeds: normal around the centre) load the
+// GPUs evenly.  first_rows[0] = 0 < first_rows[1] < ... < first_rows[nranks] = ncside; every strip
+// gets at least one row.  Boundary r is the row where the running count first reaches r/R of
+// the total, moved as little as needed to keep the strips non-empty.
+inline void balance_rows(long ncside, int nranks, const long long *row_counts, long *first_rows) {
+    long long total = 0;
+    for (long r = 0; r < ncside; r++) total += row_counts[r];
+    first_rows[0] = 0;
+    long row = 0;
+    long long run = 0;
+    for (int k = 1; k < nranks; k++) {
+        // smallest row count whose prefix sum is >= k/R of the total
+        const long long want = (total * k + nranks - 1) / nranks;
+        while (row < ncside && run < want) run += row_counts[row++];
+        long b = row;
+        const long lo = first_rows[k - 1] + 1, hi = ncside - (nranks - k);
+        if (b < lo) b = lo;
+        if (b > hi) b = hi;
+        while (row < b) run += row_counts[row++];
+        first_rows[k] = b;
+    }
+    first_rows[nranks] = ncside;
+}
+
+// first_rows == nullptr: equal-row strips (strip_rows)
 int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, int nranks,
-                int device, const unsigned char *nccl_id);
+                int device, const unsigned char *nccl_id, const long *first_rows = nullptr);
 void rank_destroy(Rank *c);
 int rank_upload_begin(Rank *c);
 int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long count, const double *x,

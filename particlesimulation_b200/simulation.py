@@ -98,18 +98,34 @@ class ParticleSimulation:
     """ParticleSimulation(seed, side, ncside, n_part) -> .simulate(n_steps) -> .print_result()."""
 
     def __init__(self, seed, side, ncside, n_part, n_gpus=1, arrays=None, rank=None, nranks=1,
-                 device=0, nccl_id=None, device_init=False, options=None, upload=True):
+                 device=0, nccl_id=None, device_init=False, options=None, upload=True, first_rows=None):
+        """`first_rows` (n_strips + 1 row indices, or "balanced"): explicit / equal-particle strips
+        instead of equal-row strips (multi-GPU only; "balanced" needs host arrays or a host init)."""
         self.lib = _lib.load()
         self.side, self.ncside, self.n_part = float(side), int(ncside), int(n_part)
         self._ctx = C.c_void_p()
+        n_strips = n_gpus if rank is None else nranks
+        if isinstance(first_rows, str):
+            if first_rows != "balanced":
+                raise ValueError("first_rows must be a sequence or 'balanced'")
+            if arrays is None:
+                arrays = init_particles(seed, side, ncside, n_part)
+            from . import strips
+            first_rows = strips.balanced_rows(strips.row_counts(arrays[1], side, ncside), n_strips)
+        rows = None
+        if first_rows is not None:
+            if len(first_rows) != n_strips + 1:
+                raise ValueError("first_rows needs n_strips + 1 entries")
+            rows = (C.c_long * (n_strips + 1))(*[int(r) for r in first_rows])
+        self.first_rows = None if first_rows is None else [int(r) for r in first_rows]
         if rank is None:
-            rc = self.lib.parsim_create(C.byref(self._ctx), self.side, self.ncside, self.n_part, n_gpus)
+            rc = self.lib.parsim_create_rows(C.byref(self._ctx), self.side, self.ncside, self.n_part, n_gpus, rows)
         else:
             idbuf = None
             if nccl_id is not None:
                 idbuf = (C.c_ubyte * 128).from_buffer_copy(bytes(nccl_id))
-            rc = self.lib.parsim_create_rank(C.byref(self._ctx), self.side, self.ncside, self.n_part,
-                                             rank, nranks, device, idbuf)
+            rc = self.lib.parsim_create_rank_rows(C.byref(self._ctx), self.side, self.ncside, self.n_part,
+                                                  rank, nranks, device, idbuf, rows)
         if rc:
             self._ctx = C.c_void_p()
             raise ParsimError(self.lib.parsim_last_error(None).decode())

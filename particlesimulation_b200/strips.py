@@ -24,10 +24,39 @@ def strip_rows(ncside, nranks, rank):
     return r0, r1 - r0
 
 
-def strip_of_row(row, ncside, nranks):
-    """Owner of a grid row: the unique r with r*nc//R <= row < (r+1)*nc//R."""
-    first = np.array([r * int(ncside) // int(nranks) for r in range(int(nranks))], dtype=np.int64)
+def strip_of_row(row, ncside, nranks, first_rows=None):
+    """Owner of a grid row: the unique r with first_rows[r] <= row < first_rows[r+1]
+    (equal-row strips, r*nc//R, when first_rows is None)."""
+    if first_rows is None:
+        first = np.array([r * int(ncside) // int(nranks) for r in range(int(nranks))], dtype=np.int64)
+    else:
+        first = np.asarray(first_rows[:-1], dtype=np.int64)
     return np.searchsorted(first, np.asarray(row, dtype=np.int64), side="right") - 1
+
+
+def row_counts(y, side, ncside):
+    """Particles per grid row (what parsim_host_row_counts accumulates)."""
+    return np.bincount(cell_row(y, side, ncside), minlength=int(ncside)).astype(np.int64)
+
+
+def balanced_rows(counts, nranks):
+    """Equal-PARTICLE strips: boundary k is the row where the running count first
+    reaches k/R of the total, moved as little as needed so that every strip keeps >= 1 row.
+    Returns nranks + 1 row indices; same arithmetic as parsim_balance_rows (csrc/parsim_rank.cuh)."""
+    counts = np.asarray(counts, dtype=np.int64)
+    nc, R = len(counts), int(nranks)
+    if not 1 <= R <= nc:
+        raise ValueError("need 1 <= nranks <= rows")
+    prefix = np.concatenate([[0], np.cumsum(counts)])  # prefix[r] = particles in rows < r
+    total = int(prefix[-1])
+    first = [0]
+    for k in range(1, R):
+        want = (total * k + R - 1) // R
+        b = int(np.searchsorted(prefix, want, side="left"))  # smallest r with prefix[r] >= want
+        b = min(max(b, first[-1] + 1), nc - (R - k))
+        first.append(b)
+    first.append(nc)
+    return first
 
 
 def cell_row(y, side, ncside):
@@ -38,15 +67,15 @@ def cell_row(y, side, ncside):
     return np.clip(row, 0, int(ncside) - 1)
 
 
-def strip_of_particles(y, side, ncside, nranks):
+def strip_of_particles(y, side, ncside, nranks, first_rows=None):
     """Rank on which each particle is binned at step 0."""
-    return strip_of_row(cell_row(y, side, ncside), int(ncside), int(nranks))
+    return strip_of_row(cell_row(y, side, ncside), int(ncside), int(nranks), first_rows)
 
 
-def select_strip(rank, nranks, side, ncside, x, y, vx, vy, m):
+def select_strip(rank, nranks, side, ncside, x, y, vx, vy, m, first_rows=None):
     """ids (ascending) and state of the particles that start on `rank`'s strip -- what a launcher
     hands to `parsim_upload_strip*` when every rank generates the full seeded stream on the host."""
-    owner = strip_of_particles(y, side, ncside, nranks)
+    owner = strip_of_particles(y, side, ncside, nranks, first_rows)
     ids = np.nonzero(owner == rank)[0].astype(np.uint32)
     return (ids,) + tuple(np.ascontiguousarray(np.asarray(a)[ids]) for a in (x, y, vx, vy, m))
 

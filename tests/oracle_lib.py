@@ -82,6 +82,7 @@ def _load_oracle():
     lib.po_create_from.restype = C.c_void_p
     lib.po_create_from.argtypes = [C.c_double, C.c_long, C.c_longlong, _dp, _dp, _dp, _dp, _dp]
     lib.po_destroy.argtypes = [C.c_void_p]
+    lib.po_set_semantics.argtypes = [C.c_void_p, C.c_int]
     lib.po_phase.argtypes = [C.c_void_p, C.c_int]
     lib.po_step.argtypes = [C.c_void_p]
     lib.po_run.argtypes = [C.c_void_p, C.c_long]
@@ -129,9 +130,12 @@ def have_ref():
     return os.path.exists(REF_SO)
 
 
-def oracle_sim(seed, side, ncside, n_part):
+def oracle_sim(seed, side, ncside, n_part, semantics=0):
+    """semantics: 0 = serial/parsim.cpp (the parity target), 1 = the OpenMP variant's list update"""
     lib = oracle_lib()
     h = lib.po_create(int(seed), float(side), int(ncside), int(n_part))
+    if semantics:
+        lib.po_set_semantics(h, int(semantics))
     return _Sim(lib, "po_", h, int(n_part), int(ncside) ** 2)
 
 

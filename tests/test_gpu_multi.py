@@ -70,6 +70,61 @@ def test_far_jumps_cross_strips(n_gpus):
     one.close(); many.close()
 
 
+@pytest.mark.parametrize("n_gpus", [2, 3, 4, 8])
+@pytest.mark.parametrize("case", [(-7, 10, 50, 20000, 5), (-3, 4, 40, 60000, 4), (5, 1, 20, 20000, 3)],
+                         ids=lambda c: " ".join(map(str, c)))
+def test_equal_particle_strips_match_single_gpu(case, n_gpus):
+    """strips cut by particle count (clustered, negative-seed inputs) instead of by
+    row count -- same bits as one GPU, default strip capacity, and an even load."""
+    from particlesimulation_b200 import strips
+    from particlesimulation_b200.simulation import init_particles
+    seed, side, nc, n, steps = case
+    if ngpu() < n_gpus:
+        pytest.skip(f"needs {n_gpus} GPUs")
+    os.environ.pop("PARSIM_CAPACITY_PCT", None)  # balanced strips must fit the default capacity
+    arrs = init_particles(seed, side, nc, n)
+    first = strips.balanced_rows(strips.row_counts(arrs[1], side, nc), n_gpus)
+    owner = strips.strip_of_particles(arrs[1], side, nc, n_gpus, first)
+    load = np.bincount(owner, minlength=n_gpus)
+    rows_max = int(strips.row_counts(arrs[1], side, nc).max())
+    assert load.max() - load.min() <= 2 * rows_max  # within one row of particles of each other
+    one = ParticleSimulation(seed, side, nc, n, arrays=arrs)
+    many = ParticleSimulation(seed, side, nc, n, arrays=arrs, n_gpus=n_gpus, first_rows="balanced")
+    assert many.first_rows == first
+    for t in range(steps):
+        one.simulate(1)
+        many.simulate(1)
+        assert one.result() == many.result(), f"step {t}"
+    a, b = one.dump(), many.dump()
+    assert b["owned"].all()
+    for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+        assert np.array_equal(a[k], b[k]), k
+    one.close(); many.close()
+
+
+def test_cli_balanced_strips_match_single_gpu():
+    if ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    exe = os.path.join(ROOT, "particlesimulation_b200", "parsim")
+    args = ["-7", "10", "50", "200000", "10"]  # golden: 5.957 6.317 / 46580 (tests/golden/reference_runs.jsonl)
+    one = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
+    env = dict(os.environ, PARSIM_NGPU=str(min(4, ngpu())), PARSIM_BALANCE="1")
+    env.pop("PARSIM_CAPACITY_PCT", None)
+    many = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300, env=env)
+    assert one.returncode == 0 and many.returncode == 0, one.stderr + many.stderr
+    assert one.stdout == many.stdout
+    assert one.stdout.split() == ["5.957", "6.317", "46580"]
+
+
+def test_bad_strip_rows_are_rejected():
+    if ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    from particlesimulation_b200.simulation import ParsimError
+    for rows in ([0, 5, 5, 10][:3], [0, 0, 10], [1, 5, 10], [0, 5, 9]):
+        with pytest.raises((ParsimError, ValueError)):
+            ParticleSimulation(1, 1.0, 10, 100, n_gpus=2, first_rows=rows)
+
+
 @pytest.mark.parametrize("n_gpus", [2, 4, 8])
 def test_bench_under_torchrun(n_gpus):
     if ngpu() < n_gpus:

@@ -121,6 +121,51 @@ def test_committed_reference_runs(r):
     g.close()
 
 
+OMP_RUNS = [json.loads(l) for l in open(os.path.join(ROOT, "tests", "golden", "omp_runs.jsonl"))]
+
+
+@pytest.mark.parametrize("r", OMP_RUNS, ids=lambda r: "omp " + " ".join(r["args"]))
+def test_omp_semantics_match_the_one_thread_openmp_binary(r):
+    """Option semantics = 1: every leaver is moved, no strays -- the OpenMP
+    variant's list update; counts pinned by parsim-omp with one thread."""
+    seed, side, nc, n, steps = int(r["args"][0]), float(r["args"][1]), int(r["args"][2]), int(r["args"][3]), int(r["args"][4])
+    g = ParticleSimulation(seed, side, nc, n, options={"semantics": 1})
+    g.simulate(steps)
+    x0, y0, col = g.result()
+    assert col == r["collisions"]
+    assert abs(x0 - float(r["x0"])) <= 1e-3 and abs(y0 - float(r["y0"])) <= 1e-3
+    assert g.stats()["strays"] == 0
+    g.close()
+
+
+@pytest.mark.parametrize("case", [(1, 10, 100, 100000, 4), (5, 1, 20, 20000, 4), (-10, 3, 3, 100, 10)],
+                         ids=lambda c: "omp " + " ".join(map(str, c)))
+def test_omp_semantics_lists_match_oracle(case):
+    seed, side, nc, n, steps = case
+    o = ol.oracle_sim(seed, side, nc, n, semantics=1)
+    g = ParticleSimulation(seed, side, nc, n, options={"semantics": 1})
+    for t in range(steps):
+        for ph in range(4):
+            o.phase(ph)
+        for st in range(3):
+            g.debug_stage(st)
+        assert gpu_lists(g.dump(), o.ncells) == oracle_lists_alive(o), f"step {t}"
+        o.phase(4)
+        g.debug_stage(3)
+        assert g.result()[2] == o.collisions, f"step {t}"
+        assert np.array_equal(g.dump()["alive"], o.particles()["alive"]), f"step {t}"
+    g.close()
+
+
+def test_cli_semantics_switch():
+    cli = os.path.join(ROOT, "particlesimulation_b200", "parsim")
+    args = "1 10 100 100000 5".split()
+    p = subprocess.run([cli] + args, capture_output=True, text=True, env=dict(os.environ, PARSIM_SEMANTICS="omp"))
+    assert p.returncode == 0 and p.stdout == "7.872 0.263\n5225\n", p.stdout + p.stderr
+    p = subprocess.run([cli] + args, capture_output=True, text=True, env=dict(os.environ, PARSIM_SEMANTICS="mpi"))
+    assert p.returncode == 1 and p.stderr.startswith("Error: ")
+
+
 def test_run_is_deterministic_and_matches_staged():
     args = (1, 10, 100, 200000)
     a = ParticleSimulation(*args); a.simulate(5)
@@ -196,6 +241,38 @@ def test_cli_matches_reference_output():
         assert p.returncode == 0, p.stderr
         assert p.stdout == exp
         assert p.stderr.strip().endswith("s")
+
+
+@pytest.mark.parametrize("args", ["1 2 3 10 3", "5 1 20 2000 3", "-10 3 3 100 4"])
+def test_cli_trace_matches_oracle(args, tmp_path):
+    """PARSIM_TRACE writes the dump the reference keeps commented out in simulate()
+    (serial/parsim.cpp:424-431,:442-446); the same text generated from the oracle's state must
+    match line for line (3 decimals; dead particles print mass 0 and their frozen state)."""
+    seed, side, nc, n, steps = args.split()
+    seed, side, nc, n, steps = int(seed), float(side), int(nc), int(n), int(steps)
+    cli = os.path.join(ROOT, "particlesimulation_b200", "parsim")
+    path = tmp_path / "trace.txt"
+    plain = subprocess.run([cli] + args.split(), capture_output=True, text=True)
+    p = subprocess.run([cli] + args.split(), capture_output=True, text=True,
+                       env=dict(os.environ, PARSIM_TRACE=str(path)))
+    assert p.returncode == 0, p.stderr
+    assert p.stdout == plain.stdout  # the trace does not disturb the two result lines
+    o = ol.oracle_sim(seed, side, nc, n)
+
+    def particles():
+        st = o.particles()
+        return ["Particle %d: mass=%.3f x=%.3f y=%.3f vx=%.3f vy=%.3f" % (j, st["m"][j] if st["alive"][j] else 0.0,
+                st["x"][j], st["y"][j], st["vx"][j], st["vy"][j]) for j in range(n)]
+
+    want = particles() + ["Cell %d x: 0.000 y: 0.000 m: 0.000" % j for j in range(nc * nc)]
+    for t in range(steps):
+        o.step()
+        want += ["t=%d" % t] + particles()
+    o.close()
+    got = path.read_text().splitlines()
+    assert len(got) == len(want)
+    bad = [(a, b) for a, b in zip(got, want) if a != b]
+    assert not bad, bad[:3]
 
 
 @pytest.mark.parametrize("args", [(1, 2, 3, 10), (7, 100, 1000, 300000), (0, 5, 7, 1000), (123456, 10, 100, 1 << 20)])

@@ -62,6 +62,50 @@ def test_strip_rows_rejects_bad_arguments():
         strips.strip_rows(4, 2, -1)
 
 
+@pytest.mark.parametrize("nc,nranks", [(10, 3), (100, 8), (7, 7), (50, 2), (1000, 8), (5, 4), (3536, 8)])
+def test_balanced_rows_c_and_python_agree(nc, nranks):
+    """Equal-particle strips: the C ABI's boundaries == the launcher's, they tile the
+    grid with >= 1 row each, and each boundary sits where the prefix sum crosses k/R of the total."""
+    lib = _lib.load()
+    rng = np.random.default_rng(nc * 31 + nranks)
+    x = np.arange(nc)
+    shapes = [rng.integers(0, 100, nc), np.zeros(nc), rng.integers(0, 3, nc) * rng.integers(0, 1000, nc),
+              np.round(1e4 * np.exp(-0.5 * ((x - nc / 2) / (0.15 * nc)) ** 2)), np.r_[np.zeros(nc - 1), 1000.0]]
+    for cnt in shapes:
+        cnt = np.ascontiguousarray(cnt, dtype=np.int64)
+        py = strips.balanced_rows(cnt, nranks)
+        out = (C.c_long * (nranks + 1))()
+        assert lib.parsim_balance_rows(nc, nranks, cnt.ctypes.data_as(C.POINTER(C.c_longlong)), out) == 0
+        assert list(out) == py
+        assert py[0] == 0 and py[-1] == nc and all(b > a for a, b in zip(py, py[1:]))
+        total, prefix = int(cnt.sum()), np.concatenate([[0], np.cumsum(cnt)])
+        for k in range(1, nranks):
+            want = -(-total * k // nranks)
+            free = py[k - 1] + 1 < py[k] < nc - (nranks - k)  # not pinned by the one-row minimum
+            if free:
+                assert prefix[py[k]] >= want and prefix[py[k] - 1] < want
+
+
+def test_balanced_rows_even_out_a_normal_cloud():
+    """Negative seeds draw a normal cloud (sigma = 0.15 side): equal rows give the middle strips
+    several times the load of the outer ones, equal-particle strips stay within one row's worth."""
+    seed, side, nc, n, R = -4, 10.0, 200, 100000, 8
+    x, y, vx, vy, m = init_particles(seed, side, nc, n)
+    cnt = strips.row_counts(y, side, nc)
+    acc = np.zeros(nc, dtype=np.int64)
+    lib = _lib.load()
+    assert lib.parsim_host_row_counts(side, nc, n, y.ctypes.data_as(C.POINTER(C.c_double)),
+                                      acc.ctypes.data_as(C.POINTER(C.c_longlong))) == 0
+    assert np.array_equal(acc, cnt) and cnt.sum() == n
+    eq = np.bincount(strips.strip_of_particles(y, side, nc, R), minlength=R)
+    first = strips.balanced_rows(cnt, R)
+    bal = np.bincount(strips.strip_of_particles(y, side, nc, R, first), minlength=R)
+    assert eq.max() > 3 * eq.min()
+    assert bal.max() - bal.min() <= 2 * cnt.max()
+    parts = [strips.select_strip(r, R, side, nc, x, y, vx, vy, m, first) for r in range(R)]
+    assert [len(p[0]) for p in parts] == bal.tolist()
+
+
 def test_cell_row_matches_oracle_binning():
     """The launcher's strip choice uses the same row as the oracle's (= the reference's) binning."""
     import oracle_lib

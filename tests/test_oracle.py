@@ -63,6 +63,27 @@ def test_committed_reference_runs(r):
     assert s.collisions == r["collisions"]
 
 
+OMP_RUNS = [json.loads(l) for l in open(os.path.join(HERE, "golden", "omp_runs.jsonl"))]
+
+
+@pytest.mark.parametrize("r", [r for r in OMP_RUNS if r["seconds"] < 3.0], ids=lambda r: " ".join(r["args"]))
+def test_omp_semantics_match_the_one_thread_openmp_binary(r):
+    """the oracle's `semantics = 1` (no strays, openMP/parsim-omp.cpp:248-278) is
+    pinned by the unmodified OpenMP binary run with one thread (tests/golden/make_omp_goldens.py)."""
+    seed, side, nc, n, steps = int(r["args"][0]), float(r["args"][1]), int(r["args"][2]), int(r["args"][3]), int(r["args"][4])
+    s = ol.oracle_sim(seed, side, nc, n, semantics=1)
+    s.run(steps)
+    p = s.particles()
+    assert f"{p['x'][0]:.3f}" == r["x0"] and f"{p['y'][0]:.3f}" == r["y0"]
+    assert s.collisions == r["collisions"]
+
+
+def test_omp_semantics_differ_from_serial_where_strays_exist():
+    a, b = ol.oracle_sim(1, 10, 100, 100000), ol.oracle_sim(1, 10, 100, 100000, semantics=1)
+    a.run(5); b.run(5)
+    assert (a.collisions, b.collisions) == (5226, 5225)
+
+
 PHASE_CASES = [(1, 2, 3, 10, 3), (-10, 3, 3, 100, 10), (1, 10, 100, 100000, 3), (5, 1, 20, 20000, 3),
                (5893, 0.05, 3, 10, 10), (-7, 10, 50, 20000, 4), (3, 1, 1, 50, 3), (3, 1, 2, 200, 3)]
 
