@@ -189,8 +189,14 @@ def main_ours(a):
     from particlesimulation_b200 import ParticleSimulation, _lib
     from particlesimulation_b200.strips import RankGroup
 
-    if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-        os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout (one JSON line only)
+    # stdout carries ONE JSON line: NCCL's banner / warnings (stdout by default) go to stderr, and
+    # fd 1 itself points at stderr until the line is printed, whatever else a library writes
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+    if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+        os.environ["NCCL_DEBUG"] = "WARN"  # NCCL_DEBUG_FILE is honoured only above the VERSION level
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
     grp = RankGroup(backend="nccl", expect_world=a.gpus)  # one process per GPU (tests: gloo, tests/test_multi_cpu.py)
     rank, world, local = grp.rank, grp.world, grp.local
     nccl_id = None
@@ -266,6 +272,8 @@ def main_ours(a):
 
     if rank != 0:
         return
+    sys.stdout.flush()
+    os.dup2(real_stdout, 1)
     # ---- roofline of the dominant kernel + the per-kernel table -----------------------------
     hbm_peak, peak_src = peaks()
     kern = {k: v for k, v in st["kernels"].items() if v["launches"] > 0}

@@ -4,6 +4,8 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <dlfcn.h>
+#include <stdlib.h>
+#include <strings.h>
 
 #include <string>
 
@@ -30,6 +32,14 @@ struct NcclApi {
 
     bool load() {
         if (lib) return true;
+        // NCCL writes its version banner / warnings to STDOUT unless told otherwise; stdout of the
+        // drop-in CLI is exactly two lines (serial/parsim.cpp:450-453), so send them to stderr
+        // (read by NCCL at its first call; an explicit NCCL_DEBUG_FILE of the user wins)
+        setenv("NCCL_DEBUG_FILE", "/dev/stderr", 0);
+        // NCCL honours NCCL_DEBUG_FILE only above the VERSION level: WARN prints the same banner
+        // plus warnings, into the file
+        if (const char *lvl = getenv("NCCL_DEBUG"))
+            if (strcasecmp(lvl, "VERSION") == 0) setenv("NCCL_DEBUG", "WARN", 1);
         const char *names[] = {"libnccl.so.2", "libnccl.so", nullptr};
         for (int i = 0; names[i] && !lib; i++) lib = dlopen(names[i], RTLD_NOW | RTLD_GLOBAL);
         if (!lib) {
