@@ -23,6 +23,12 @@
 namespace parsim {
 
 constexpr int kFarCap = 4096;  // far records per strip per exchange (see exchange_records)
+// One NCCL round per exchange: every message is a header record (the count) followed by a fixed
+// "eager" number of record slots, so the receiver needs no count before it posts the receive.
+// Counts above the eager size (rare: about 1e3 records cross a strip border per step at 1e8
+// particles per GPU) travel in a second round that both sides know to post from the header.
+constexpr int kEagerRecs = 8192;  // neighbour messages: 512 KB + header
+constexpr int kFarEager = 32;     // all-gathered far records per strip in the first round
 constexpr int kRec = 8;  // doubles per migrant record: x y vx vy m (id|src<<32) (cell|kind<<32) pad
 
 __device__ __forceinline__ double pack_u64(unsigned long long v) { return __longlong_as_double((long long)v); }
@@ -45,15 +51,24 @@ __device__ __forceinline__ void write_record(double *buf, int slot, double2 p, d
     r[7] = 0.0;
 }
 
+// counts into the header record of the three send buffers
+__global__ void k_seal_headers(const int *__restrict__ hdr, double *send_up, double *send_dn, double *send_far) {
+    if (threadIdx.x == 0) send_up[0] = pack_u64((unsigned long long)(unsigned)hdr[0]);
+    if (threadIdx.x == 1) send_dn[0] = pack_u64((unsigned long long)(unsigned)hdr[1]);
+    if (threadIdx.x == 2) send_far[0] = pack_u64((unsigned long long)(unsigned)hdr[2]);
+}
+
 // hdr[0] / hdr[1] = records for the strip above / below
-__global__ void k_pack_emigrants(Geom g, int n, int mig_cap, const unsigned char *__restrict__ flags,
+// (over the short list k_classify wrote: hdr[3] entries)
+__global__ void k_pack_emigrants(Geom g, const int *__restrict__ list, int list_cap, int mig_cap,
                                  const double2 *__restrict__ pos, const double2 *__restrict__ vel,
                                  const double *__restrict__ m, const unsigned *__restrict__ id,
                                  const int *__restrict__ cell, const int *__restrict__ newcell,
                                  double *send_up, double *send_dn, double *send_far, int *hdr,
                                  Counters *ctr) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n || !(flags[i] & F_EMIGRANT)) return;
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= min(hdr[3], list_cap)) return;
+    const int i = list[t];
     int dir = strip_dir(g, newcell[i]);
     if (dir < 0) dir = 2;  // far
     int slot = atomicAdd(&hdr[dir], 1);
@@ -100,15 +115,16 @@ __global__ void k_unpack_guests(Geom g, int n_rec, const double *__restrict__ re
 
 // after the collisions: strays that survived but now lie in another strip (kind 0) and
 // tombstones of particles that died here but lie in another strip (kind 1)
-__global__ void k_pack_late(Geom g, int n, int mig_cap, const unsigned char *__restrict__ fate,
-                            const double2 *__restrict__ pos,
+// (over the short list k_resolve wrote: hdr[3] entries)
+__global__ void k_pack_late(Geom g, const int *__restrict__ list, int list_cap, int mig_cap,
+                            const unsigned char *__restrict__ fate, const double2 *__restrict__ pos,
                             const double2 *__restrict__ vel, const double *__restrict__ m,
                             const unsigned *__restrict__ id, const int *__restrict__ newcell,
                             double *send_up, double *send_dn, double *send_far, int *hdr, Counters *ctr) {
-    int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= min(hdr[3], list_cap)) return;
+    const int i = list[t];
     const int ft = fate[i];
-    if (ft != FATE_LEFT_ALIVE && ft != FATE_LEFT_DEAD) return;
     int dir = strip_dir(g, newcell[i]);
     if (dir < 0) dir = 2;  // far
     int slot = atomicAdd(&hdr[dir], 1);
@@ -168,7 +184,7 @@ inline int exchange_create(Rank *c, const unsigned char *nccl_id) {
     PS_NCCL(c, api.CommInitRank(&c->comm.comm, c->nranks, id, c->rank));
     c->up = (c->rank - 1 + c->nranks) % c->nranks;
     c->dn = (c->rank + 1) % c->nranks;
-    const size_t rec = (size_t)c->mig_cap * kRec;
+    const size_t rec = ((size_t)std::max(c->mig_cap, kEagerRecs) + 1) * kRec;  // + header record
     for (int d = 0; d < 2; d++) {
         if (cudaMalloc((void **)&c->mig_send[d], rec * sizeof(double)) != cudaSuccess ||
             cudaMalloc((void **)&c->mig_recv[d], rec * sizeof(double)) != cudaSuccess)
@@ -179,13 +195,21 @@ inline int exchange_create(Rank *c, const unsigned char *nccl_id) {
         return c->fail("cudaMalloc failed");
     c->mig_hdr_recv = c->mig_hdr_send + 4;
     const size_t far = (size_t)kFarCap * kRec;
-    if (cudaMalloc((void **)&c->far_send, far * sizeof(double)) != cudaSuccess ||
+    if (cudaMalloc((void **)&c->far_send, (far + kRec) * sizeof(double)) != cudaSuccess ||
         cudaMalloc((void **)&c->far_recv, far * c->nranks * sizeof(double)) != cudaSuccess ||
-        cudaMalloc((void **)&c->far_cnt_recv, c->nranks * sizeof(int)) != cudaSuccess)
+        cudaMalloc((void **)&c->far_eager_recv, (size_t)(1 + kFarEager) * kRec * c->nranks * sizeof(double)) != cudaSuccess)
         return c->fail("cudaMalloc of far-record buffers failed");
+    for (int d = 0; d < 2; d++) {  // slots beyond the count are sent too: keep them defined
+        cudaMemset(c->mig_send[d], 0, rec * sizeof(double));
+    }
+    cudaMemset(c->far_send, 0, (far + kRec) * sizeof(double));
     if (cudaMalloc((void **)&c->guest_src, sizeof(int) * (2 * (size_t)c->mig_cap + (size_t)c->nranks * kFarCap)) != cudaSuccess)
         return c->fail("cudaMalloc failed");
-    if (cudaMallocHost((void **)&c->h_mig_hdr, (8 + c->nranks) * sizeof(int)) != cudaSuccess)
+    c->mig_list_cap = 2 * c->mig_cap + kFarCap;
+    if (cudaMalloc((void **)&c->mig_list, sizeof(int) * (size_t)c->mig_list_cap) != cudaSuccess)
+        return c->fail("cudaMalloc failed");
+    if (cudaMallocHost((void **)&c->h_mig_hdr, (8 + c->nranks) * sizeof(int)) != cudaSuccess ||
+        cudaMallocHost((void **)&c->h_hdr64, (2 + c->nranks) * sizeof(unsigned long long)) != cudaSuccess)
         return c->fail("cudaMallocHost failed");
     return 0;
 }
@@ -200,8 +224,10 @@ inline void exchange_destroy(Rank *c) {
     if (c->mig_hdr_send) cudaFree(c->mig_hdr_send);
     if (c->far_send) cudaFree(c->far_send);
     if (c->far_recv) cudaFree(c->far_recv);
-    if (c->far_cnt_recv) cudaFree(c->far_cnt_recv);
+    if (c->far_eager_recv) cudaFree(c->far_eager_recv);
+    if (c->mig_list) cudaFree(c->mig_list);
     if (c->h_mig_hdr) cudaFreeHost(c->h_mig_hdr);
+    if (c->h_hdr64) cudaFreeHost(c->h_hdr64);
 }
 
 // Ghost rows.  Receives are posted "from below" first so that with two strips (both
@@ -226,57 +252,74 @@ inline int exchange_halo(Rank *c) {
     return 0;
 }
 
-// Ship hdr_send[0] records up, hdr_send[1] down and all-gather the hdr_send[2] far records; learn
-// how many arrive.  recv[1] holds what came from below, recv[0] what came from above, far_recv the
-// far records of every strip (stride *far_stride records per strip, far_cnt[r] of them valid).
+// Ship hdr_send[0] records up, hdr_send[1] down and all-gather the hdr_send[2] far records, in ONE
+// NCCL round (header + eager slots; see kEagerRecs).  On return mig_recv[0] / mig_recv[1] hold the
+// header and then *from_up / *from_dn records from above / below, and far_base[r] points at the
+// h_mig_hdr[8 + r] far records of strip r.
 // h_mig_hdr: [0..2] sent up / down / far, [4..5] received from up / down, [8..8+nranks) far counts.
-inline int exchange_records(Rank *c, int *from_up, int *from_dn, int *far_stride) {
+inline int exchange_records(Rank *c, int *from_up, int *from_dn, const double **far_base) {
     NcclApi &api = nccl_api();
+    const size_t eager = (size_t)(1 + std::min(c->mig_cap, kEagerRecs)) * kRec;
+    const size_t far_eager = (size_t)(1 + kFarEager) * kRec;
+    k_seal_headers<<<1, 32, 0, c->stream>>>(c->mig_hdr_send, c->mig_send[0], c->mig_send[1], c->far_send);
     PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr, c->mig_hdr_send, 3 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     PS_NCCL(c, api.GroupStart());
-    PS_NCCL(c, api.Send(c->mig_hdr_send + 0, 1, kNcclInt32, c->up, c->comm.comm, c->stream));
-    PS_NCCL(c, api.Send(c->mig_hdr_send + 1, 1, kNcclInt32, c->dn, c->comm.comm, c->stream));
-    PS_NCCL(c, api.Recv(c->mig_hdr_recv + 1, 1, kNcclInt32, c->dn, c->comm.comm, c->stream));
-    PS_NCCL(c, api.Recv(c->mig_hdr_recv + 0, 1, kNcclInt32, c->up, c->comm.comm, c->stream));
-    PS_NCCL(c, api.AllGather(c->mig_hdr_send + 2, c->far_cnt_recv, 1, kNcclInt32, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Send(c->mig_send[0], eager, kNcclFloat64, c->up, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Send(c->mig_send[1], eager, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Recv(c->mig_recv[1], eager, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+    PS_NCCL(c, api.Recv(c->mig_recv[0], eager, kNcclFloat64, c->up, c->comm.comm, c->stream));
+    PS_NCCL(c, api.AllGather(c->far_send, c->far_eager_recv, far_eager, kNcclFloat64, c->comm.comm, c->stream));
     PS_NCCL(c, api.GroupEnd());
-    PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr + 4, c->mig_hdr_recv, 2 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr + 8, c->far_cnt_recv, c->nranks * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->h_hdr64 + 0, c->mig_recv[0], 8, cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaMemcpyAsync(c->h_hdr64 + 1, c->mig_recv[1], 8, cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaMemcpy2DAsync(c->h_hdr64 + 2, 8, c->far_eager_recv, far_eager * sizeof(double), 8, c->nranks,
+                                 cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error) +
                                         " (3 = migrant buffer overflow; 22 / 24 = a record for another strip arrived)");
-    const int su = c->h_mig_hdr[0], sd = c->h_mig_hdr[1], ru = c->h_mig_hdr[4], rd = c->h_mig_hdr[5];
+    const int su = c->h_mig_hdr[0], sd = c->h_mig_hdr[1];
+    const int ru = (int)c->h_hdr64[0], rd = (int)c->h_hdr64[1];
+    c->h_mig_hdr[4] = ru;
+    c->h_mig_hdr[5] = rd;
     if (ru > c->mig_cap || rd > c->mig_cap) return c->fail("migrant buffer overflow on receive");
     int far_max = 0;  // the same on every strip: everybody sees all the counts
-    for (int r = 0; r < c->nranks; r++) far_max = std::max(far_max, c->h_mig_hdr[8 + r]);
+    for (int r = 0; r < c->nranks; r++) {
+        c->h_mig_hdr[8 + r] = (int)c->h_hdr64[2 + r];
+        far_max = std::max(far_max, c->h_mig_hdr[8 + r]);
+    }
     if (far_max > kFarCap) return c->fail("far-record buffer overflow");
     c->stats.migrants += su + sd + c->h_mig_hdr[2];
-    if (su + sd + ru + rd + far_max > 0) {
+    // second round for what did not fit the eager slots (both ends know from the headers)
+    const int E = (int)(eager / kRec) - 1;
+    if (su > E || sd > E || ru > E || rd > E || far_max > kFarEager) {
         PS_NCCL(c, api.GroupStart());
-        if (su) PS_NCCL(c, api.Send(c->mig_send[0], (size_t)su * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
-        if (sd) PS_NCCL(c, api.Send(c->mig_send[1], (size_t)sd * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));
-        if (rd) PS_NCCL(c, api.Recv(c->mig_recv[1], (size_t)rd * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));
-        if (ru) PS_NCCL(c, api.Recv(c->mig_recv[0], (size_t)ru * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
-        if (far_max)
-            PS_NCCL(c, api.AllGather(c->far_send, c->far_recv, (size_t)far_max * kRec, kNcclFloat64, c->comm.comm, c->stream));
+        if (su > E) PS_NCCL(c, api.Send(c->mig_send[0] + eager, (size_t)(su - E) * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
+        if (sd > E) PS_NCCL(c, api.Send(c->mig_send[1] + eager, (size_t)(sd - E) * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+        if (rd > E) PS_NCCL(c, api.Recv(c->mig_recv[1] + eager, (size_t)(rd - E) * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+        if (ru > E) PS_NCCL(c, api.Recv(c->mig_recv[0] + eager, (size_t)(ru - E) * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
+        if (far_max > kFarEager)
+            PS_NCCL(c, api.AllGather(c->far_send + kRec, c->far_recv, (size_t)far_max * kRec, kNcclFloat64, c->comm.comm, c->stream));
         PS_NCCL(c, api.GroupEnd());
     }
+    for (int r = 0; r < c->nranks; r++)
+        far_base[r] = far_max > kFarEager ? c->far_recv + (size_t)r * far_max * kRec
+                                          : c->far_eager_recv + (size_t)r * far_eager + kRec;
     *from_up = ru;
     *from_dn = rd;
-    *far_stride = far_max;
     return 0;
 }
 
 inline int exchange_emigrants(Rank *c) {
     const Geom &g = c->g;
     timed_begin(c, K_MIGRATE, 0);
-    PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 3 * sizeof(int), c->stream));
-    k_pack_emigrants<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
-        g, c->n_alive, c->mig_cap, c->flags, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->cell_cur,
-        c->newcell, c->mig_send[0], c->mig_send[1], c->far_send, c->mig_hdr_send, c->d_ctr);
-    int ru = 0, rd = 0, far_stride = 0;
-    if (exchange_records(c, &ru, &rd, &far_stride)) return 1;
+    // hdr[3] = length of the emigrant list (k_classify); hdr[0..2] were zeroed with it
+    k_pack_emigrants<<<grid_for(c->mig_list_cap), kThreads, 0, c->stream>>>(
+        g, c->mig_list, c->mig_list_cap, c->mig_cap, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->cell_cur,
+        c->newcell, c->mig_send[0] + kRec, c->mig_send[1] + kRec, c->far_send + kRec, c->mig_hdr_send, c->d_ctr);
+    int ru = 0, rd = 0;
+    std::vector<const double *> far_base(c->nranks);
+    if (exchange_records(c, &ru, &rd, far_base.data())) return 1;
     int n_far = 0;
     for (int r = 0; r < c->nranks; r++) if (r != c->rank) n_far += c->h_mig_hdr[8 + r];
     if (c->n_alive + ru + rd + n_far > c->cap) return c->fail("strip capacity exceeded by arriving particles");
@@ -289,10 +332,10 @@ inline int exchange_emigrants(Rank *c) {
         first += cnt;
         gfirst += cnt;
     };
-    unpack(ru, c->mig_recv[0], 0);
-    unpack(rd, c->mig_recv[1], 0);
+    unpack(ru, c->mig_recv[0] + kRec, 0);
+    unpack(rd, c->mig_recv[1] + kRec, 0);
     for (int r = 0; r < c->nranks; r++)
-        if (r != c->rank) unpack(c->h_mig_hdr[8 + r], c->far_recv + (size_t)r * far_stride * kRec, 1);
+        if (r != c->rank) unpack(c->h_mig_hdr[8 + r], far_base[r], 1);
     timed_end(c);
     c->n_guest = ru + rd + n_far;
     return check_launch(c, "exchange_emigrants");
@@ -302,12 +345,13 @@ inline int exchange_late(Rank *c, int *n_src, int *n_tombstones_in) {
     const Geom &g = c->g;
     const int n_tot = c->n_alive + c->n_guest;
     timed_begin(c, K_MIGRATE, 0);
-    PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 3 * sizeof(int), c->stream));
-    k_pack_late<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
-        g, n_tot, c->mig_cap, c->fate, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->newcell,
-        c->mig_send[0], c->mig_send[1], c->far_send, c->mig_hdr_send, c->d_ctr);
-    int ru = 0, rd = 0, far_stride = 0;
-    if (exchange_records(c, &ru, &rd, &far_stride)) return 1;
+    // hdr[3] = length of the late list (k_resolve); hdr[0..2] were zeroed with it
+    k_pack_late<<<grid_for(c->mig_list_cap), kThreads, 0, c->stream>>>(
+        g, c->mig_list, c->mig_list_cap, c->mig_cap, c->fate, c->pos_alt, c->vel_cur, c->m_cur, c->id_cur, c->newcell,
+        c->mig_send[0] + kRec, c->mig_send[1] + kRec, c->far_send + kRec, c->mig_hdr_send, c->d_ctr);
+    int ru = 0, rd = 0;
+    std::vector<const double *> far_base(c->nranks);
+    if (exchange_records(c, &ru, &rd, far_base.data())) return 1;
     int n_far = 0;
     for (int r = 0; r < c->nranks; r++) if (r != c->rank) n_far += c->h_mig_hdr[8 + r];
     if (n_tot + ru + rd + n_far > c->cap) return c->fail("strip capacity exceeded by arriving particles");
@@ -319,10 +363,10 @@ inline int exchange_late(Rank *c, int *n_src, int *n_tombstones_in) {
             c->dead_new_count, c->mv_head, c->dm_head, c->mv_next, filter, c->d_ctr);
         first += cnt;
     };
-    unpack(ru, c->mig_recv[0], 0);
-    unpack(rd, c->mig_recv[1], 0);
+    unpack(ru, c->mig_recv[0] + kRec, 0);
+    unpack(rd, c->mig_recv[1] + kRec, 0);
     for (int r = 0; r < c->nranks; r++)
-        if (r != c->rank) unpack(c->h_mig_hdr[8 + r], c->far_recv + (size_t)r * far_stride * kRec, 1);
+        if (r != c->rank) unpack(c->h_mig_hdr[8 + r], far_base[r], 1);
     timed_end(c);
     *n_src = first;
     *n_tombstones_in = ru + rd + n_far;  // upper bound

@@ -733,7 +733,8 @@ k_classify(Geom g, const int *__restrict__ mover_list, const int *__restrict__ n
            const int *__restrict__ dead_start, const unsigned *__restrict__ dead_id,
            unsigned char *__restrict__ flags, int *arr_head, int *__restrict__ arr_next,
            const double2 *__restrict__ pos_new, int *arr_cnt, ArrRec *__restrict__ arr_rec,
-           unsigned long long *stat_strays) {
+           unsigned long long *stat_strays, int *__restrict__ emig_list, int *emig_count, int emig_cap,
+           Counters *ctr) {
     const int nm = *n_movers;
     for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < nm; t += gridDim.x * blockDim.x) {
         const int i = mover_list[t];
@@ -766,7 +767,10 @@ k_classify(Geom g, const int *__restrict__ mover_list, const int *__restrict__ n
                     }
                 }
             } else {
-                f |= F_EMIGRANT;
+                f |= F_EMIGRANT;  // multi-strip only: packed for the exchange from this short list
+                const int sl = atomicAdd(emig_count, 1);
+                if (sl < emig_cap) emig_list[sl] = i;
+                else ctr->error = DE_MIGRANT_OVERFLOW;
             }
         } else {
             atomicAdd(stat_strays, 1ull);  // rare

@@ -42,7 +42,8 @@ k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner, const int *
           const unsigned *__restrict__ id, unsigned char *__restrict__ fate, int *count,
           int *dead_new_count, int *mv_head, int *dm_head, int *__restrict__ mv_next,
           double2 *__restrict__ grave_pos, double2 *__restrict__ grave_vel,
-          unsigned *__restrict__ grave_id, int *__restrict__ grave_cell, Counters *ctr) {
+          unsigned *__restrict__ grave_id, int *__restrict__ grave_cell, Counters *ctr,
+          int *__restrict__ late_list, int *late_count, int late_cap) {
     constexpr int kWarps = kThreads / 32;
     __shared__ int warp_dying[kResolveRows][kWarps];
     __shared__ int tile_base;
@@ -85,7 +86,12 @@ k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner, const int *
                     const int p = pp[r];
                     const bool dead = p >= 0;
                     if (dead && qq[r] == i && i < p) mine++;  // mutual-first pair, counted once
-                    if (!in_strip) ft = dead ? FATE_LEFT_DEAD : FATE_LEFT_ALIVE;
+                    if (!in_strip) {  // multi-strip only: packed for the late exchange from this short list
+                        ft = dead ? FATE_LEFT_DEAD : FATE_LEFT_ALIVE;
+                        const int sl = atomicAdd(late_count, 1);
+                        if (sl < late_cap) late_list[sl] = i;
+                        else ctr->error = DE_MIGRANT_OVERFLOW;
+                    }
                     else if (nl == c) ft = dead ? FATE_DEAD_HERE : FATE_STAY;
                     else ft = dead ? FATE_DEAD_MOVED : FATE_MOVE;
                 }

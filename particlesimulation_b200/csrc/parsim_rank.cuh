@@ -109,7 +109,10 @@ struct Rank {
     int *mig_hdr_send = nullptr, *mig_hdr_recv = nullptr, *h_mig_hdr = nullptr;
     // far records: particles that a close encounter threw beyond the neighbouring row (any strip)
     double *far_send = nullptr, *far_recv = nullptr;
-    int *far_cnt_recv = nullptr;
+    int *mig_list = nullptr;                // indices of this step's emigrants (k_classify) / late records (k_resolve)
+    int mig_list_cap = 0;
+    double *far_eager_recv = nullptr;       // first-round all-gather: (1 + kFarEager) records per strip
+    unsigned long long *h_hdr64 = nullptr;  // pinned: received headers (up, down, far of every strip)
 
     cudaStream_t stream = nullptr;
     std::string err;

@@ -201,11 +201,13 @@ static int stage_lists(Rank *c) {
     const Geom &g = c->g;
     // the mover list (written by k_force_integrate) lives in `partner`, which is free until the
     // collision search; about 1-5 % of the particles are on it
+    if (c->nranks > 1) PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 4 * sizeof(int), c->stream));
     PS_LAUNCH(c, K_CLASSIFY, 0.5 * c->n_alive, "k_classify",
               k_classify<<<148 * 4, kThreads, 0, c->stream>>>(
                   g, c->partner, &c->d_ctr->n_movers, c->cell_cur, c->cs_cur, c->newcell, c->id_cur,
                   c->n_tomb > 0 ? c->dead_start_cur : nullptr, c->dead_id_cur, c->flags, c->arr_head,
-                  c->arr_next, c->pos_alt, c->arr_cnt, c->arr_rec, &c->d_ctr->strays));
+                  c->arr_next, c->pos_alt, c->arr_cnt, c->arr_rec, &c->d_ctr->strays, c->mig_list,
+                  c->nranks > 1 ? c->mig_hdr_send + 3 : nullptr, c->mig_list_cap, c->d_ctr));
     c->n_guest = 0;
     if (c->nranks > 1 && exchange_emigrants(c)) return 1;
     c->have_flags = true;
@@ -261,11 +263,13 @@ static int stage_collide(Rank *c) {
                       c->id_cur, c->flags, c->arr_head, c->arr_next, c->guest_src, c->partner,
                       c->opt_stats ? &c->d_ctr->collision_pairs : nullptr));
     }
+    if (c->nranks > 1) PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 4 * sizeof(int), c->stream));
     PS_LAUNCH(c, K_RESOLVE, 10.0 * n_tot, "k_resolve",
               k_resolve<<<std::min(grid_for(n_tot, kThreads * kResolveRows), 148 * 8), kThreads, 0, c->stream>>>(
                   g, n_tot, c->n_alive, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,
                   c->vel_cur, c->id_cur, c->fate, c->count, c->dead_new_count, c->mv_head, c->dm_head,
-                  c->mv_next, c->grave_pos, c->grave_vel, c->grave_id, c->grave_cell, c->d_ctr));
+                  c->mv_next, c->grave_pos, c->grave_vel, c->grave_id, c->grave_cell, c->d_ctr, c->mig_list,
+                  c->nranks > 1 ? c->mig_hdr_send + 3 : nullptr, c->mig_list_cap));
     PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error));
