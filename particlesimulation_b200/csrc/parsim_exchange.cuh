@@ -205,6 +205,10 @@ inline int exchange_create(Rank *c, const unsigned char *nccl_id) {
     cudaMemset(c->far_send, 0, (far + kRec) * sizeof(double));
     if (cudaMalloc((void **)&c->guest_src, sizeof(int) * (2 * (size_t)c->mig_cap + (size_t)c->nranks * kFarCap)) != cudaSuccess)
         return c->fail("cudaMalloc failed");
+    if (const char *e = getenv("PARSIM_EAGER_RECS")) {  // tests: force the overflow round (same value on every rank)
+        c->eager_recs = std::min(std::max(atoi(e), 1), kEagerRecs);
+        c->far_eager = std::min(c->eager_recs, kFarEager);
+    }
     c->mig_list_cap = 2 * c->mig_cap + kFarCap;
     if (cudaMalloc((void **)&c->mig_list, sizeof(int) * (size_t)c->mig_list_cap) != cudaSuccess)
         return c->fail("cudaMalloc failed");
@@ -259,8 +263,8 @@ inline int exchange_halo(Rank *c) {
 // h_mig_hdr: [0..2] sent up / down / far, [4..5] received from up / down, [8..8+nranks) far counts.
 inline int exchange_records(Rank *c, int *from_up, int *from_dn, const double **far_base) {
     NcclApi &api = nccl_api();
-    const size_t eager = (size_t)(1 + std::min(c->mig_cap, kEagerRecs)) * kRec;
-    const size_t far_eager = (size_t)(1 + kFarEager) * kRec;
+    const size_t eager = (size_t)(1 + std::min(c->mig_cap, c->eager_recs)) * kRec;
+    const size_t far_eager = (size_t)(1 + c->far_eager) * kRec;
     k_seal_headers<<<1, 32, 0, c->stream>>>(c->mig_hdr_send, c->mig_send[0], c->mig_send[1], c->far_send);
     PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr, c->mig_hdr_send, 3 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     PS_NCCL(c, api.GroupStart());
@@ -292,18 +296,18 @@ inline int exchange_records(Rank *c, int *from_up, int *from_dn, const double **
     c->stats.migrants += su + sd + c->h_mig_hdr[2];
     // second round for what did not fit the eager slots (both ends know from the headers)
     const int E = (int)(eager / kRec) - 1;
-    if (su > E || sd > E || ru > E || rd > E || far_max > kFarEager) {
+    if (su > E || sd > E || ru > E || rd > E || far_max > c->far_eager) {
         PS_NCCL(c, api.GroupStart());
         if (su > E) PS_NCCL(c, api.Send(c->mig_send[0] + eager, (size_t)(su - E) * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
         if (sd > E) PS_NCCL(c, api.Send(c->mig_send[1] + eager, (size_t)(sd - E) * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));
         if (rd > E) PS_NCCL(c, api.Recv(c->mig_recv[1] + eager, (size_t)(rd - E) * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));
         if (ru > E) PS_NCCL(c, api.Recv(c->mig_recv[0] + eager, (size_t)(ru - E) * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
-        if (far_max > kFarEager)
+        if (far_max > c->far_eager)
             PS_NCCL(c, api.AllGather(c->far_send + kRec, c->far_recv, (size_t)far_max * kRec, kNcclFloat64, c->comm.comm, c->stream));
         PS_NCCL(c, api.GroupEnd());
     }
     for (int r = 0; r < c->nranks; r++)
-        far_base[r] = far_max > kFarEager ? c->far_recv + (size_t)r * far_max * kRec
+        far_base[r] = far_max > c->far_eager ? c->far_recv + (size_t)r * far_max * kRec
                                           : c->far_eager_recv + (size_t)r * far_eager + kRec;
     *from_up = ru;
     *from_dn = rd;

@@ -111,6 +111,7 @@ struct Rank {
     double *far_send = nullptr, *far_recv = nullptr;
     int *mig_list = nullptr;                // indices of this step's emigrants (k_classify) / late records (k_resolve)
     int mig_list_cap = 0;
+    int eager_recs = 8192, far_eager = 32;  // record slots of the first exchange round (<= kEagerRecs / kFarEager)
     double *far_eager_recv = nullptr;       // first-round all-gather: (1 + kFarEager) records per strip
     unsigned long long *h_hdr64 = nullptr;  // pinned: received headers (up, down, far of every strip)
 

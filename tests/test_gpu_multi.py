@@ -46,6 +46,35 @@ def test_strips_match_single_gpu(case, n_gpus):
     one.close(); many.close()
 
 
+@pytest.mark.parametrize("n_gpus", [2, 4])
+def test_exchange_overflow_round(n_gpus, monkeypatch):
+    """More records than the eager slots of the one-round exchange: the second round carries the
+    rest (neighbour messages and the far all-gather), same bits as one GPU."""
+    import oracle_lib as ol
+    if ngpu() < n_gpus:
+        pytest.skip(f"needs {n_gpus} GPUs")
+    monkeypatch.setenv("PARSIM_CAPACITY_PCT", "400")
+    monkeypatch.setenv("PARSIM_EAGER_RECS", "3")
+    for case in ("dense", "far"):
+        if case == "dense":
+            seed, side, nc, n = 1, 10, 100, 100000
+            arrs = None
+        else:
+            side, nc, arrs = ol.far_jump_case()
+            seed, n = 0, len(arrs[0])
+        one = ParticleSimulation(seed, side, nc, n, arrays=arrs)
+        many = ParticleSimulation(seed, side, nc, n, arrays=arrs, n_gpus=n_gpus)
+        for t in range(4):
+            one.simulate(1)
+            many.simulate(1)
+            assert one.result() == many.result(), f"{case} step {t}"
+        a, b = one.dump(), many.dump()
+        for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+            assert np.array_equal(a[k], b[k]), (case, k)
+        assert many.stats()["migrants"] > 3 * 4
+        one.close(); many.close()
+
+
 @pytest.mark.parametrize("n_gpus", [2, 3, 4, 8])
 def test_far_jumps_cross_strips(n_gpus):
     """Close encounters throw particles many rows away (any strip, not just the neighbour): the
