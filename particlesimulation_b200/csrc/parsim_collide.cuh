@@ -193,26 +193,32 @@ __device__ long long collide_cell(const CollideArgs &a, int L, int t, Staging sm
 // All-pairs sweep for lists that fit no staging area (tens of thousands of entries per cell).
 // Such a cell is cut into slices of kThreads bin-time entries (+ one slice for the arrivals bag),
 // and k_collide_huge spreads the slices of all such cells over the whole GPU.
+// The bin-time entries are id-sorted and every arrival's key is above every id, so the FIRST
+// close bin-time entry met in ascending order is the partner (first(i) of the mutual-first rule):
+// the sweep stops there.  At the densities that produce such cells a particle has hundreds of
+// close neighbours, so a thread looks at a few dozen entries, not at the whole cell.
 __device__ __forceinline__ long long sweep_allpairs(const CollideArgs &a, int i, int s, int e, int head) {
     const double2 p = a.pos[i];
-    unsigned long long best = ~0ull;
     int best_idx = -1;
-#pragma unroll 4
-    for (int k = s; k < e; k++) {
+    int k = s;
+    for (; k < e; k++) {
         if (is_close(p, __ldg(&a.pos[k]), a.thr2) && k != i && !(a.flags[k] & F_REMOVED)) {
-            const unsigned long long key = a.id[k];
-            if (key < best) { best = key; best_idx = k; }
+            best_idx = k;
+            break;
         }
     }
-    int walked = 0;
-    for (int k = head; k >= 0; k = a.arr_next[k], walked++) {
-        if (k != i && is_close(p, a.pos[k], a.thr2)) {
-            const unsigned long long key = entry_key(a, k);
-            if (key < best) { best = key; best_idx = k; }
+    long long walked = k - s;
+    if (best_idx < 0) {
+        unsigned long long best = ~0ull;
+        for (int x = head; x >= 0; x = a.arr_next[x], walked++) {
+            if (x != i && is_close(p, a.pos[x], a.thr2)) {
+                const unsigned long long key = entry_key(a, x);
+                if (key < best) { best = key; best_idx = x; }
+            }
         }
     }
     a.partner[i] = best_idx;
-    return e - s + walked;
+    return walked;
 }
 
 __global__ void __launch_bounds__(kThreads)

@@ -13,6 +13,7 @@
 //               rebuilds the cell's tombstone list.  No atomics, deterministic layout.
 #pragma once
 #include <cooperative_groups.h>
+#include <limits.h>
 
 #include "parsim_kernels.cuh"
 
@@ -170,17 +171,28 @@ struct MoveArgs {
     unsigned *id_out;
     int *cell_out;
     unsigned *dead_new;
+    int *big_list, *big_count;           // cells with more than big_min old entries: left to k_move_big
+    int big_min;
 };
 
-template <int LANES>
-__global__ void __launch_bounds__(kThreads) k_move(Geom g, MoveArgs a) {
+// BIG: leave cells (or tombstone lists) above a.big_min entries to k_move_big.  The test costs the
+// ordinary case about 5 % (this kernel is a chain of dependent loads per cell), so the host asks
+// for it only when the cells are huge on average.
+template <int LANES, bool BIG>
+__device__ __forceinline__ void move_cell(const Geom &g, const MoveArgs &a, int c) {
     auto tile = cg::tiled_partition<LANES>(cg::this_thread_block());
-    const int c = (blockIdx.x * blockDim.x + threadIdx.x) / LANES;
-    if (c >= g.ncells) return;  // whole tiles leave together
     const int lane = tile.thread_rank();
     const unsigned lt = (1u << lane) - 1u;
     const int s = a.cs_old[c], e = a.cs_old[c + 1];
     const int ns = a.cs_new[c];
+    if (BIG) {
+        int nd = 0;
+        if (a.ds_new) nd = a.ds_old[c + 1] - a.ds_old[c];
+        if (max(e - s, nd) > a.big_min) {  // would keep this one lane group busy for the whole kernel
+            if (lane == 0) a.big_list[atomicAdd(a.big_count, 1)] = c;
+            return;
+        }
+    }
 
     // the first LANES arrivals live in registers (lane j holds arrival j); more are walked
     int n_arr = 0, my_arr = -1, rest = -1;
@@ -256,6 +268,135 @@ __global__ void __launch_bounds__(kThreads) k_move(Geom g, MoveArgs a) {
         a.arr_head[c] = -1;
         if (a.arr_cnt) a.arr_cnt[c] = 0;
         a.count[c] = 0;
+    }
+}
+
+template <int LANES, bool BIG>
+__global__ void __launch_bounds__(kThreads) k_move(Geom g, MoveArgs a) {
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) / LANES;
+    if (c >= g.ncells) return;  // whole tiles leave together
+    move_cell<LANES, BIG>(g, a, c);
+}
+
+__device__ __noinline__ void move_cell_lanes32(const Geom &g, const MoveArgs &a, int c) { move_cell<32, false>(g, a, c); }
+
+// Huge cells (tens of thousands of entries, BASELINE config 5): one BLOCK per cell.  The arrivals
+// (<= kMoveBigArr, else the block falls back to a single lane group's generic loop) are sorted by
+// id in shared memory; a stayer's slot is (stayers before it) + (arrivals with a smaller id, by
+// binary search); the histogram of those search results, prefix-summed, gives every arrival its
+// slot without looking at the stayers again.
+constexpr int kMoveBigArr = 2048;
+
+__global__ void __launch_bounds__(kThreads) k_move_big(Geom g, MoveArgs a) {
+    __shared__ unsigned a_id[kMoveBigArr], s_id[kMoveBigArr];
+    __shared__ int a_ix[kMoveBigArr], s_ix[kMoveBigArr];
+    __shared__ int hist[kMoveBigArr + 1];
+    __shared__ int wsum[kThreads / 32], wdead[kThreads / 32];
+    __shared__ int sh_n_arr, sh_run, sh_doff;
+    const int t = threadIdx.x, lane = t & 31, warp = t >> 5;
+    const unsigned lt = (1u << lane) - 1u;
+    const int nbig = *a.big_count;
+    for (int w = blockIdx.x; w < nbig; w += gridDim.x) {
+        const int c = a.big_list[w];
+        const int s = a.cs_old[c], e = a.cs_old[c + 1];
+        const int ns = a.cs_new[c];
+        if (t == 0) {
+            int n = 0;
+            for (int x = a.mv_head[c]; x >= 0; x = a.mv_next[x], n++)
+                if (n < kMoveBigArr) a_ix[n] = x;
+            sh_n_arr = n;
+        }
+        __syncthreads();
+        const int n_arr = sh_n_arr;
+        if (n_arr > kMoveBigArr) {  // block-uniform; never seen in practice (1 % of a cell moves per step)
+            // the generic loop needs no cooperation beyond one lane group: run it on the first warp
+            // with the big-cell test switched off
+            if (warp == 0) move_cell_lanes32(g, a, c);
+            __syncthreads();
+            continue;
+        }
+        for (int j = t; j < n_arr; j += kThreads) a_id[j] = a.id_in[a_ix[j]];
+        for (int j = t; j <= n_arr; j += kThreads) hist[j] = 0;
+        __syncthreads();
+        for (int j = t; j < n_arr; j += kThreads) {  // rank sort by id (ids are distinct)
+            const unsigned me = a_id[j];
+            int r = 0;
+            for (int q = 0; q < n_arr; q++) r += a_id[q] < me ? 1 : 0;
+            s_id[r] = me;
+            s_ix[r] = a_ix[j];
+        }
+        // tombstones: old entries first
+        int doff = 0;
+        if (a.ds_new) {
+            const int ds = a.ds_old[c], de = a.ds_old[c + 1];
+            doff = a.ds_new[c];
+            for (int q = ds + t; q < de; q += kThreads) a.dead_new[doff + (q - ds)] = a.dead_old[q];
+            doff += de - ds;
+        }
+        if (t == 0) { sh_run = 0; sh_doff = doff; }
+        __syncthreads();
+        for (int base = s; base < e; base += kThreads) {
+            const int k = base + t;
+            const int ft = k < e ? a.fate[k] : 255;
+            const unsigned me = k < e ? a.id_in[k] : 0u;
+            const bool stay = ft == FATE_STAY, dead = ft == FATE_DEAD_HERE;
+            const unsigned smask = __ballot_sync(0xffffffffu, stay), dmask = __ballot_sync(0xffffffffu, dead);
+            if (lane == 0) { wsum[warp] = __popc(smask); wdead[warp] = __popc(dmask); }
+            __syncthreads();
+            int sbefore = 0, dbefore = 0, stot = 0, dtot = 0;
+#pragma unroll
+            for (int q = 0; q < kThreads / 32; q++) {
+                sbefore += q < warp ? wsum[q] : 0;
+                dbefore += q < warp ? wdead[q] : 0;
+                stot += wsum[q];
+                dtot += wdead[q];
+            }
+            const int run = sh_run, dbase = sh_doff;
+            if (stay) {
+                int lo = 0, hi = n_arr;  // arrivals with a smaller id
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (s_id[mid] < me) lo = mid + 1; else hi = mid;
+                }
+                atomicAdd(&hist[lo], 1);
+                const int o = ns + run + sbefore + __popc(smask & lt) + lo;
+                a.pos_out[o] = a.pos_in[k];
+                a.vel_out[o] = a.vel_in[k];
+                a.m_out[o] = a.m_in[k];
+                a.id_out[o] = me;
+                a.cell_out[o] = c;
+            }
+            if (dead && a.ds_new) a.dead_new[dbase + dbefore + __popc(dmask & lt)] = me;
+            __syncthreads();
+            if (t == 0) { sh_run = run + stot; sh_doff = dbase + dtot; }
+            __syncthreads();
+        }
+        // arrival j (id order): j arrivals and hist[0..j] stayers lie before it
+        if (t == 0) {
+            int acc = 0;
+            for (int j = 0; j <= n_arr; j++) { acc += hist[j]; hist[j] = acc; }
+        }
+        __syncthreads();
+        for (int j = t; j < n_arr; j += kThreads) {
+            const int x = s_ix[j];
+            const int o = ns + j + hist[j];
+            a.pos_out[o] = a.pos_in[x];
+            a.vel_out[o] = a.vel_in[x];
+            a.m_out[o] = a.m_in[x];
+            a.id_out[o] = s_id[j];
+            a.cell_out[o] = c;
+        }
+        if (t == 0) {
+            int d = sh_doff;
+            if (a.ds_new)
+                for (int x = a.dm_head[c]; x >= 0; x = a.mv_next[x]) a.dead_new[d++] = a.id_in[x];
+            a.mv_head[c] = -1;
+            a.dm_head[c] = -1;
+            a.arr_head[c] = -1;
+            if (a.arr_cnt) a.arr_cnt[c] = 0;
+            a.count[c] = 0;
+        }
+        __syncthreads();
     }
 }
 

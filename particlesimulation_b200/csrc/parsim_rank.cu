@@ -136,6 +136,12 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     PS_ALLOC(c, c->rec0, N, false);
     PS_ALLOC(c, c->pos_cur, N, false); PS_ALLOC(c, c->pos_alt, N, false);
     PS_ALLOC(c, c->vel_cur, N, false); PS_ALLOC(c, c->vel_alt, N, false);
+    if (const char *e = getenv("PARSIM_MOVE_BIG_MIN")) {
+        c->move_big_min = std::max(1, atoi(e));
+        c->move_big_force = true;
+    }
+    PS_ALLOC(c, c->move_big_list, std::min(C, (N + (size_t)n_part) / (size_t)c->move_big_min + 16), false);
+    PS_ALLOC(c, c->d_move_big_count, 1, true);
     if (!c->collide_grid) PS_ALLOC(c, c->posf, N, false);
     else {
         PS_ALLOC(c, c->big_cells, C, false); PS_ALLOC(c, c->d_big_count, 2, true);
@@ -190,7 +196,8 @@ void rank_destroy(Rank *c) {
                     c->dead_start_cur, c->dead_start_alt, c->dead_id_cur, c->dead_id_alt,
                     c->mv_head, c->dm_head, c->mv_next, c->fate, c->grave_pos, c->grave_vel, c->grave_id,
                     c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->posf, c->rec0,
-                    c->big_cells, c->d_big_count, c->huge_items, c->arr_cnt, c->arr_rec, c->stage_ids, c->stage[0],
+                    c->big_cells, c->d_big_count, c->huge_items, c->move_big_list, c->d_move_big_count, c->arr_cnt, c->arr_rec,
+                    c->stage_ids, c->stage[0],
                     c->stage[1], c->stage[2], c->stage[3], c->stage[4]};
     for (void *p : ptrs) if (p) cudaFree(p);
     if (c->h_ctr) cudaFreeHost(c->h_ctr);

@@ -58,6 +58,9 @@ struct Rank {
     int grid_nb = 1, grid_cap = 0, grid_it = 2, big_nb = 1, big_cap = 0;
     int *big_cells = nullptr, *d_big_count = nullptr;  // d_big_count[0]: big cells, [1]: huge-cell slices
     int2 *huge_items = nullptr;
+    int *move_big_list = nullptr, *d_move_big_count = nullptr;  // cells above move_big_min entries (k_move_big)
+    int move_big_min = 4096;                                    // PARSIM_MOVE_BIG_MIN (setting it forces the path)
+    bool move_big_force = false;
     int *arr_cnt = nullptr;
     ArrRec *arr_rec = nullptr;
     bool have_newcell = false, have_flags = false;

@@ -87,9 +87,10 @@ static int sort_initial(Rank *c) {
 }
 
 template <int LANES>
-static void launch_move(Rank *c, const MoveArgs &a) {
+static void launch_move(Rank *c, const MoveArgs &a, bool big) {
     long long threads = (long long)c->g.ncells * LANES;
-    k_move<LANES><<<grid_for(threads), kThreads, 0, c->stream>>>(c->g, a);
+    if (big) k_move<LANES, true><<<grid_for(threads), kThreads, 0, c->stream>>>(c->g, a);
+    else k_move<LANES, false><<<grid_for(threads), kThreads, 0, c->stream>>>(c->g, a);
 }
 
 // End of step: new cell_start (and tombstone_start) by scan, then the per-cell merge.
@@ -113,17 +114,23 @@ static int merge_step(Rank *c, int n_src, int n_surv, bool with_dead) {
     a.dead_old = c->dead_id_cur; a.dead_new = c->dead_id_alt;
     a.pos_out = c->pos_cur; a.vel_out = c->vel_alt; a.m_out = c->m_alt; a.id_out = c->id_alt;
     a.cell_out = c->cell_alt;
+    a.big_list = c->move_big_list; a.big_count = c->d_move_big_count; a.big_min = c->move_big_min;
+    PS_CUDA(c, cudaMemsetAsync(c->d_move_big_count, 0, sizeof(int), c->stream));
     // 1 fate + 4 id read per source entry, 40 read + 48 written per survivor, 8 B per tombstone
     PS_LAUNCH(c, K_MOVE, 5.0 * n_src + 88.0 * n_surv + 16.0 * g.ncells + (with_dead ? 8.0 * c->n_tomb : 0.0), "k_move", {
         // lanes per cell from the CURRENT occupancy (the result does not depend on it)
         const double occ = (double)n_src / std::max(1, g.ncells);
         const int lanes = occ <= 6 ? 4 : occ <= 12 ? 8 : occ <= 24 ? 16 : 32;
+        // huge cells / tombstone lists on average (BASELINE config 5): those go to k_move_big
+        const bool big = c->move_big_force || occ > 0.125 * c->move_big_min ||
+                         (with_dead && (double)c->n_tomb > 0.125 * c->move_big_min * g.ncells);
         switch (lanes) {
-        case 4: launch_move<4>(c, a); break;
-        case 8: launch_move<8>(c, a); break;
-        case 16: launch_move<16>(c, a); break;
-        default: launch_move<32>(c, a); break;
+        case 4: launch_move<4>(c, a, big); break;
+        case 8: launch_move<8>(c, a, big); break;
+        case 16: launch_move<16>(c, a, big); break;
+        default: launch_move<32>(c, a, big); break;
         }
+        if (big) k_move_big<<<148 * 2, kThreads, 0, c->stream>>>(g, a);
     });
     std::swap(c->vel_cur, c->vel_alt);
     std::swap(c->m_cur, c->m_alt);
@@ -280,7 +287,9 @@ static int stage_collide(Rank *c) {
     if (c->nranks > 1) {
         if (exchange_late(c, &n_src, &tomb_in)) return 1;
     }
-    const bool with_dead = c->n_tomb > 0 || deaths > 0 || tomb_in > 0;
+    // the tombstone lists change only when somebody died or a tombstone arrived: otherwise they
+    // stay where they are (no scan, no copy)
+    const bool with_dead = deaths > 0 || tomb_in > 0;
     if (merge_step(c, n_src, n_src - deaths, with_dead)) return 1;
     c->n_tomb += deaths + tomb_in;  // upper bound; exact total is dead_start[ncells]
     if (c->nranks == 1) {

@@ -166,6 +166,29 @@ def test_cli_semantics_switch():
     assert p.returncode == 1 and p.stderr.startswith("Error: ")
 
 
+@pytest.mark.parametrize("case", [(1, 10, 100, 100000, 6), (5, 1, 20, 20000, 6), (-7, 10, 50, 20000, 6), (5, 1, 4, 60000, 5),
+                                  (9, 0.3, 4, 3000, 6)], ids=lambda c: " ".join(map(str, c)))
+def test_block_per_cell_merge_matches_lane_groups(case, monkeypatch):
+    """k_move_big (one block per huge cell: sorted arrivals, binary search, histogram) must build the
+    same (cell, id) order as the lane-group merge; forced on ordinary cells by a tiny threshold."""
+    seed, side, nc, n, steps = case
+    ref = ParticleSimulation(seed, side, nc, n)
+    monkeypatch.setenv("PARSIM_MOVE_BIG_MIN", "6")
+    big = ParticleSimulation(seed, side, nc, n)
+    monkeypatch.delenv("PARSIM_MOVE_BIG_MIN")
+    for t in range(steps):
+        ref.simulate(1)
+        big.simulate(1)
+        assert ref.result() == big.result(), f"step {t}"
+        a, b = ref.dump(), big.dump()
+        for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+            assert np.array_equal(a[k], b[k]), (t, k)
+        ia, ib = ref.download(), big.download()  # device order = (cell, id) order
+        for u, v in zip(ia, ib):
+            assert np.array_equal(u, v), f"layout differs at step {t}"
+    ref.close(); big.close()
+
+
 def test_run_is_deterministic_and_matches_staged():
     args = (1, 10, 100, 200000)
     a = ParticleSimulation(*args); a.simulate(5)
