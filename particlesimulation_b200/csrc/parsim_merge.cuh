@@ -240,22 +240,44 @@ __device__ __forceinline__ void move_cell(const Geom &g, const MoveArgs &a, int 
     }
 
     // arrivals: position = stayers with a smaller id + arrivals with a smaller id
-    for (int x = a.mv_head[c]; x >= 0; x = a.mv_next[x]) {
-        const unsigned aid = a.id_in[x];
-        int r = 0;
-        for (int base = s; base < e; base += LANES) {
-            const int k = base + lane;
-            const bool less = k < e && a.fate[k] == FATE_STAY && a.id_in[k] < aid;
-            r += __popc(tile.ballot(less));
+    if (rest < 0) {
+        // all of them are in registers (lane q holds arrival q): no second walk of the bag
+        for (int q = 0; q < n_arr; q++) {
+            const unsigned aid = tile.shfl(my_aid, q);
+            const int x = tile.shfl(my_arr, q);
+            int r = __popc(tile.ballot(lane < n_arr && my_aid < aid));
+            for (int base = s; base < e; base += LANES) {
+                const int k = base + lane;
+                const bool less = k < e && a.fate[k] == FATE_STAY && a.id_in[k] < aid;
+                r += __popc(tile.ballot(less));
+            }
+            if (lane == 0) {
+                const int o = ns + r;
+                a.pos_out[o] = a.pos_in[x];
+                a.vel_out[o] = a.vel_in[x];
+                a.m_out[o] = a.m_in[x];
+                a.id_out[o] = aid;
+                a.cell_out[o] = c;
+            }
         }
-        for (int y = a.mv_head[c]; y >= 0; y = a.mv_next[y]) r += a.id_in[y] < aid ? 1 : 0;
-        if (lane == 0) {
-            const int o = ns + r;
-            a.pos_out[o] = a.pos_in[x];
-            a.vel_out[o] = a.vel_in[x];
-            a.m_out[o] = a.m_in[x];
-            a.id_out[o] = aid;
-            a.cell_out[o] = c;
+    } else {
+        for (int x = a.mv_head[c]; x >= 0; x = a.mv_next[x]) {
+            const unsigned aid = a.id_in[x];
+            int r = 0;
+            for (int base = s; base < e; base += LANES) {
+                const int k = base + lane;
+                const bool less = k < e && a.fate[k] == FATE_STAY && a.id_in[k] < aid;
+                r += __popc(tile.ballot(less));
+            }
+            for (int y = a.mv_head[c]; y >= 0; y = a.mv_next[y]) r += a.id_in[y] < aid ? 1 : 0;
+            if (lane == 0) {
+                const int o = ns + r;
+                a.pos_out[o] = a.pos_in[x];
+                a.vel_out[o] = a.vel_in[x];
+                a.m_out[o] = a.m_in[x];
+                a.id_out[o] = aid;
+                a.cell_out[o] = c;
+            }
         }
     }
     // tombstones of particles that died this step and came to rest in this cell from elsewhere
@@ -272,7 +294,7 @@ __device__ __forceinline__ void move_cell(const Geom &g, const MoveArgs &a, int 
 }
 
 template <int LANES, bool BIG>
-__global__ void __launch_bounds__(kThreads) k_move(Geom g, MoveArgs a) {
+__global__ void __launch_bounds__(kThreads, 8) k_move(Geom g, MoveArgs a) {
     const int c = (blockIdx.x * blockDim.x + threadIdx.x) / LANES;
     if (c >= g.ncells) return;  // whole tiles leave together
     move_cell<LANES, BIG>(g, a, c);
