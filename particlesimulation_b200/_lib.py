@@ -7,7 +7,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libparsim_b200.so")
+LIB_PATH = os.environ.get("PARSIM_LIB") or os.path.join(HERE, "libparsim_b200.so")  # PARSIM_LIB: tuning builds
 NKERNELS = 16
 
 

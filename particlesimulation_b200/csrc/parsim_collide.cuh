@@ -285,8 +285,11 @@ __device__ __forceinline__ void warp_scan_bins(int *cnt, int lane) {
 // id-sorted), so ord = position in the segment; arrivals follow, ordered by (source cell, id).
 // Each unordered candidate pair is tested ONCE (own bin behind the entry, the next bin of the
 // row, three bins of the next row) and a close pair lowers `best` of both members (smem min).
+#ifndef PS_COLLIDE_MINB
+#define PS_COLLIDE_MINB 5  // 48 registers; 1 (more registers) and 7-8 (spills) are both 15 % slower
+#endif
 template <int IT>
-__global__ void __launch_bounds__(kCollideWarps * 32)
+__global__ void __launch_bounds__(kCollideWarps * 32, PS_COLLIDE_MINB)
 k_collide_cells(CollideArgs a) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;

@@ -410,8 +410,11 @@ k_init_strip(Geom g, const XsJumpTable *__restrict__ jt, unsigned s0, long long 
 constexpr int kComCells = 2;  // consecutive cells per lane group
 constexpr int kComAhead = 4;  // rounds of every cell whose loads are issued before any is used
 
+#ifndef PS_COM_MINB
+#define PS_COM_MINB 4
+#endif
 template <int LANES>
-__global__ void k_com(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
+__global__ void __launch_bounds__(kThreads, PS_COM_MINB) k_com(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
                       const int *__restrict__ cell_start, double2 *__restrict__ com_xy,
                       double *__restrict__ com_m, unsigned long long *force_pairs) {
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
@@ -805,7 +808,10 @@ __device__ __forceinline__ bool is_close(double2 a, double2 b, double thr2) {
 
 // n = residents (+ guests that arrived from other strips, which have cell[i] = -1 and carry
 // their source cell in guest_src[i - n_res]).
-__global__ void __launch_bounds__(kThreads)
+#ifndef PS_FIND_MINB
+#define PS_FIND_MINB 6
+#endif
+__global__ void __launch_bounds__(kThreads, PS_FIND_MINB)
 k_collide_find(Geom g, int n, int n_res, double thr2, float thrf, const double2 *__restrict__ pos,
                const float2 *__restrict__ posf,
                const int *__restrict__ cell, const int *__restrict__ cell_start,

@@ -34,9 +34,15 @@ enum Fate : unsigned char {
 // Persistent blocks walk tiles of kThreads * kResolveRows entries, so the two contended global
 // counters cost one atomic per TILE (graveyard slots) and one per BLOCK (collision total)
 // instead of one per warp -- same-address atomics serialise in L2 at about 1 ns each.
-constexpr int kResolveRows = 8;
+#ifndef PS_RESOLVE_ROWS
+#define PS_RESOLVE_ROWS 4  // measured: 4 rows at 8 blocks per SM (32 registers) beat 8 rows at 4 blocks by 15-25 %
+#endif
+#ifndef PS_RESOLVE_MINB
+#define PS_RESOLVE_MINB 8
+#endif
+constexpr int kResolveRows = PS_RESOLVE_ROWS;
 
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, PS_RESOLVE_MINB)
 k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner, const int *__restrict__ cell,
           const int *__restrict__ newcell, const unsigned char *__restrict__ flags,
           const double2 *__restrict__ pos, const double2 *__restrict__ vel,
@@ -222,12 +228,16 @@ __device__ __forceinline__ void move_cell(const Geom &g, const MoveArgs &a, int 
         int before = 0;  // arrivals with a smaller id (shuffles stay outside divergent code)
         for (int j = 0; j < n_arr; j++) before += tile.shfl(my_aid, j) < me ? 1 : 0;
         if (ft == FATE_STAY) {
+            // the pointers of MoveArgs may alias as far as the compiler knows, so loads and stores
+            // issue in program order: the whole payload is in flight before the first store
+            const double2 pp = a.pos_in[k], vv = a.vel_in[k];
+            const double mm = a.m_in[k];
             int r = run + __popc(smask & lt) + before;
             for (int x = rest; x >= 0; x = a.mv_next[x]) r += a.id_in[x] < me ? 1 : 0;
             const int o = ns + r;
-            a.pos_out[o] = a.pos_in[k];
-            a.vel_out[o] = a.vel_in[k];
-            a.m_out[o] = a.m_in[k];
+            a.pos_out[o] = pp;
+            a.vel_out[o] = vv;
+            a.m_out[o] = mm;
             a.id_out[o] = me;
             a.cell_out[o] = c;
         }
