@@ -251,24 +251,27 @@ __device__ __forceinline__ void move_cell(const Geom &g, const MoveArgs &a, int 
 
     // arrivals: position = stayers with a smaller id + arrivals with a smaller id
     if (rest < 0) {
-        // all of them are in registers (lane q holds arrival q): no second walk of the bag
+        // all of them are in registers (lane q holds arrival q): no second walk of the bag, and
+        // the lanes move their arrivals together (one round of loads, then the stores)
+        int myo = -1;
         for (int q = 0; q < n_arr; q++) {
             const unsigned aid = tile.shfl(my_aid, q);
-            const int x = tile.shfl(my_arr, q);
             int r = __popc(tile.ballot(lane < n_arr && my_aid < aid));
             for (int base = s; base < e; base += LANES) {
                 const int k = base + lane;
                 const bool less = k < e && a.fate[k] == FATE_STAY && a.id_in[k] < aid;
                 r += __popc(tile.ballot(less));
             }
-            if (lane == 0) {
-                const int o = ns + r;
-                a.pos_out[o] = a.pos_in[x];
-                a.vel_out[o] = a.vel_in[x];
-                a.m_out[o] = a.m_in[x];
-                a.id_out[o] = aid;
-                a.cell_out[o] = c;
-            }
+            if (lane == q) myo = ns + r;
+        }
+        if (myo >= 0) {
+            const double2 pp = a.pos_in[my_arr], vv = a.vel_in[my_arr];
+            const double mm = a.m_in[my_arr];
+            a.pos_out[myo] = pp;
+            a.vel_out[myo] = vv;
+            a.m_out[myo] = mm;
+            a.id_out[myo] = my_aid;
+            a.cell_out[myo] = c;
         }
     } else {
         for (int x = a.mv_head[c]; x >= 0; x = a.mv_next[x]) {
