@@ -438,9 +438,10 @@ __global__ void __launch_bounds__(kThreads, PS_COM_MINB) k_com(Geom g, const dou
         }
     }
     unsigned long long pairs = 0;
+    double Ms[kComCells], Mxs[kComCells], Mys[kComCells];
 #pragma unroll
     for (int q = 0; q < kComCells; q++) {
-        const int c = c0 + q, s = b[q], e = b[q + 1];
+        const int s = b[q], e = b[q + 1];
         double M = 0, Mx = 0, My = 0;
 #pragma unroll
         for (int j = 0; j < kComAhead; j++) {
@@ -461,12 +462,24 @@ __global__ void __launch_bounds__(kThreads, PS_COM_MINB) k_com(Geom g, const dou
             Mx += __shfl_xor_sync(0xffffffffu, Mx, o);
             My += __shfl_xor_sync(0xffffffffu, My, o);
         }
-        if (lane == 0 && c < g.ncells) {
-            double2 r = make_double2(0.0, 0.0);
-            if (M > 0) r = make_double2(Mx / M, My / M);
-            com_xy[c + g.nc] = r;
-            com_m[c + g.nc] = M;
-            unsigned long long a = (unsigned long long)(e - s);
+        Ms[q] = M; Mxs[q] = Mx; Mys[q] = My;  // every lane of the group holds the totals
+    }
+    // The two divisions per cell are the long pole of this kernel (an FP64 division is ~40
+    // instructions and the whole warp steps through it): lanes 0..3 of the group do the four
+    // divisions of its two cells in ONE pass -- lane 2q + j divides component j of cell q.
+    static_assert(kComCells == 2 && LANES >= 4, "division layout");
+    {
+        const int q = (lane >> 1) & 1;
+        const double num = (lane & 1) ? (q ? Mys[1] : Mys[0]) : (q ? Mxs[1] : Mxs[0]);
+        const double den = q ? Ms[1] : Ms[0];
+        double val = 0.0;
+        if (lane < 4 && den > 0) val = num / den;
+        const double other = __shfl_down_sync(0xffffffffu, val, 1);
+        const int c = c0 + q;
+        if (lane < 4 && (lane & 1) == 0 && c < g.ncells) {
+            com_xy[c + g.nc] = make_double2(val, other);
+            com_m[c + g.nc] = den;
+            unsigned long long a = (unsigned long long)(q ? b[2] - b[1] : b[1] - b[0]);
             pairs += a * (a - 1);
         }
     }

@@ -194,6 +194,11 @@ static int stage_force(Rank *c) {
         case 1: PS_FORCE(2, 256, 0, 8); break;    // sparse cells: neighbourhood through L1
         case 3: PS_FORCE(8, 1280, 16, 5); break;  // deep unroll, 96 registers (comparison)
         case 4: PS_FORCE(4, 256, 0, 8); break;
+        case 5: PS_FORCE(2, 256, 0, 12); break;
+        case 6: PS_FORCE(2, 256, 0, 16); break;
+        case 7: PS_FORCE(2, 256, 64, 12); break;
+        case 8: PS_FORCE(4, 768, 16, 10); break;
+        case 9: PS_FORCE(4, 768, 16, 12); break;
         default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
         }
     });
