@@ -408,15 +408,20 @@ k_init_strip(Geom g, const XsJumpTable *__restrict__ jt, unsigned s0, long long 
 // the cell's (id-sorted) contents, never on scheduling or on the number of GPUs.
 // com_xy / com_m carry one ghost row above and below the strip: index = (local_row+1)*nc + gx.
 constexpr int kComCells = 2;  // consecutive cells per lane group
-constexpr int kComAhead = 4;  // rounds of every cell whose loads are issued before any is used
+// rounds of every cell whose loads are issued before any is used (fewer for narrow lane groups:
+// they are chosen for sparse cells, where the later rounds are mostly empty)
+#ifndef PS_COM_AHEAD_NARROW
+#define PS_COM_AHEAD_NARROW 2
+#endif
 
 #ifndef PS_COM_MINB
 #define PS_COM_MINB 4
 #endif
 template <int LANES>
-__global__ void __launch_bounds__(kThreads, PS_COM_MINB) k_com(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
+__global__ void __launch_bounds__(kThreads, LANES <= 8 ? 8 : PS_COM_MINB) k_com(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
                       const int *__restrict__ cell_start, double2 *__restrict__ com_xy,
                       double *__restrict__ com_m, unsigned long long *force_pairs) {
+    constexpr int kComAhead = LANES <= 8 ? PS_COM_AHEAD_NARROW : 4;
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     const int c0 = (t / LANES) * kComCells, lane = t % LANES;
     // Each lane group takes kComCells consecutive cells and has the first kComAhead rounds of all of
