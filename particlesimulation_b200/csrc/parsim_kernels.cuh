@@ -666,6 +666,18 @@ k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
         const int lrow = c / g.nc;
         const int gx = c - lrow * g.nc;
         const int grow = g.row0 + lrow;
+        if ((unsigned)(gx - 1) < (unsigned)(g.nc - 2) && (unsigned)(grow - 1) < (unsigned)(g.nc - 2)) {
+            // interior cell: no periodic shift, the eight neighbours sit at fixed offsets (same
+            // order as the general loop below: dx outer, dy inner)
+            const int base = c + g.nc;  // + the ghost row
+            const int off[8] = {-g.nc - 1, -1, g.nc - 1, -g.nc, g.nc, -g.nc + 1, 1, g.nc + 1};
+#pragma unroll
+            for (int j = 0; j < 8; j++) {
+                const double2 cm = __ldg(&com_xy[base + off[j]]);
+                const double M = __ldg(&com_m[base + off[j]]);
+                accumulate(cm.x - p.x, cm.y - p.y, M, ax, ay);
+            }
+        } else
 #pragma unroll
         for (int dxn = -1; dxn <= 1; dxn++) {
             int nx = gx + dxn;
