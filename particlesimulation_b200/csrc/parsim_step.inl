@@ -188,17 +188,12 @@ static int stage_force(Rank *c) {
     PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->n_movers, 0, sizeof(int), c->stream));
     // variant by current occupancy (cells fill up or empty out as the run goes on)
     int v = c->force_variant;
-    if (v <= 0) v = (double)c->n_alive < 12.0 * c->g.ncells ? 1 : 2;
+    if (v <= 0) v = (double)c->n_alive < 28.0 * c->g.ncells ? 1 : 2;  // measured crossover: about 30 per cell
     PS_LAUNCH(c, K_FORCE, 81.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate", {
         switch (v) {
-        case 1: PS_FORCE(2, 256, 0, 8); break;    // sparse cells: neighbourhood through L1
+        case 1: PS_FORCE(2, 256, 0, 16); break;   // sparse cells: neighbourhood through L1, 32 registers, full occupancy
         case 3: PS_FORCE(8, 1280, 16, 5); break;  // deep unroll, 96 registers (comparison)
-        case 4: PS_FORCE(4, 256, 0, 8); break;
-        case 5: PS_FORCE(2, 256, 0, 12); break;
-        case 6: PS_FORCE(2, 256, 0, 16); break;
-        case 7: PS_FORCE(2, 256, 64, 12); break;
-        case 8: PS_FORCE(4, 768, 16, 10); break;
-        case 9: PS_FORCE(4, 768, 16, 12); break;
+        case 4: PS_FORCE(2, 256, 0, 8); break;    // sparse cells at 64 registers (comparison)
         default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
         }
     });
