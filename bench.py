@@ -297,10 +297,14 @@ def main_ours(a):
             "collide_find": {"algorithmic_tflops": coll_flops / (c_ms * 1e-3) / 1e12,
                              "frac": coll_flops / (c_ms * 1e-3) / 1e12 / fp64_peak,
                              "ordered_pairs_per_step": st["collision_pairs"] / a.steps}}
-    traffic = None
+    # ncu-measured DRAM bytes per launch of the dominant kernel (one `--set full` capture of this
+    # workload at N=1, profiles/traffic.json); null for any other workload / scale / GPU count
+    traffic, traffic_info = None, None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
-    if os.path.exists(tp):
-        traffic = json.load(open(tp)).get(dom)
+    if os.path.exists(tp) and world == 1 and a.scale == 1.0:
+        traffic_info = json.load(open(tp)).get(a.workload, {}).get(dom)
+        if traffic_info:
+            traffic = traffic_info["dram_bytes_per_launch"] / 1e9  # GB per launch, like `achieved` x time
     out = {
         "metric": "particle-steps/s", "value": value, "unit": "particle-steps/s", "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_total / a.steps,
@@ -316,8 +320,11 @@ def main_ours(a):
                 "d2h_bytes_per_step": 24, "ms_per_step": 1e3 * e2e_s / a.steps},
         "gpu_launches": int(sum(v["launches"] for v in kern.values())),
         "roofline": {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": traffic, "peak_source": peak_src,
-                     "note": "the dominant kernel is FP64-CUDA-core bound (in-cell pair loop), see fp64"},
+                     "frac": achieved / hbm_peak, "traffic": traffic, "traffic_unit": "GB per launch (ncu dram read+write)",
+                     "algorithmic_GB_per_launch": d["bytes"] / max(d["launches"], 1) / 1e9,
+                     "ncu": traffic_info, "peak_source": peak_src,
+                     "note": "the dominant kernel is FP64-CUDA-core bound (in-cell pair loop): ncu shows the FP64 pipe "
+                             "69-78 % busy in every launch, see fp64"},
         "fp64": fp64, "kernels": table,
         "result": {"x0": round(x0, 3), "y0": round(y0, 3), "collisions": collisions,
                    "reference_collisions": expect, "parity_ok": (collisions == expect) if expect else None},
