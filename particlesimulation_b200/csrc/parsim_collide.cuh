@@ -52,6 +52,16 @@ __device__ __forceinline__ int sub_bin(const CollideArgs &a, double2 p, double x
     return by * a.nb + bx;
 }
 
+// warp kernel: rows of the sub-grid are always 16 bins apart (a.nb <= 16; the unused bins stay
+// empty), so row and column of a bin are a shift and a mask instead of a division
+__device__ __forceinline__ int sub_bin16(const CollideArgs &a, double2 p, double x0, double y0) {
+    int bx = __double2int_rd((p.x - x0) * a.inv_h);
+    int by = __double2int_rd((p.y - y0) * a.inv_h);
+    bx = min(max(bx, 0), a.nb - 1);
+    by = min(max(by, 0), a.nb - 1);
+    return (by << 4) | bx;
+}
+
 template <int G>
 __device__ __forceinline__ void group_sync() {
     if (G == 32) __syncwarp(); else __syncthreads();
@@ -352,7 +362,7 @@ k_collide_cells(CollideArgs a) {
             for (int j = 0; j < IT; j++) {
                 br[j] = -1;
                 if (!(f[j] & F_REMOVED)) {
-                    const int b = sub_bin(a, p[j], x0, y0);
+                    const int b = sub_bin16(a, p[j], x0, y0);
                     br[j] = (b << 16) | atomicAdd(&start[b], 1);
                 } else if (f[j] & F_EMIGRANT) {
                     a.partner[s + lane + 32 * j] = -1;  // checked on the strip it moved to
@@ -360,7 +370,7 @@ k_collide_cells(CollideArgs a) {
             }
             br[IT] = -1;
             if (ax >= 0) {
-                const int b = sub_bin(a, p[IT], x0, y0);
+                const int b = sub_bin16(a, p[IT], x0, y0);
                 br[IT] = (b << 16) | atomicAdd(&start[b], 1);
             }
             __syncwarp();
@@ -380,9 +390,9 @@ k_collide_cells(CollideArgs a) {
                 const int b = br[j] >> 16;
                 const int o = start[b] + (br[j] & 0xffff);
                 const unsigned my = j < IT ? (unsigned)(lane + 32 * j) : (0x80000000u | aord);
-                const int by = b / a.nb, bx = b - by * a.nb;
+                const int by = b >> 4, bx = b & 15;
                 // rest of the own bin and the next bin of the row
-                int q0 = o + 1, q1 = start[by * a.nb + min(bx + 1, a.nb - 1) + 1];
+                int q0 = o + 1, q1 = start[(by << 4) + min(bx + 1, a.nb - 1) + 1];
                 for (int r = 0; r < 2; r++) {
                     tested += q1 - q0;
                     for (int q = q0; q < q1; q++) {
@@ -392,8 +402,8 @@ k_collide_cells(CollideArgs a) {
                         }
                     }
                     if (by + 1 >= a.nb) break;
-                    q0 = start[(by + 1) * a.nb + max(bx - 1, 0)];
-                    q1 = start[(by + 1) * a.nb + min(bx + 1, a.nb - 1) + 1];
+                    q0 = start[((by + 1) << 4) + max(bx - 1, 0)];
+                    q1 = start[((by + 1) << 4) + min(bx + 1, a.nb - 1) + 1];
                 }
             }
             __syncwarp();
