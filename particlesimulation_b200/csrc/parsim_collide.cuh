@@ -379,6 +379,7 @@ k_collide_cells(CollideArgs a) {
             for (int j = 0; j <= IT; j++) {
                 if (br[j] >= 0) {
                     const int o = start[br[j] >> 16] + (br[j] & 0xffff);
+                    br[j] = (br[j] & ~0xffff) | o;  // from here on: bin << 16 | slot in bin order
                     spos[o] = p[j];
                     sord[o] = j < IT ? (unsigned)(lane + 32 * j) : (0x80000000u | aord);
                 }
@@ -388,7 +389,7 @@ k_collide_cells(CollideArgs a) {
             for (int j = 0; j <= IT; j++) {
                 if (br[j] < 0) continue;
                 const int b = br[j] >> 16;
-                const int o = start[b] + (br[j] & 0xffff);
+                const int o = br[j] & 0xffff;
                 const unsigned my = j < IT ? (unsigned)(lane + 32 * j) : (0x80000000u | aord);
                 const int by = b >> 4, bx = b & 15;
                 // rest of the own bin and the next bin of the row
@@ -410,7 +411,7 @@ k_collide_cells(CollideArgs a) {
 #pragma unroll
             for (int j = 0; j <= IT; j++) {
                 if (br[j] < 0) continue;
-                const int o = start[br[j] >> 16] + (br[j] & 0xffff);
+                const int o = br[j] & 0xffff;
                 const unsigned w = best[o];
                 const int idx = w == 0xffffffffu ? -1 : (w & 0x80000000u) ? arr_idx[w & 0x7fffffffu] : s + (int)w;
                 a.partner[j < IT ? s + lane + 32 * j : ax] = idx;
