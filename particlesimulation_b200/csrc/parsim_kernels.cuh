@@ -121,27 +121,18 @@ __device__ __forceinline__ void store_rec(InitRec *rec, int slot, double2 p, dou
     q[2] = make_double2(m, __hiloint2double(0, (int)id));  // id in the low word of the 4th double
 }
 
-// Upload: interleave host SoA (x,y,vx,vy,m) into records and keep the particles of this strip.
-// Single strip: slot = id (id order).  Several strips: claimed slots (any order).
+// Upload on a single strip: interleave host SoA (x,y,vx,vy,m) into records, slot = id.
+// (Several strips: k_ingest_strip below keeps the strip's particles, in id order.)
 __global__ void k_ingest(Geom g, long long id_base, const unsigned *__restrict__ ids, int count,
                          const double *__restrict__ x,
                          const double *__restrict__ y, const double *__restrict__ vx,
                          const double *__restrict__ vy, const double *__restrict__ m,
-                         int single_rank, int capacity, InitRec *rec, Counters *ctr) {
+                         int capacity, InitRec *rec, Counters *ctr) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= count) return;
-    double2 p = make_double2(x[t], y[t]);
-    int slot;
     const unsigned pid = ids ? ids[t] : (unsigned)(id_base + t);
-    if (single_rank) {
-        slot = (int)pid;
-    } else {
-        int row = cell_coord(p.y, g);
-        if (row < g.row0 || row >= g.row0 + g.rows) return;
-        slot = atomicAdd(&ctr->n_staged, 1);
-        if (slot >= capacity) { ctr->error = DE_CAPACITY; return; }
-    }
-    store_rec(rec, slot, p, make_double2(vx[t], vy[t]), m[t], pid);
+    if (pid >= (unsigned)capacity) { ctr->error = DE_CAPACITY; return; }
+    store_rec(rec, (int)pid, make_double2(x[t], y[t]), make_double2(vx[t], vy[t]), m[t], pid);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -173,8 +164,9 @@ __device__ __forceinline__ double xs_draw(unsigned &s) {
     return __dadd_rn(0.5, __dmul_rn(0.2328306e-09, (double)sum));  // no FMA: reference rounding
 }
 
+// (single strip: slot = id; several strips use k_init_strip below)
 __global__ void k_init_particles(Geom g, const XsJumpTable *__restrict__ jt, unsigned s0, long long n_part,
-                                 int single_rank, int capacity, InitRec *rec, Counters *ctr) {
+                                 InitRec *rec) {
     const long long T = (long long)gridDim.x * blockDim.x;
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_part) return;
@@ -193,16 +185,7 @@ __global__ void k_init_particles(Geom g, const XsJumpTable *__restrict__ jt, uns
         double m = __dmul_rn(__ddiv_rn(__ddiv_rn(__dmul_rn(__dmul_rn(xs_draw(s), 0.01), cc), nd), kG),
                              0.005 * 0.005);
         s = xs_apply(jt->stride, s);
-        int slot;
-        if (single_rank) {
-            slot = (int)i;
-        } else {
-            int row = cell_coord(y, g);
-            if (row < g.row0 || row >= g.row0 + g.rows) continue;
-            slot = atomicAdd(&ctr->n_staged, 1);
-            if (slot >= capacity) { ctr->error = DE_CAPACITY; continue; }
-        }
-        store_rec(rec, slot, make_double2(x, y), make_double2(vx, vy), m, (unsigned)i);
+        store_rec(rec, (int)i, make_double2(x, y), make_double2(vx, vy), m, (unsigned)i);
     }
 }
 

@@ -265,7 +265,7 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
             PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest",
                       k_ingest<<<grid_for(cnt), kThreads, 0, c->stream>>>(
                           c->g, id_base + off, dids, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
-                          c->stage[4], 1, c->cap, c->rec0, c->d_ctr));
+                          c->stage[4], c->cap, c->rec0, c->d_ctr));
         } else {  // stable compaction of this strip's particles: count, scan, write
             const int nb = grid_for(cnt);
             PS_LAUNCH(c, K_INGEST, 8.0 * cnt, "k_ingest_strip<0>",
@@ -395,7 +395,7 @@ int rank_init_device(Rank *c, long seed) {
     if (!strips) {
         PS_LAUNCH(c, K_INIT, 44.0 * c->n_part, "k_init_particles",
                   k_init_particles<<<blocks, kThreads, 0, c->stream>>>(
-                      c->g, d_jt, s0, c->n_part, 1, c->cap, c->rec0, c->d_ctr));
+                      c->g, d_jt, s0, c->n_part, c->rec0));
     } else {  // every strip walks the whole stream and keeps its rows, in id order
         const int nb = grid_for(c->n_part, kThreads * kInitPer);
         PS_LAUNCH(c, K_INIT, 0.0, "k_init_strip<0>",

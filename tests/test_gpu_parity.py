@@ -336,6 +336,66 @@ def test_reset_and_id_upload_reproduce_the_run():
     a.close(); b.close()
 
 
+def test_upload_rejects_out_of_range_ids():
+    n = 1000
+    x, y, vx, vy, m = init_particles(1, 10, 100, n)
+    ids = np.arange(n, dtype=np.uint32)
+    ids[5] = 5 * n
+    g = ParticleSimulation(1, 10, 100, n, upload=False)
+    with pytest.raises(Exception):
+        g.upload_strip_ptrs(n, ids.ctypes.data, [v.ctypes.data for v in (x, y, vx, vy, m)])
+        g.simulate(1)
+    g.close()
+
+
+@pytest.mark.parametrize("args", [(1, 1, 1, 1, 3), (2, 5, 1, 2, 4), (3, 1, 2, 1, 2), (4, 7, 3, 2, 0), (5, 0.02, 2, 40, 3),
+                                  (6, 1, 30, 3, 5), (-2, 3, 5, 1, 2)], ids=lambda a: " ".join(map(str, a)))
+def test_degenerate_sizes_match_oracle(args):
+    """One particle, one cell, more cells than particles, zero steps, a box a few EPSILON wide
+    (everything collides): same answers as the oracle, bit-exact counts and alive flags."""
+    seed, side, nc, n, steps = args
+    g = ParticleSimulation(seed, side, nc, n)
+    o = ol.oracle_sim(seed, side, nc, n)
+    g.simulate(steps)
+    o.run(steps)
+    d, p = g.dump(), o.particles()
+    assert g.result()[2] == o.collisions
+    assert np.array_equal(d["alive"], p["alive"])
+    for k in ("x", "y", "vx", "vy"):
+        assert np.allclose(d[k], p[k], rtol=0, atol=1e-9 * side), k
+    x0, y0, _ = g.result()
+    assert abs(x0 - p["x"][0]) <= 1e-9 * side and abs(y0 - p["y"][0]) <= 1e-9 * side
+    g.close(); o.close()
+
+
+def test_full_size_properties():
+    """Size-independent properties at BASELINE config 3's full size (1e8 particles), where the
+    oracle cannot follow: the (cell, id) layout invariant after the run, alive + dead = n, every
+    collision kills at least two, a second run from the resident state repeats the first bit for
+    bit, and the count equals the serial reference's committed golden."""
+    n, steps = 100_000_000, 10
+    g = ParticleSimulation(7, 100.0, 1000, n, device_init=True, options={"keep_initial": 1, "stats": 1})
+    g.simulate(steps)
+    x0, y0, col = g.result()
+    golden = [r for r in RUNS if r["args"] == ["7", "100", "1000", "100000000", "10"]][0]
+    assert col == golden["collisions"] and f"{x0:.3f}" == golden["x0"] and f"{y0:.3f}" == golden["y0"]
+    ids, x, y, vx, vy, m = g.download()  # device order
+    deaths = g.stats()["deaths"]
+    assert len(ids) + deaths == n and deaths >= 2 * col
+    cw = 100.0 / 1000
+    cell = np.clip((y / cw).astype(np.int64), 0, 999) * 1000 + np.clip((x / cw).astype(np.int64), 0, 999)
+    key = cell * (1 << 32) + ids.astype(np.int64)
+    assert np.all(np.diff(key) > 0)  # sorted by (cell, id), no duplicates
+    assert np.all(m > 0) and np.all((x >= 0) & (x < 100.0) & (y >= 0) & (y < 100.0))
+    del x, y, vx, vy, m, cell, key
+    g.reset()
+    g.simulate(steps)
+    assert g.result() == (x0, y0, col)
+    ids2 = g.download()[0]
+    assert np.array_equal(ids, ids2)
+    g.close()
+
+
 def test_stats_counters():
     g = ParticleSimulation(1, 10, 100, 100000, options={"stats": 1})
     g.simulate(3)
