@@ -34,9 +34,10 @@ WORKLOADS = {
     "config4w": (3, 354.0, 3536, 100_000_000, 10, 6103556),  # config 4 density, 1e8 per GPU
 }
 CONFIG4_SERIES = {2: (500.0, 5000, 200_000_000), 4: (707.0, 7071, 400_000_000), 8: (1000.0, 10000, 800_000_000)}
-# bounded CPU sample of the same density (ppc = 100, cell = 0.1): config 3 at 1/100 size
-CPU_SAMPLE = {"config3": "7 10 100 1000000 10", "config2": "1 10 100 1000000 20",
-              "config4w": "3 35.4 354 1000000 10"}
+# bounded CPU sample of the same density and cell size (config 3: ppc = 100, cell = 0.1, 1/16 of the
+# particles: 10-30 s on one host core, a few seconds with every core under OpenMP)
+CPU_SAMPLE = {"config3": "7 25 250 6250000 10", "config2": "1 10 100 1000000 20",
+              "config4w": "3 88.4 884 6250000 10"}
 
 
 def workload_for(name, n_gpus, scale):
@@ -131,12 +132,12 @@ def run_reference_binary(binary, sample, threads):
     except Exception:
         secs = wall
     n, steps = int(sample.split()[3]), int(sample.split()[4])
-    return n * steps / secs, secs, p.stdout.split()
+    return n * steps / secs, secs, p.stdout.split()[-3:]  # x0 y0 collisions (the OpenMP build also prints PANIC lines)
 
 
 def cpu_baseline(workload, threads=1):
     """The reference's own CPU code on this box's host cores, on a bounded sample of the workload
-    (same particles-per-cell and cell size, 1/100 of the particles)."""
+    (same particles-per-cell and cell size, 1/16 of the particles: 10-30 s on one core)."""
     sample = CPU_SAMPLE[workload]
     ref = os.path.join(ROOT, "oracle", "_ref", "parsim-omp" if threads > 1 else "parsim")
     kind = "reference"
@@ -146,7 +147,8 @@ def cpu_baseline(workload, threads=1):
             subprocess.run(["make", "-C", os.path.join(ROOT, "oracle")], check=True, capture_output=True)
     v, secs, out = run_reference_binary(ref, sample, threads)
     return {"value": v, "unit": "particle-steps/s", "cores": threads, "kind": kind,
-            "sample": f"{os.path.basename(ref)} {sample} ({secs:.1f} s; same density, 1/100 of the particles)",
+            "sample": f"{os.path.basename(ref)} {sample} ({secs:.1f} s; same particles per cell and cell size as the "
+                      f"workload, {int(sample.split()[3]) / WORKLOADS[workload][3]:.4g} of its particles)",
             "stdout": out}
 
 
@@ -233,8 +235,6 @@ def main_ours(a):
     clocks.start()  # before the warm-up: nvidia-smi takes a while to come up on an 8-GPU box
     for _ in range(a.warmup):
         one_run()
-    sim.set_option("stats", 1)
-    sim.stats_reset()
     barrier()
     clocks.mark()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -245,8 +245,20 @@ def main_ours(a):
     barrier()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
     clk = clocks.stop()
-    st = sim.stats()
     x0, y0, collisions = sim.result()
+    # the per-kernel table comes from a second, instrumented pass over the same K runs (CUDA events
+    # around every launch and the pair counters cost a little, so they stay out of `value`)
+    sim.set_option("stats", 1)
+    sim.stats_reset()
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record(stream)
+    for _ in range(a.steps):
+        one_run()
+    s1.record(stream)
+    barrier()
+    ms_stats = max_over_ranks(s0.elapsed_time(s1))
+    st = sim.stats()
+    assert sim.result()[2] == collisions, "instrumented pass disagrees with the timed pass"
     sim.set_option("stats", 0)
     work = float(n) * nstep
     value = work * a.steps / (ms_total / 1e3)
@@ -308,6 +320,7 @@ def main_ours(a):
     out = {
         "metric": "particle-steps/s", "value": value, "unit": "particle-steps/s", "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_total / a.steps,
+        "ms_per_step_instrumented": ms_stats / a.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": f"synthetic (seeded init_particles, seed {seed}, generated on the device)",
         "config": {"workload": f"{a.workload}: seed={seed} side={side:g} ncside={nc} n_part={n} n_step={nstep}"
@@ -331,9 +344,14 @@ def main_ours(a):
         "counters": {k: st[k] / a.steps for k in ("movers", "strays", "deaths", "migrants", "alive_particle_steps")},
     }
     if world == 1 and not a.no_cpu_baseline:
+        # north_star: the reference's serial, OpenMP and MPI builds on this box's host cores, same run
         cb = cpu_baseline(a.workload, 1)
         cb.pop("stdout", None)
         out["cpu_baseline"] = cb
+        omp = cpu_baseline(a.workload, os.cpu_count() or 1)
+        omp.pop("stdout", None)
+        out["cpu_baseline_openmp"] = omp
+        out["cpu_baseline_mpi"] = "unavailable on this box (no mpic++ / mpi.h / mpirun in the image)"
     print(json.dumps(out))
 
 

@@ -55,6 +55,15 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     if (device < 0 || device >= ndev) return c->fail("CUDA device index out of range");
     PS_CUDA(c, cudaSetDevice(device));
     PS_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    if (const char *e = getenv("PARSIM_L2_FETCH")) {
+        // measurement switch: cap the L2 fetch granularity (32 / 64 / 128 bytes) -- the step-0 gather
+        // reads one random 64-byte record per particle and ncu shows 128 bytes of DRAM traffic for
+        // each.  A hint only: the driver may ignore it, so failure is not an error.
+        const int gran = atoi(e);
+        if (gran == 32 || gran == 64 || gran == 128) {
+            if (cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)gran) != cudaSuccess) cudaGetLastError();
+        }
+    }
 
     Geom &g = c->g;
     g.side = side;
