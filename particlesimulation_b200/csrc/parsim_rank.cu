@@ -55,15 +55,6 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     if (device < 0 || device >= ndev) return c->fail("CUDA device index out of range");
     PS_CUDA(c, cudaSetDevice(device));
     PS_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
-    if (const char *e = getenv("PARSIM_L2_FETCH")) {
-        // measurement switch: cap the L2 fetch granularity (32 / 64 / 128 bytes) -- the step-0 gather
-        // reads one random 64-byte record per particle and ncu shows 128 bytes of DRAM traffic for
-        // each.  A hint only: the driver may ignore it, so failure is not an error.
-        const int gran = atoi(e);
-        if (gran == 32 || gran == 64 || gran == 128) {
-            if (cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)gran) != cudaSuccess) cudaGetLastError();
-        }
-    }
 
     Geom &g = c->g;
     g.side = side;
@@ -206,9 +197,15 @@ void rank_destroy(Rank *c) {
                     c->mv_head, c->dm_head, c->mv_next, c->fate, c->grave_pos, c->grave_vel, c->grave_id,
                     c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->posf, c->rec0,
                     c->big_cells, c->d_big_count, c->huge_items, c->move_big_list, c->d_move_big_count, c->arr_cnt, c->arr_rec,
-                    c->stage_ids, c->stage[0],
-                    c->stage[1], c->stage[2], c->stage[3], c->stage[4]};
+                    c->stage_ids[0], c->stage_ids[1], c->stage[0][0], c->stage[0][1], c->stage[0][2],
+                    c->stage[0][3], c->stage[0][4], c->stage[1][0], c->stage[1][1], c->stage[1][2],
+                    c->stage[1][3], c->stage[1][4]};
     for (void *p : ptrs) if (p) cudaFree(p);
+    if (c->copy_stream) { cudaStreamSynchronize(c->copy_stream); cudaStreamDestroy(c->copy_stream); }
+    for (int b = 0; b < 2; b++) {
+        if (c->ev_copied[b]) cudaEventDestroy(c->ev_copied[b]);
+        if (c->ev_ingested[b]) cudaEventDestroy(c->ev_ingested[b]);
+    }
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
     for (auto &t : c->pending) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     for (auto &e : c->event_pool) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
@@ -243,8 +240,10 @@ static int reset_state(Rank *c) {
 
 int rank_upload_begin(Rank *c) {
     PS_CUDA(c, cudaSetDevice(c->device));
+    PS_CUDA(c, cudaStreamSynchronize(c->stream));  // an abandoned upload may still be reading the staging sets
     if (reset_state(c)) return 1;
     c->uploading = true;
+    c->stage_pieces = 0;
     return 0;
 }
 
@@ -254,43 +253,60 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
     if (count < 0 || (!ids && (id_base < 0 || id_base + count > c->n_part)))
         return c->fail("upload chunk outside [0, n_part)");
     PS_CUDA(c, cudaSetDevice(c->device));
-    const long long piece = 1 << 24;  // 16 Mi particles per staging pass (5 x 128 MiB)
-    if (!c->stage[0]) {
+    // Staging passes of 8 Mi particles (5 x 64 MiB per set).  The host->device copies of a pass run
+    // on copy_stream into one staging set while k_ingest (on the step stream) interleaves the
+    // previous pass out of the other set, so the copy engine never waits for a kernel.
+    const long long piece = 1 << 23;
+    if (!c->stage[0][0]) {
         c->stage_cap = (int)std::min<long long>(piece, c->n_part);
-        for (int k = 0; k < 5; k++) PS_ALLOC(c, c->stage[k], c->stage_cap, false);
-        PS_ALLOC(c, c->stage_ids, c->stage_cap, false);
+        for (int b = 0; b < 2; b++) {
+            for (int k = 0; k < 5; k++) PS_ALLOC(c, c->stage[b][k], c->stage_cap, false);
+            PS_ALLOC(c, c->stage_ids[b], c->stage_cap, false);
+            PS_CUDA(c, cudaEventCreateWithFlags(&c->ev_copied[b], cudaEventDisableTiming));
+            PS_CUDA(c, cudaEventCreateWithFlags(&c->ev_ingested[b], cudaEventDisableTiming));
+        }
+        PS_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
     }
     const double *src[5] = {x, y, vx, vy, m};
     for (long long off = 0; off < count; off += c->stage_cap) {
-        int cnt = (int)std::min<long long>(c->stage_cap, count - off);
+        const int cnt = (int)std::min<long long>(c->stage_cap, count - off);
+        const int b = (int)(c->stage_pieces & 1);
+        double *const *st = c->stage[b];
+        // the set is free once the k_ingest of two passes ago has read it
+        if (c->stage_pieces >= 2) PS_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_ingested[b], 0));
         for (int k = 0; k < 5; k++)
-            PS_CUDA(c, cudaMemcpyAsync(c->stage[k], src[k] + off, sizeof(double) * cnt,
-                                       cudaMemcpyHostToDevice, c->stream));
+            PS_CUDA(c, cudaMemcpyAsync(st[k], src[k] + off, sizeof(double) * cnt, cudaMemcpyHostToDevice,
+                                       c->copy_stream));
         if (ids)
-            PS_CUDA(c, cudaMemcpyAsync(c->stage_ids, ids + off, sizeof(unsigned) * cnt,
-                                       cudaMemcpyHostToDevice, c->stream));
-        const unsigned *dids = ids ? c->stage_ids : nullptr;
+            PS_CUDA(c, cudaMemcpyAsync(c->stage_ids[b], ids + off, sizeof(unsigned) * cnt,
+                                       cudaMemcpyHostToDevice, c->copy_stream));
+        PS_CUDA(c, cudaEventRecord(c->ev_copied[b], c->copy_stream));
+        PS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[b], 0));
+        const unsigned *dids = ids ? c->stage_ids[b] : nullptr;
         if (c->nranks == 1) {
             PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest",
                       k_ingest<<<grid_for(cnt), kThreads, 0, c->stream>>>(
-                          c->g, id_base + off, dids, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
-                          c->stage[4], c->cap, c->rec0, c->d_ctr));
+                          c->g, id_base + off, dids, cnt, st[0], st[1], st[2], st[3], st[4], c->cap, c->rec0,
+                          c->d_ctr));
         } else {  // stable compaction of this strip's particles: count, scan, write
             const int nb = grid_for(cnt);
             PS_LAUNCH(c, K_INGEST, 8.0 * cnt, "k_ingest_strip<0>",
                       k_ingest_strip<0><<<nb, kThreads, 0, c->stream>>>(
-                          c->g, id_base + off, dids, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
-                          c->stage[4], c->cap - 2 * c->mig_cap, c->sort_hist, c->rec0, c->d_ctr));
+                          c->g, id_base + off, dids, cnt, st[0], st[1], st[2], st[3], st[4],
+                          c->cap - 2 * c->mig_cap, c->sort_hist, c->rec0, c->d_ctr));
             if (device_scan(c, c->sort_hist, nb, c->sort_hist_scan, nullptr)) return 1;
             PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest_strip<1>",
                       k_ingest_strip<1><<<nb, kThreads, 0, c->stream>>>(
-                          c->g, id_base + off, dids, cnt, c->stage[0], c->stage[1], c->stage[2], c->stage[3],
-                          c->stage[4], c->cap - 2 * c->mig_cap, c->sort_hist_scan, c->rec0, c->d_ctr));
+                          c->g, id_base + off, dids, cnt, st[0], st[1], st[2], st[3], st[4],
+                          c->cap - 2 * c->mig_cap, c->sort_hist_scan, c->rec0, c->d_ctr));
             k_advance_staged<<<1, 1, 0, c->stream>>>(c->d_ctr, c->sort_hist_scan + nb);
         }
-        // the staging buffers are reused by the next piece
-        PS_CUDA(c, cudaStreamSynchronize(c->stream));
+        PS_CUDA(c, cudaEventRecord(c->ev_ingested[b], c->stream));
+        c->stage_pieces++;
     }
+    // the caller's arrays are free again when this returns ("they are copied"); the ingest kernels
+    // may still be running -- parsim_upload_end waits for them
+    PS_CUDA(c, cudaStreamSynchronize(c->copy_stream));
     c->n_uploaded += count;
     return 0;
 }

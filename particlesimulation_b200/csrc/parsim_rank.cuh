@@ -92,9 +92,13 @@ struct Rank {
     int *d_found = nullptr;
 
     // upload staging
-    double *stage[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-    unsigned *stage_ids = nullptr;
+    // two staging sets: the copy engine fills one (copy_stream) while k_ingest reads the other
+    double *stage[2][5] = {{nullptr, nullptr, nullptr, nullptr, nullptr}, {nullptr, nullptr, nullptr, nullptr, nullptr}};
+    unsigned *stage_ids[2] = {nullptr, nullptr};
     int stage_cap = 0;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_ingested[2] = {nullptr, nullptr};
+    long long stage_pieces = 0;  // staging passes since upload_begin (set = pass & 1)
     long long n_uploaded = 0;
     // the uploaded state (one 64-byte record per slot, parsim_kernels.cuh); the step-0 sort reads
     // it and never modifies it, so parsim_reset only rewinds the bookkeeping
