@@ -113,6 +113,20 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
         }
     }
     if (const char *e = getenv("PARSIM_FORCE_VARIANT")) c->force_variant = atoi(e);
+    if (c->force_variant == 5 || c->force_variant == 6) {  // persistent tile pipeline (parsim_force_tiles.cuh)
+        const int sh = (int)force_tiles_smem();
+        int per_sm = 0, sms = 0;
+        PS_CUDA(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+        if (c->force_variant == 5) {
+            PS_CUDA(c, cudaFuncSetAttribute(k_force_tiles<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, sh));
+            PS_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_force_tiles<4>, kFtThreads, sh));
+        } else {
+            PS_CUDA(c, cudaFuncSetAttribute(k_force_tiles<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, sh));
+            PS_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_force_tiles<8>, kFtThreads, sh));
+        }
+        if (per_sm < 1) return c->fail("k_force_tiles does not fit an SM");
+        c->ft_grid = sms * per_sm;
+    }
     if (const char *e = getenv("PARSIM_CAPACITY_PCT")) {
         double pct = atof(e);
         if (pct >= 100) c->capacity_factor = pct / 100.0;
@@ -148,10 +162,10 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
         PS_ALLOC(c, c->huge_items, N / kThreads + 2 * C + 16, false);
         PS_ALLOC(c, c->arr_cnt, C, true); PS_ALLOC(c, c->arr_rec, C * kArrSlots, false);
     }
-    PS_ALLOC(c, c->m_cur, N, false);   PS_ALLOC(c, c->m_alt, N, false);
+    PS_ALLOC(c, c->m_cur, N + kFtPad, false);   PS_ALLOC(c, c->m_alt, N + kFtPad, false);  // + the bulk-copy windows
     PS_ALLOC(c, c->id_cur, N, false);  PS_ALLOC(c, c->id_alt, N, false);
-    PS_ALLOC(c, c->cell_cur, N, false); PS_ALLOC(c, c->cell_alt, N, false);
-    PS_ALLOC(c, c->cs_cur, C + 1, true); PS_ALLOC(c, c->cs_alt, C + 1, true);
+    PS_ALLOC(c, c->cell_cur, N + kFtPad, false); PS_ALLOC(c, c->cell_alt, N + kFtPad, false);
+    PS_ALLOC(c, c->cs_cur, C + 1 + kFtPad, true); PS_ALLOC(c, c->cs_alt, C + 1 + kFtPad, true);
     PS_ALLOC(c, c->count, C, true);
     const size_t H = (size_t)kSortMaxBins * (N / kSortTile + 1);  // radix-sort tile histograms
     PS_ALLOC(c, c->tile_sums, std::max(C, H) / kScanTile + 2, true);
