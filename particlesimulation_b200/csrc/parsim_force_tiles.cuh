@@ -17,8 +17,15 @@
 // buffer back on its "empty" mbarrier and only then do the integration and the global stores, so
 // neither a block-wide barrier nor a global load sits in front of the FP64-bound loop.
 //
-// Selected with PARSIM_FORCE_VARIANT=5 (pair loop unrolled 4 times) or 6 (8 times); NOT the
-// default until it has been measured on a B200.
+// Selected with PARSIM_FORCE_VARIANT=5 (pair loop unrolled 4 times, 768-source buffers, 4 blocks per
+// SM at 96 registers), 6 (unrolled 8 times) or 7 (448-source buffers, 6 blocks per SM at 64
+// registers).  Measured on B200 (config 3, profiles/bench_r01_v11_fv*.json): results identical to
+// the default (all GPU parity tests, 29 214 105 collisions at 1e8 particles), but 33.1 / 32.7 /
+// 32.8 ms per run for variants 5 / 6 / 7 against 28.8 ms of k_force_integrate.  The three agree
+// although their occupancy and unrolling differ, so the limit is common to them -- most likely the
+// producer's chain per tile (two dependent index loads, the neighbourhood loads, five small bulk
+// copies) with only one tile of look-ahead, which the thin later timesteps (30 per cell, about
+// 1.5 us of pair work per tile) cannot hide.  NOT the default; deeper look-ahead is the next step.
 #pragma once
 #include "parsim_kernels.cuh"
 
@@ -26,7 +33,6 @@ namespace parsim {
 
 constexpr int kFtTargets = 128;               // targets per tile = consumer threads per block
 constexpr int kFtThreads = kFtTargets + 32;   // + the producer warp
-constexpr int kFtTile = 768;                  // staged sources per tile
 constexpr int kFtCells = 16;                  // cells per tile whose neighbourhood is staged
 constexpr int kFtCs = 144;                    // staged cell_start entries (16-byte aligned window)
 
@@ -35,20 +41,23 @@ constexpr int kFtCs = 144;                    // staged cell_start entries (16-b
 // past the part that is used; rank_create pads m, cell and cell_start accordingly (kFtPad).
 constexpr int kFtPad = 8;
 
+template <int TILE>  // staged sources per tile
 struct __align__(16) FtBuf {
-    double2 pos[kFtTile];        // sources r0 .. r1
+    double2 pos[TILE];           // sources r0 .. r1
     double2 vel[kFtTargets];     // velocities of the tile's targets
     double2 nxy[kFtCells * 8];   // shifted neighbour centres of mass, 8 per cell of the tile
-    double m[kFtTile + 2];       // masses from m_base = r0 rounded down to even
+    double m[TILE + 2];          // masses from m_base = r0 rounded down to even
     double nm[kFtCells * 8];
     int cell[kFtTargets];        // cells of the tile's targets
     int cs[kFtCs];               // cell_start from cs_base = first cell rounded down to a multiple of 4
     int r0, r1, m_base, cs_base, cf, ncb, flags, pad;
 };
-static_assert(sizeof(FtBuf) % 16 == 0, "FtBuf must keep its members 16-byte aligned in an array");
+static_assert(sizeof(FtBuf<768>) % 16 == 0 && sizeof(FtBuf<448>) % 16 == 0,
+              "FtBuf must keep its members 16-byte aligned in an array");
 enum { FT_SRC = 1, FT_NB = 2, FT_CS = 4 };  // FtBuf::flags: what was staged for this tile
 
-inline size_t force_tiles_smem() { return 2 * sizeof(FtBuf) + 4 * sizeof(unsigned long long); }
+template <int TILE>
+inline size_t force_tiles_smem() { return 2 * sizeof(FtBuf<TILE>) + 4 * sizeof(unsigned long long); }
 
 __device__ __forceinline__ unsigned ft_smem(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
@@ -79,8 +88,8 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
                    "r"(ft_smem(bar)) : "memory");
 }
 
-template <int UNROLL>
-__global__ void __launch_bounds__(kFtThreads, 4)
+template <int UNROLL, int TILE, int MINB>
+__global__ void __launch_bounds__(kFtThreads, MINB)
 k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *__restrict__ m,
               const int *__restrict__ cell, const int *__restrict__ cell_start,
               const double2 *__restrict__ com_xy, const double *__restrict__ com_m,
@@ -88,8 +97,9 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
               int *__restrict__ newcell, unsigned char *__restrict__ flags, int *__restrict__ mover_list,
               int *n_movers, double2 *__restrict__ dbg_acc) {
     extern __shared__ __align__(16) unsigned char ft_raw[];
-    FtBuf *buf = reinterpret_cast<FtBuf *>(ft_raw);
-    unsigned long long *full = reinterpret_cast<unsigned long long *>(ft_raw + 2 * sizeof(FtBuf));
+    typedef FtBuf<TILE> Buf;
+    Buf *buf = reinterpret_cast<Buf *>(ft_raw);
+    unsigned long long *full = reinterpret_cast<unsigned long long *>(ft_raw + 2 * sizeof(Buf));
     unsigned long long *empty = full + 2;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ntiles = (n + kFtTargets - 1) / kFtTargets;
@@ -108,7 +118,7 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
         int j = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, j++) {
             const int b = j & 1, use = j >> 1;
-            FtBuf &B = buf[b];
+            Buf &B = buf[b];
             if (use > 0) mbar_wait(&empty[b], (unsigned)((use - 1) & 1));  // consumers are done with it
             const int b0 = tile * kFtTargets;
             const int cnt = min(kFtTargets, n - b0);
@@ -118,7 +128,7 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
             const int m_base = r0 & ~1, m_cnt = ((r1 + 1) & ~1) - m_base;
             const int cs_base = cf & ~3, cs_cnt = ((cl + 2 + 3) & ~3) - cs_base;
             const int cell_cnt = (cnt + 3) & ~3;
-            const bool src_staged = r1 - r0 <= kFtTile;
+            const bool src_staged = r1 - r0 <= TILE;
             const bool nb_staged = ncb <= kFtCells;
             const bool cs_staged = cs_cnt <= kFtCs;
             if (nb_staged) {
@@ -164,7 +174,7 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
     int j = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, j++) {
         const int b = j & 1, use = j >> 1;
-        const FtBuf &B = buf[b];
+        const Buf &B = buf[b];
         mbar_wait(&full[b], (unsigned)(use & 1));
         const int i = tile * kFtTargets + threadIdx.x;
         const bool valid = i < n;
