@@ -21,11 +21,13 @@
 // SM at 96 registers), 6 (unrolled 8 times) or 7 (448-source buffers, 6 blocks per SM at 64
 // registers).  Measured on B200 (config 3, profiles/bench_r01_v11_fv*.json): results identical to
 // the default (all GPU parity tests, 29 214 105 collisions at 1e8 particles), but 33.1 / 32.7 /
-// 32.8 ms per run for variants 5 / 6 / 7 against 28.8 ms of k_force_integrate.  The three agree
-// although their occupancy and unrolling differ, so the limit is common to them -- most likely the
-// producer's chain per tile (two dependent index loads, the neighbourhood loads, five small bulk
-// copies) with only one tile of look-ahead, which the thin later timesteps (30 per cell, about
-// 1.5 us of pair work per tile) cannot hide.  NOT the default; deeper look-ahead is the next step.
+// 32.8 ms per run for variants 5 / 6 / 7 against 28.8 ms of k_force_integrate.  The slowdown is the
+// same 13-16 % in EVERY timestep (profiles/force_steps_r01_v11.txt: 11.7 against 10.3 ms in the
+// full first step, 1.8 against 1.5 ms in the thinnest), and the three settings agree although
+// their occupancy (16 / 16 / 24 consumer warps per SM against the default's 32) and unrolling
+// differ; the unrolled pair loops are the same SASS (74 against 72 instructions per 4 pairs).  So
+// neither the producer's latency nor the loop body explains it; an ncu capture of this kernel is
+// the next step.  NOT the default.
 #pragma once
 #include "parsim_kernels.cuh"
 
