@@ -26,8 +26,10 @@
 // full first step, 1.8 against 1.5 ms in the thinnest), and the three settings agree although
 // their occupancy (16 / 16 / 24 consumer warps per SM against the default's 32) and unrolling
 // differ; the unrolled pair loops are the same SASS (74 against 72 instructions per 4 pairs).  So
-// neither the producer's latency nor the loop body explains it; an ncu capture of this kernel is
-// the next step.  NOT the default.
+// neither the producer's latency nor the loop body explains it, and parking the waiting warps
+// (try_wait with a suspend-time hint, nanosleep back-off in the producer) instead of spinning on
+// the mbarriers changed nothing (force_steps_r01_v12.txt); an ncu capture of this kernel is the
+// next step.  NOT the default.
 #pragma once
 #include "parsim_kernels.cuh"
 
@@ -71,17 +73,26 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long *bar) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long *bar, unsigned bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(ft_smem(bar)), "r"(bytes) : "memory");
 }
-// returns once the phase of the given parity has completed
+// returns once the phase of the given parity has completed.  The suspend-time hint lets the
+// hardware park the warp until the phase completes instead of returning early to poll again.
+__device__ __forceinline__ bool mbar_try_wait(unsigned a, unsigned parity) {
+    unsigned done;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done) : "r"(a), "r"(parity), "r"(0x989680u) : "memory");
+    return done != 0;
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity) {
     const unsigned a = ft_smem(bar);
-    unsigned done;
-    do {
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(done) : "r"(a), "r"(parity) : "memory");
-    } while (!done);
+    while (!mbar_try_wait(a, parity)) {}
+}
+// the producer waits a whole tile's worth of pair work: back off between polls so that its
+// mbarrier traffic does not compete with the consumers' shared-memory loads
+__device__ __forceinline__ void mbar_wait_backoff(unsigned long long *bar, unsigned parity) {
+    const unsigned a = ft_smem(bar);
+    while (!mbar_try_wait(a, parity)) __nanosleep(200);
 }
 // 1-D bulk copy global -> shared (TMA engine); bytes % 16 == 0, both addresses 16-byte aligned
 __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned bytes, unsigned long long *bar) {
@@ -121,7 +132,7 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, j++) {
             const int b = j & 1, use = j >> 1;
             Buf &B = buf[b];
-            if (use > 0) mbar_wait(&empty[b], (unsigned)((use - 1) & 1));  // consumers are done with it
+            if (use > 0) mbar_wait_backoff(&empty[b], (unsigned)((use - 1) & 1));  // consumers are done with it
             const int b0 = tile * kFtTargets;
             const int cnt = min(kFtTargets, n - b0);
             const int cf = __ldg(&cell[b0]), cl = __ldg(&cell[b0 + cnt - 1]);
