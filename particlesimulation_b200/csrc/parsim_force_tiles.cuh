@@ -6,8 +6,8 @@
 // with, per scheduler, about 2 of 7 resident warps parked at the staging __syncthreads and 1.4-3
 // more waiting for the global loads that precede it: every block pays its own load -> barrier ->
 // pair loop -> store sequence.  Here a block stays resident and walks over many 128-target tiles;
-// a PRODUCER warp runs one to two tiles ahead of the four CONSUMER warps and stages everything a
-// tile needs in one of two shared-memory buffers:
+// a PRODUCER warp runs up to NST - 1 tiles ahead of the four CONSUMER warps and stages everything a
+// tile needs in one of NST shared-memory buffers:
 //   * the contiguous source range of the tile (positions, masses), the tile's cell indices,
 //     velocities and the window of cell_start it needs -- five 1-D bulk copies of the TMA engine
 //     (cp.async.bulk global -> shared, completion counted in bytes on an mbarrier);
@@ -17,10 +17,11 @@
 // buffer back on its "empty" mbarrier and only then do the integration and the global stores, so
 // neither a block-wide barrier nor a global load sits in front of the FP64-bound loop.
 //
-// Selected with PARSIM_FORCE_VARIANT=5 (pair loop unrolled 4 times, 768-source buffers, 4 blocks per
-// SM at 96 registers), 6 (unrolled 8 times) or 7 (448-source buffers, 6 blocks per SM at 64
-// registers).  Measured on B200 (config 3, profiles/bench_r01_v11_fv*.json): results identical to
-// the default (all GPU parity tests, 29 214 105 collisions at 1e8 particles), but 33.1 / 32.7 /
+// Selected with PARSIM_FORCE_VARIANT=5 (pair loop unrolled 4 times, two 768-source buffers, 4 blocks
+// per SM at 96 registers), 6 (unrolled 8 times), 7 (two 448-source buffers, 6 blocks per SM at 64
+// registers) or 8 (three 448-source buffers, 4 blocks per SM; not measured yet).  Measured on B200
+// (config 3, profiles/bench_r01_v11_fv*.json): results identical to the default (all GPU parity
+// tests, 29 214 105 collisions at 1e8 particles), but 33.1 / 32.7 /
 // 32.8 ms per run for variants 5 / 6 / 7 against 28.8 ms of k_force_integrate.  The slowdown is the
 // same 13-16 % in EVERY timestep (profiles/force_steps_r01_v11.txt: 11.7 against 10.3 ms in the
 // full first step, 1.8 against 1.5 ms in the thinnest), and the three settings agree although
@@ -60,8 +61,8 @@ static_assert(sizeof(FtBuf<768>) % 16 == 0 && sizeof(FtBuf<448>) % 16 == 0,
               "FtBuf must keep its members 16-byte aligned in an array");
 enum { FT_SRC = 1, FT_NB = 2, FT_CS = 4 };  // FtBuf::flags: what was staged for this tile
 
-template <int TILE>
-inline size_t force_tiles_smem() { return 2 * sizeof(FtBuf<TILE>) + 4 * sizeof(unsigned long long); }
+template <int TILE, int NST>  // NST buffers: the producer runs up to NST - 1 tiles ahead
+inline size_t force_tiles_smem() { return NST * sizeof(FtBuf<TILE>) + 2 * NST * sizeof(unsigned long long); }
 
 __device__ __forceinline__ unsigned ft_smem(const void *p) { return (unsigned)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count) {
@@ -101,7 +102,7 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
                    "r"(ft_smem(bar)) : "memory");
 }
 
-template <int UNROLL, int TILE, int MINB>
+template <int UNROLL, int TILE, int MINB, int NST>
 __global__ void __launch_bounds__(kFtThreads, MINB)
 k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *__restrict__ m,
               const int *__restrict__ cell, const int *__restrict__ cell_start,
@@ -112,15 +113,15 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
     extern __shared__ __align__(16) unsigned char ft_raw[];
     typedef FtBuf<TILE> Buf;
     Buf *buf = reinterpret_cast<Buf *>(ft_raw);
-    unsigned long long *full = reinterpret_cast<unsigned long long *>(ft_raw + 2 * sizeof(Buf));
-    unsigned long long *empty = full + 2;
+    unsigned long long *full = reinterpret_cast<unsigned long long *>(ft_raw + NST * sizeof(Buf));
+    unsigned long long *empty = full + NST;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int ntiles = (n + kFtTargets - 1) / kFtTargets;
     if (threadIdx.x == 0) {
-        mbar_init(&full[0], 32);  // the 32 producer lanes (+ the bytes of the bulk copies)
-        mbar_init(&full[1], 32);
-        mbar_init(&empty[0], kFtTargets);
-        mbar_init(&empty[1], kFtTargets);
+        for (int b = 0; b < NST; b++) {
+            mbar_init(&full[b], 32);  // the 32 producer lanes (+ the bytes of the bulk copies)
+            mbar_init(&empty[b], kFtTargets);
+        }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -130,7 +131,7 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
         // ---------------- producer warp: one to two tiles ahead of the consumers ----------------
         int j = 0;
         for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, j++) {
-            const int b = j & 1, use = j >> 1;
+            const int b = j % NST, use = j / NST;
             Buf &B = buf[b];
             if (use > 0) mbar_wait_backoff(&empty[b], (unsigned)((use - 1) & 1));  // consumers are done with it
             const int b0 = tile * kFtTargets;
@@ -186,7 +187,7 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
     // -------------------------------- consumer warps ------------------------------------------
     int j = 0;
     for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, j++) {
-        const int b = j & 1, use = j >> 1;
+        const int b = j % NST, use = j / NST;
         const Buf &B = buf[b];
         mbar_wait(&full[b], (unsigned)(use & 1));
         const int i = tile * kFtTargets + threadIdx.x;

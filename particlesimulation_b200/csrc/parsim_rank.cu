@@ -113,20 +113,21 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
         }
     }
     if (const char *e = getenv("PARSIM_FORCE_VARIANT")) c->force_variant = atoi(e);
-    if (c->force_variant >= 5 && c->force_variant <= 7) {  // persistent tile pipeline (parsim_force_tiles.cuh)
+    if (c->force_variant >= 5 && c->force_variant <= 8) {  // persistent tile pipeline (parsim_force_tiles.cuh)
         int per_sm = 0, sms = 0;
         PS_CUDA(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
-#define PS_FT_SETUP(UN, TILE, MINB)                                                                          \
+#define PS_FT_SETUP(UN, TILE, MINB, NST)                                                                     \
     do {                                                                                                     \
-        const int sh = (int)force_tiles_smem<TILE>();                                                        \
-        PS_CUDA(c, cudaFuncSetAttribute(k_force_tiles<UN, TILE, MINB>,                                       \
+        const int sh = (int)force_tiles_smem<TILE, NST>();                                                   \
+        PS_CUDA(c, cudaFuncSetAttribute(k_force_tiles<UN, TILE, MINB, NST>,                                  \
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, sh));                   \
-        PS_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_force_tiles<UN, TILE, MINB>,     \
+        PS_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_force_tiles<UN, TILE, MINB, NST>, \
                                                                  kFtThreads, sh));                           \
     } while (0)
-        if (c->force_variant == 5) PS_FT_SETUP(4, 768, 4);
-        else if (c->force_variant == 6) PS_FT_SETUP(8, 768, 4);
-        else PS_FT_SETUP(4, 448, 6);
+        if (c->force_variant == 5) PS_FT_SETUP(4, 768, 4, 2);
+        else if (c->force_variant == 6) PS_FT_SETUP(8, 768, 4, 2);
+        else if (c->force_variant == 7) PS_FT_SETUP(4, 448, 6, 2);
+        else PS_FT_SETUP(4, 448, 4, 3);
 #undef PS_FT_SETUP
         if (per_sm < 1) return c->fail("k_force_tiles does not fit an SM");
         c->ft_grid = sms * per_sm;
