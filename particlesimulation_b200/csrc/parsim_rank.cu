@@ -131,6 +131,9 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
 #undef PS_FT_SETUP
         if (per_sm < 1) return c->fail("k_force_tiles does not fit an SM");
         c->ft_grid = sms * per_sm;
+        if (getenv("PARSIM_DEBUG"))
+            fprintf(stderr, "parsim_b200: k_force_tiles variant %d: %d blocks per SM, grid %d\n", c->force_variant,
+                    per_sm, c->ft_grid);
     }
     if (const char *e = getenv("PARSIM_CAPACITY_PCT")) {
         double pct = atof(e);

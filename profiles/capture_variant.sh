@@ -8,8 +8,8 @@ tag=${1:-scratch}
 variant=${2:-5}
 out=gpurun_out
 mkdir -p $out
-for v in 0 $variant; do
-    PARSIM_FORCE_VARIANT=$v timeout 240 ncu --set full --clock-control none --import-source on \
+for v in 0 $variant; do  # PARSIM_DEBUG prints the resident blocks per SM of the persistent variants
+    PARSIM_DEBUG=1 PARSIM_FORCE_VARIANT=$v timeout 240 ncu --set full --clock-control none --import-source on \
         -k regex:'k_force_integrate|k_force_tiles' -c 3 -o $out/prof_${tag}_fv$v -f \
         python tools/force_steps.py > $out/ncu_${tag}_fv$v.log 2>&1 || { echo "ncu fv$v failed"; tail -5 $out/ncu_${tag}_fv$v.log; }
     ncu -i $out/prof_${tag}_fv$v.ncu-rep --page raw --csv > $out/prof_${tag}_fv${v}_raw.csv 2>/dev/null
