@@ -19,7 +19,8 @@
 //
 // Selected with PARSIM_FORCE_VARIANT=5 (pair loop unrolled 4 times, two 768-source buffers, 4 blocks
 // per SM at 96 registers), 6 (unrolled 8 times), 7 (two 448-source buffers, 6 blocks per SM at 64
-// registers) or 8 (three 448-source buffers, 4 blocks per SM; not measured yet).  Measured on B200
+// registers), 8 (three 448-source buffers, 4 blocks per SM) or 9 (as 5 with one mbarrier arrival per
+// warp); 8 and 9 have not run on a GPU yet.  Measured on B200
 // (config 3, profiles/bench_r01_v11_fv*.json): results identical to the default (all GPU parity
 // tests, 29 214 105 collisions at 1e8 particles), but 33.1 / 32.7 /
 // 32.8 ms per run for variants 5 / 6 / 7 against 28.8 ms of k_force_integrate.  The slowdown is the
@@ -102,7 +103,10 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, unsigned by
                    "r"(ft_smem(bar)) : "memory");
 }
 
-template <int UNROLL, int TILE, int MINB, int NST>
+// ELECT: one arrival per WARP on the mbarriers (after __syncwarp, which orders the lanes' shared-memory
+// accesses before the elected lane's release) instead of one per thread: 5 instead of 160 mbarrier
+// operations per tile.
+template <int UNROLL, int TILE, int MINB, int NST, bool ELECT = false>
 __global__ void __launch_bounds__(kFtThreads, MINB)
 k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *__restrict__ m,
               const int *__restrict__ cell, const int *__restrict__ cell_start,
@@ -119,8 +123,8 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
     const int ntiles = (n + kFtTargets - 1) / kFtTargets;
     if (threadIdx.x == 0) {
         for (int b = 0; b < NST; b++) {
-            mbar_init(&full[b], 32);  // the 32 producer lanes (+ the bytes of the bulk copies)
-            mbar_init(&empty[b], kFtTargets);
+            mbar_init(&full[b], ELECT ? 1 : 32);  // the producer lanes (+ the bytes of the bulk copies)
+            mbar_init(&empty[b], ELECT ? kFtTargets / 32 : kFtTargets);
         }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -164,6 +168,7 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
                     B.nm[idx] = __ldg(&com_m[q]);
                 }
             }
+            if (ELECT) __syncwarp();  // the lanes' nxy / nm stores come before lane 0's release
             if (lane == 0) {
                 B.r0 = r0; B.r1 = r1; B.m_base = m_base; B.cs_base = cs_base; B.cf = cf; B.ncb = ncb;
                 B.flags = (src_staged ? FT_SRC : 0) | (nb_staged ? FT_NB : 0) | (cs_staged ? FT_CS : 0);
@@ -177,7 +182,7 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
                     bulk_g2s(B.m, m + m_base, 8u * m_cnt, &full[b]);
                 }
                 if (cs_staged) bulk_g2s(B.cs, cell_start + cs_base, 4u * cs_cnt, &full[b]);
-            } else {
+            } else if (!ELECT) {
                 mbar_arrive(&full[b]);  // releases this lane's nxy / nm stores
             }
         }
@@ -248,7 +253,13 @@ k_force_tiles(Geom g, int n, const double2 *__restrict__ pos_in, const double *_
                 }
             }
         }
-        mbar_arrive(&empty[b]);  // every shared-memory read of this tile is behind us
+        // every shared-memory read of this tile is behind us
+        if (ELECT) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[b]);
+        } else {
+            mbar_arrive(&empty[b]);
+        }
         if (!valid) continue;
         ax *= kG;
         ay *= kG;

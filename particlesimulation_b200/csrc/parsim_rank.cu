@@ -113,21 +113,22 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
         }
     }
     if (const char *e = getenv("PARSIM_FORCE_VARIANT")) c->force_variant = atoi(e);
-    if (c->force_variant >= 5 && c->force_variant <= 8) {  // persistent tile pipeline (parsim_force_tiles.cuh)
+    if (c->force_variant >= 5 && c->force_variant <= 9) {  // persistent tile pipeline (parsim_force_tiles.cuh)
         int per_sm = 0, sms = 0;
         PS_CUDA(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
-#define PS_FT_SETUP(UN, TILE, MINB, NST)                                                                     \
+#define PS_FT_SETUP(UN, TILE, MINB, NST, EL)                                                                 \
     do {                                                                                                     \
         const int sh = (int)force_tiles_smem<TILE, NST>();                                                   \
-        PS_CUDA(c, cudaFuncSetAttribute(k_force_tiles<UN, TILE, MINB, NST>,                                  \
+        PS_CUDA(c, cudaFuncSetAttribute(k_force_tiles<UN, TILE, MINB, NST, EL>,                              \
                                         cudaFuncAttributeMaxDynamicSharedMemorySize, sh));                   \
-        PS_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_force_tiles<UN, TILE, MINB, NST>, \
-                                                                 kFtThreads, sh));                           \
+        PS_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(                                            \
+                       &per_sm, k_force_tiles<UN, TILE, MINB, NST, EL>, kFtThreads, sh));                    \
     } while (0)
-        if (c->force_variant == 5) PS_FT_SETUP(4, 768, 4, 2);
-        else if (c->force_variant == 6) PS_FT_SETUP(8, 768, 4, 2);
-        else if (c->force_variant == 7) PS_FT_SETUP(4, 448, 6, 2);
-        else PS_FT_SETUP(4, 448, 4, 3);
+        if (c->force_variant == 5) PS_FT_SETUP(4, 768, 4, 2, false);
+        else if (c->force_variant == 6) PS_FT_SETUP(8, 768, 4, 2, false);
+        else if (c->force_variant == 7) PS_FT_SETUP(4, 448, 6, 2, false);
+        else if (c->force_variant == 8) PS_FT_SETUP(4, 448, 4, 3, false);
+        else PS_FT_SETUP(4, 768, 4, 2, true);
 #undef PS_FT_SETUP
         if (per_sm < 1) return c->fail("k_force_tiles does not fit an SM");
         c->ft_grid = sms * per_sm;

@@ -185,9 +185,9 @@ static int stage_force(Rank *c) {
         c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,        \
         c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
         c->dbg_acc)
-#define PS_FORCE_TILES(UN, TILE, MINB, NST)                                                          \
-    k_force_tiles<UN, TILE, MINB, NST><<<std::min(c->ft_grid, grid_for(c->n_alive, kFtTargets)),     \
-                                         kFtThreads, force_tiles_smem<TILE, NST>(), c->stream>>>(    \
+#define PS_FORCE_TILES(UN, TILE, MINB, NST, EL)                                                      \
+    k_force_tiles<UN, TILE, MINB, NST, EL><<<std::min(c->ft_grid, grid_for(c->n_alive, kFtTargets)), \
+                                             kFtThreads, force_tiles_smem<TILE, NST>(), c->stream>>>( \
         c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,         \
         c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,      \
         c->dbg_acc)
@@ -200,10 +200,11 @@ static int stage_force(Rank *c) {
         case 1: PS_FORCE(2, 256, 0, 16); break;   // sparse cells: neighbourhood through L1, 32 registers, full occupancy
         case 3: PS_FORCE(8, 1280, 16, 5); break;  // deep unroll, 96 registers (comparison)
         case 4: PS_FORCE(2, 256, 0, 8); break;    // sparse cells at 64 registers (comparison)
-        case 5: PS_FORCE_TILES(4, 768, 4, 2); break;  // persistent tile pipeline (parsim_force_tiles.cuh; comparison)
-        case 6: PS_FORCE_TILES(8, 768, 4, 2); break;
-        case 7: PS_FORCE_TILES(4, 448, 6, 2); break;
-        case 8: PS_FORCE_TILES(4, 448, 4, 3); break;
+        case 5: PS_FORCE_TILES(4, 768, 4, 2, false); break;  // persistent tile pipeline (parsim_force_tiles.cuh; comparison)
+        case 6: PS_FORCE_TILES(8, 768, 4, 2, false); break;
+        case 7: PS_FORCE_TILES(4, 448, 6, 2, false); break;
+        case 8: PS_FORCE_TILES(4, 448, 4, 3, false); break;
+        case 9: PS_FORCE_TILES(4, 768, 4, 2, true); break;
         default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
         }
     });
