@@ -10,6 +10,7 @@
 #include "../../include/parsim_b200.h"
 #include "parsim_kernels.cuh"
 #include "parsim_force_tiles.cuh"
+#include "parsim_force_pairs2.cuh"
 #include "parsim_merge.cuh"
 #include "parsim_sort.cuh"
 #include "parsim_collide.cuh"

@@ -186,6 +186,11 @@ static int stage_force(Rank *c) {
         c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
         c->dbg_acc)
 #define PS_FORCE(UN, TILE, CELLS, MINB) PS_FORCE_TB(128, UN, TILE, CELLS, MINB)
+#define PS_FORCE2(UN, TILE, CELLS, MINB)                                                            \
+    k_force_integrate2<128, UN, TILE, CELLS, MINB><<<grid_for(c->n_alive, 256), 128, 0, c->stream>>>( \
+        c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,        \
+        c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
+        c->dbg_acc)
 #define PS_FORCE_TILES(UN, TILE, MINB, NST, EL)                                                      \
     k_force_tiles<UN, TILE, MINB, NST, EL><<<std::min(c->ft_grid, grid_for(c->n_alive, kFtTargets)), \
                                              kFtThreads, force_tiles_smem<TILE, NST>(), c->stream>>>( \
@@ -208,11 +213,15 @@ static int stage_force(Rank *c) {
         case 9: PS_FORCE_TILES(4, 768, 4, 2, true); break;
         case 10: PS_FORCE_TB(64, 4, 384, 8, 16); break;   // 2-warp blocks, 16 per SM: 29.7 ms per config-3 run (default 28.8)
         case 11: PS_FORCE_TB(256, 4, 1024, 16, 4); break; // 8-warp blocks, 4 per SM: 28.9 ms
+        case 12: PS_FORCE2(2, 1024, 16, 6); break;  // two targets per thread (parsim_force_pairs2.cuh; unmeasured)
+        case 13: PS_FORCE2(4, 1024, 16, 5); break;
+        case 14: PS_FORCE2(2, 1024, 16, 8); break;
         default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
         }
     });
 #undef PS_FORCE
 #undef PS_FORCE_TB
+#undef PS_FORCE2
 #undef PS_FORCE_TILES
     c->pos_latest = c->pos_alt;
     c->have_newcell = true;

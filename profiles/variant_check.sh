@@ -3,11 +3,11 @@
 # against the default: per-timestep force times (tools/force_steps.py, about 4 s each) and, for the
 # FIRST variant listed, the GPU parity suite under that variant.  Every leg runs under its own
 # timeout: a deadlocked pipeline must not hang the box.
-#   gpurun --timeout 300 -- 'bash profiles/variant_check.sh r02_v1 9 8 5'
+#   gpurun --timeout 300 -- 'bash profiles/variant_check.sh r02_v1 12 13 14 9 8 5'
 set -u
 tag=${1:-scratch}
 shift
-variants=${*:-"5 8 9"}
+variants=${*:-"12 13 14 9 8 5"}
 out=gpurun_out
 mkdir -p $out
 for v in 0 $variants; do
