@@ -336,6 +336,8 @@ def main_ours(a):
                      "frac": achieved / hbm_peak, "traffic": traffic, "traffic_unit": "GB per launch (ncu dram read+write)",
                      "algorithmic_GB_per_launch": d["bytes"] / max(d["launches"], 1) / 1e9,
                      "ncu": traffic_info, "peak_source": peak_src,
+                     "timing": "CUDA events around every launch, on the launching stream, in a second pass over the "
+                               "same K runs (ms_per_step_instrumented); the timed pass behind `value` runs without them",
                      "note": "the dominant kernel is FP64-CUDA-core bound (in-cell pair loop): ncu shows the FP64 pipe "
                              "69-78 % busy in every launch, see fp64"},
         "fp64": fp64, "kernels": table,
