@@ -201,6 +201,9 @@ static int stage_force(Rank *c) {
     // variant by current occupancy (cells fill up or empty out as the run goes on)
     int v = c->force_variant;
     if (v <= 0) v = (double)c->n_alive < 28.0 * c->g.ncells ? 1 : 2;  // measured crossover: about 30 per cell
+    // an empty strip (everybody dead, or a strip the cloud does not reach) has nothing to move; the
+    // kernels read cell[first] / cell[last] of their block unconditionally, so they are not launched
+    if (c->n_alive > 0)
     PS_LAUNCH(c, K_FORCE, 81.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate", {
         switch (v) {
         case 1: PS_FORCE(2, 256, 0, 16); break;   // sparse cells: neighbourhood through L1, 32 registers, full occupancy
