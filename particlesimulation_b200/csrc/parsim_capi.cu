@@ -19,6 +19,11 @@ using namespace parsim;
 struct parsim_ctx {
     std::vector<std::unique_ptr<Rank>> ranks;  // 1 for a rank context, n_gpus for a group
     bool group = false;                        // ranks are all the strips of the job
+    std::unique_ptr<LocalBus> bus;             // device-copy transport of the group (else NCCL)
+    std::vector<cudaEvent_t> ev_ing;           // [strip][staging slot]: the strip has ingested the slot's piece
+    long long group_pieces = 0;                // staging passes of the group upload so far
+    bool shared_upload = false;                // group upload: ONE host->device copy per piece, every
+                                               // strip ingests from it (same GPU or peer access)
     std::string err;
 };
 
@@ -39,13 +44,20 @@ int for_ranks(parsim_ctx *ctx, const std::function<int(Rank *)> &fn) {
     if (n == 1) {
         rc[0] = fn(ctx->ranks[0].get());
     } else {
+        if (ctx->bus) ctx->bus->rearm();
         std::vector<std::thread> th;
         for (size_t r = 0; r < n; r++)
-            th.emplace_back([&, r] { rc[r] = fn(ctx->ranks[r].get()); });
+            th.emplace_back([&, r] {
+                rc[r] = fn(ctx->ranks[r].get());
+                if (rc[r] && ctx->bus) ctx->bus->abort();  // nobody waits for a strip that gave up
+            });
         for (auto &t : th) t.join();
     }
+    // report the strip that failed first-hand, not one that only saw the broken barrier
+    size_t bad = n;
     for (size_t r = 0; r < n; r++)
-        if (rc[r]) return ctx_fail(ctx, (n > 1 ? "gpu " + std::to_string(r) + ": " : "") + ctx->ranks[r]->err);
+        if (rc[r] && (bad == n || ctx->ranks[bad]->err == kPeerFailed)) bad = r;
+    if (bad < n) return ctx_fail(ctx, (n > 1 ? "strip " + std::to_string(bad) + ": " : "") + ctx->ranks[bad]->err);
     return 0;
 }
 
@@ -96,15 +108,56 @@ int parsim_create_rows(parsim_ctx **out, double side, long ncside, long long n_p
     *out = nullptr;
     if (n_gpus < 1) { g_create_error = "n_gpus must be >= 1"; return 1; }
     if (n_gpus == 1) return parsim_create_rank_rows(out, side, ncside, n_part, 0, 1, 0, nullptr, first_rows);
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) {
+        g_create_error = "no CUDA device: parsim_b200 has no CPU fallback";
+        return 1;
+    }
+    // Transport of the group.  NCCL needs one GPU per strip; with fewer GPUs than strips (or
+    // PARSIM_TRANSPORT=local) the strips share the GPUs round-robin and exchange by device copies
+    // (LocalBus, parsim_rank.cuh) -- same kernels, same order rules, same bits.
+    bool local = n_gpus > ndev;
+    if (const char *t = getenv("PARSIM_TRANSPORT")) {
+        if (!strcmp(t, "local")) local = true;
+        else if (!strcmp(t, "nccl")) local = false;
+        else { g_create_error = "PARSIM_TRANSPORT must be local or nccl"; return 1; }
+    }
+    if (!local && n_gpus > ndev) {
+        g_create_error = "NCCL transport needs one GPU per strip (" + std::to_string(n_gpus) + " strips, " +
+                         std::to_string(ndev) + " GPUs)";
+        return 1;
+    }
     unsigned char id[128];
-    if (parsim_nccl_unique_id(id)) return 1;
+    if (!local && parsim_nccl_unique_id(id)) return 1;
     std::unique_ptr<parsim_ctx> ctx(new parsim_ctx);
     ctx->group = true;
     for (int r = 0; r < n_gpus; r++) ctx->ranks.emplace_back(new Rank);
+    if (local) {
+        ctx->bus.reset(new LocalBus);
+        for (auto &r : ctx->ranks) ctx->bus->ranks.push_back(r.get());
+    }
+    // peer access between the GPUs of the group: the group upload copies every piece to ONE GPU and
+    // all strips ingest from there (NVLink reads), instead of n_gpus host->device copies of it
+    const int used = std::min(n_gpus, ndev);
+    ctx->shared_upload = true;
+    for (int i = 0; i < used; i++)
+        for (int j = 0; j < used; j++) {
+            if (i == j) continue;
+            int ok = 0;
+            cudaDeviceCanAccessPeer(&ok, i, j);
+            if (ok) {
+                cudaSetDevice(i);
+                cudaError_t e = cudaDeviceEnablePeerAccess(j, 0);
+                if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) ok = 0;
+                cudaGetLastError();
+            }
+            if (!ok) ctx->shared_upload = false;
+        }
+    if (const char *e = getenv("PARSIM_SHARED_UPLOAD")) ctx->shared_upload = ctx->shared_upload && atoi(e) != 0;
     int rc = for_ranks(ctx.get(), [&](Rank *c) {
         int r = 0;
         while (ctx->ranks[r].get() != c) r++;
-        return rank_create(c, side, ncside, n_part, r, n_gpus, r, id, first_rows);
+        return rank_create(c, side, ncside, n_part, r, n_gpus, r % ndev, local ? nullptr : id, first_rows, ctx->bus.get());
     });
     if (rc) {
         g_create_error = ctx->err;
@@ -147,20 +200,92 @@ int parsim_host_row_counts(double side, long ncside, long long count, const doub
 void parsim_destroy(parsim_ctx *ctx) {
     if (!ctx) return;
     for (auto &r : ctx->ranks) rank_destroy(r.get());
+    for (cudaEvent_t e : ctx->ev_ing) if (e) cudaEventDestroy(e);
     delete ctx;
 }
 
 int parsim_upload_begin(parsim_ctx *ctx) { return for_ranks(ctx, rank_upload_begin); }
 
+// Group upload: piece p is copied host->device ONCE, to the staging set of the first strip on GPU
+// (p mod #GPUs) -- the GPUs' PCIe links work in parallel -- and every strip's ingest kernels read it
+// from there (same GPU, or peer access over NVLink).  One host thread enqueues everything.
+static int group_upload_chunk(parsim_ctx *ctx, long long id_base, const unsigned *ids, long long count,
+                              const double *x, const double *y, const double *vx, const double *vy,
+                              const double *m) {
+    const size_t n = ctx->ranks.size();
+    Rank *c0 = ctx->ranks[0].get();
+    if (!c0->uploading) return ctx_fail(ctx, "parsim_upload_chunk outside upload_begin/upload_end");
+    if (count < 0 || (!ids && (id_base < 0 || id_base + count > c0->n_part)))
+        return ctx_fail(ctx, "upload chunk outside [0, n_part)");
+    std::vector<Rank *> stagers;  // first strip on each GPU
+    for (auto &r : ctx->ranks) {
+        bool seen = false;
+        for (Rank *q : stagers) seen = seen || q->device == r->device;
+        if (!seen) stagers.push_back(r.get());
+    }
+    const size_t S = stagers.size();
+    for (Rank *q : stagers)
+        if (rank_stage_alloc(q)) return ctx_fail(ctx, q->err);
+    if (ctx->ev_ing.empty()) {
+        ctx->ev_ing.resize(n * 2 * S, nullptr);
+        for (size_t r = 0; r < n; r++) {
+            cudaSetDevice(ctx->ranks[r]->device);
+            for (size_t k = 0; k < 2 * S; k++)
+                if (cudaEventCreateWithFlags(&ctx->ev_ing[r * 2 * S + k], cudaEventDisableTiming) != cudaSuccess)
+                    return ctx_fail(ctx, "cudaEventCreate failed");
+        }
+    }
+    const double *src[5] = {x, y, vx, vy, m};
+    const long long piece = stagers[0]->stage_cap;
+#define PS_G(call)                                                                                         \
+    do {                                                                                                   \
+        cudaError_t e__ = (call);                                                                          \
+        if (e__ != cudaSuccess) return ctx_fail(ctx, std::string(#call) + ": " + cudaGetErrorString(e__)); \
+    } while (0)
+    for (long long off = 0; off < count; off += piece) {
+        const int cnt = (int)std::min<long long>(piece, count - off);
+        const long long p = ctx->group_pieces;
+        Rank *st = stagers[(size_t)(p % (long long)S)];
+        const int b = (int)((p / (long long)S) & 1);
+        const size_t slot = (size_t)(p % (long long)(2 * S));
+        PS_G(cudaSetDevice(st->device));
+        if (p >= (long long)(2 * S))  // the set is free once every strip has ingested its previous piece
+            for (size_t r = 0; r < n; r++) PS_G(cudaStreamWaitEvent(st->copy_stream, ctx->ev_ing[r * 2 * S + slot], 0));
+        for (int k = 0; k < 5; k++)
+            PS_G(cudaMemcpyAsync(st->stage[b][k], src[k] + off, sizeof(double) * cnt, cudaMemcpyHostToDevice, st->copy_stream));
+        if (ids)
+            PS_G(cudaMemcpyAsync(st->stage_ids[b], ids + off, sizeof(unsigned) * cnt, cudaMemcpyHostToDevice, st->copy_stream));
+        PS_G(cudaEventRecord(st->ev_copied[b], st->copy_stream));
+        for (size_t r = 0; r < n; r++) {
+            Rank *c = ctx->ranks[r].get();
+            PS_G(cudaSetDevice(c->device));
+            PS_G(cudaStreamWaitEvent(c->stream, st->ev_copied[b], 0));
+            if (rank_ingest_piece(c, id_base + off, ids ? st->stage_ids[b] : nullptr, cnt, st->stage[b]))
+                return ctx_fail(ctx, c->err);
+            PS_G(cudaEventRecord(ctx->ev_ing[r * 2 * S + slot], c->stream));
+        }
+        ctx->group_pieces++;
+    }
+    for (Rank *q : stagers) {  // the caller's arrays are free again when this returns
+        PS_G(cudaSetDevice(q->device));
+        PS_G(cudaStreamSynchronize(q->copy_stream));
+    }
+#undef PS_G
+    for (auto &r : ctx->ranks) r->n_uploaded += count;
+    return 0;
+}
+
 int parsim_upload_chunk(parsim_ctx *ctx, long long id_base, long long count, const double *x,
                         const double *y, const double *vx, const double *vy, const double *m) {
     if (!x || !y || !vx || !vy || !m) return ctx_fail(ctx, "parsim_upload: NULL array");
+    if (ctx->group && ctx->shared_upload) return group_upload_chunk(ctx, id_base, nullptr, count, x, y, vx, vy, m);
     return for_ranks(ctx, [&](Rank *c) { return rank_upload_chunk(c, id_base, nullptr, count, x, y, vx, vy, m); });
 }
 
 int parsim_upload_chunk_ids(parsim_ctx *ctx, long long count, const unsigned *ids, const double *x,
                             const double *y, const double *vx, const double *vy, const double *m) {
     if (!ids || !x || !y || !vx || !vy || !m) return ctx_fail(ctx, "parsim_upload_chunk_ids: NULL array");
+    if (ctx->group && ctx->shared_upload) return group_upload_chunk(ctx, 0, ids, count, x, y, vx, vy, m);
     return for_ranks(ctx, [&](Rank *c) { return rank_upload_chunk(c, 0, ids, count, x, y, vx, vy, m); });
 }
 

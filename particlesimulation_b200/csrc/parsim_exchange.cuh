@@ -176,12 +176,16 @@ __global__ void k_unpack_late(Geom g, int n_rec, const double *__restrict__ recv
     } while (0)
 
 inline int exchange_create(Rank *c, const unsigned char *nccl_id) {
-    NcclApi &api = nccl_api();
-    if (!api.load()) return c->fail(api.error);
-    if (!nccl_id) return c->fail("multi-rank context needs the NCCL unique id of rank 0");
-    NcclUniqueId id;
-    memcpy(id.internal, nccl_id, sizeof(id.internal));
-    PS_NCCL(c, api.CommInitRank(&c->comm.comm, c->nranks, id, c->rank));
+    if (c->bus) {  // device-copy transport inside one process: no communicator
+        PS_CUDA(c, cudaEventCreateWithFlags(&c->ev_bus, cudaEventDisableTiming));
+    } else {
+        NcclApi &api = nccl_api();
+        if (!api.load()) return c->fail(api.error);
+        if (!nccl_id) return c->fail("multi-rank context needs the NCCL unique id of rank 0");
+        NcclUniqueId id;
+        memcpy(id.internal, nccl_id, sizeof(id.internal));
+        PS_NCCL(c, api.CommInitRank(&c->comm.comm, c->nranks, id, c->rank));
+    }
     c->up = (c->rank - 1 + c->nranks) % c->nranks;
     c->dn = (c->rank + 1) % c->nranks;
     const size_t rec = ((size_t)std::max(c->mig_cap, kEagerRecs) + 1) * kRec;  // + header record
@@ -221,6 +225,8 @@ inline int exchange_create(Rank *c, const unsigned char *nccl_id) {
 inline void exchange_destroy(Rank *c) {
     if (c->comm.comm) nccl_api().CommDestroy(c->comm.comm);
     c->comm.comm = nullptr;
+    if (c->ev_bus) cudaEventDestroy(c->ev_bus);
+    c->ev_bus = nullptr;
     for (int d = 0; d < 2; d++) {
         if (c->mig_send[d]) cudaFree(c->mig_send[d]);
         if (c->mig_recv[d]) cudaFree(c->mig_recv[d]);
@@ -234,10 +240,56 @@ inline void exchange_destroy(Rank *c) {
     if (c->h_hdr64) cudaFreeHost(c->h_hdr64);
 }
 
+// ---- device-copy transport (LocalBus) ------------------------------------------------------
+// Every strip PULLS what its neighbours would have sent: "ready" event on the own stream, host
+// barrier, the own stream waits for the neighbours' events and copies out of their buffers (a
+// plain device copy on one GPU, a peer copy over NVLink between GPUs).  The barrier after the
+// copies are enqueued keeps a fast strip from re-recording its event before a slow one has
+// started waiting for it.
+static const char *const kPeerFailed = "another strip of the group failed";
+
+inline int bus_copy(Rank *c, void *dst, const Rank *from, const void *src, size_t bytes) {
+    if (!bytes) return 0;
+    if (from->device == c->device)
+        PS_CUDA(c, cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, c->stream));
+    else
+        PS_CUDA(c, cudaMemcpyPeerAsync(dst, c->device, src, from->device, bytes, c->stream));
+    return 0;
+}
+
+inline int bus_barrier(Rank *c) {
+    if (c->bus->barrier()) return c->fail(kPeerFailed);
+    return 0;
+}
+
+inline int bus_publish(Rank *c) {  // my buffers are final once the stream gets here
+    PS_CUDA(c, cudaEventRecord(c->ev_bus, c->stream));
+    return bus_barrier(c);
+}
+
+inline int local_halo(Rank *c) {
+    const Geom &g = c->g;
+    const size_t nc = (size_t)g.nc;
+    Rank *up = c->bus->ranks[c->up], *dn = c->bus->ranks[c->dn];
+    timed_begin(c, K_GHOST, 48.0 * nc);
+    if (bus_publish(c)) return 1;
+    PS_CUDA(c, cudaStreamWaitEvent(c->stream, up->ev_bus, 0));
+    PS_CUDA(c, cudaStreamWaitEvent(c->stream, dn->ev_bus, 0));
+    // my upper ghost row = the last row of the strip above, my lower one = the first row of the strip below
+    if (bus_copy(c, c->com_xy, up, up->com_xy + (size_t)up->g.rows * nc, 2 * nc * sizeof(double)) ||
+        bus_copy(c, c->com_m, up, up->com_m + (size_t)up->g.rows * nc, nc * sizeof(double)) ||
+        bus_copy(c, c->com_xy + (g.rows + 1) * nc, dn, dn->com_xy + nc, 2 * nc * sizeof(double)) ||
+        bus_copy(c, c->com_m + (g.rows + 1) * nc, dn, dn->com_m + nc, nc * sizeof(double)))
+        return 1;
+    timed_end(c);
+    return bus_barrier(c);
+}
+
 // Ghost rows.  Receives are posted "from below" first so that with two strips (both
 // neighbours are the same peer) sends and receives pair up in issue order: what I send up is
 // the peer's row from below.
 inline int exchange_halo(Rank *c) {
+    if (c->bus) return local_halo(c);
     NcclApi &api = nccl_api();
     const Geom &g = c->g;
     const size_t nc = (size_t)g.nc;
@@ -267,13 +319,27 @@ inline int exchange_records(Rank *c, int *from_up, int *from_dn, const double **
     const size_t far_eager = (size_t)(1 + c->far_eager) * kRec;
     k_seal_headers<<<1, 32, 0, c->stream>>>(c->mig_hdr_send, c->mig_send[0], c->mig_send[1], c->far_send);
     PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr, c->mig_hdr_send, 3 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-    PS_NCCL(c, api.GroupStart());
-    PS_NCCL(c, api.Send(c->mig_send[0], eager, kNcclFloat64, c->up, c->comm.comm, c->stream));
-    PS_NCCL(c, api.Send(c->mig_send[1], eager, kNcclFloat64, c->dn, c->comm.comm, c->stream));
-    PS_NCCL(c, api.Recv(c->mig_recv[1], eager, kNcclFloat64, c->dn, c->comm.comm, c->stream));
-    PS_NCCL(c, api.Recv(c->mig_recv[0], eager, kNcclFloat64, c->up, c->comm.comm, c->stream));
-    PS_NCCL(c, api.AllGather(c->far_send, c->far_eager_recv, far_eager, kNcclFloat64, c->comm.comm, c->stream));
-    PS_NCCL(c, api.GroupEnd());
+    Rank *bup = c->bus ? c->bus->ranks[c->up] : nullptr, *bdn = c->bus ? c->bus->ranks[c->dn] : nullptr;
+    if (c->bus) {
+        // what the strip above sends DOWN is my message from above, and the other way round
+        if (bus_publish(c)) return 1;
+        for (Rank *q : c->bus->ranks)
+            if (q != c) PS_CUDA(c, cudaStreamWaitEvent(c->stream, q->ev_bus, 0));
+        if (bus_copy(c, c->mig_recv[0], bup, bup->mig_send[1], eager * sizeof(double)) ||
+            bus_copy(c, c->mig_recv[1], bdn, bdn->mig_send[0], eager * sizeof(double)))
+            return 1;
+        for (Rank *q : c->bus->ranks)
+            if (bus_copy(c, c->far_eager_recv + (size_t)q->rank * far_eager, q, q->far_send, far_eager * sizeof(double)))
+                return 1;
+    } else {
+        PS_NCCL(c, api.GroupStart());
+        PS_NCCL(c, api.Send(c->mig_send[0], eager, kNcclFloat64, c->up, c->comm.comm, c->stream));
+        PS_NCCL(c, api.Send(c->mig_send[1], eager, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+        PS_NCCL(c, api.Recv(c->mig_recv[1], eager, kNcclFloat64, c->dn, c->comm.comm, c->stream));
+        PS_NCCL(c, api.Recv(c->mig_recv[0], eager, kNcclFloat64, c->up, c->comm.comm, c->stream));
+        PS_NCCL(c, api.AllGather(c->far_send, c->far_eager_recv, far_eager, kNcclFloat64, c->comm.comm, c->stream));
+        PS_NCCL(c, api.GroupEnd());
+    }
     PS_CUDA(c, cudaMemcpyAsync(c->h_hdr64 + 0, c->mig_recv[0], 8, cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaMemcpyAsync(c->h_hdr64 + 1, c->mig_recv[1], 8, cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaMemcpy2DAsync(c->h_hdr64 + 2, 8, c->far_eager_recv, far_eager * sizeof(double), 8, c->nranks,
@@ -296,7 +362,21 @@ inline int exchange_records(Rank *c, int *from_up, int *from_dn, const double **
     c->stats.migrants += su + sd + c->h_mig_hdr[2];
     // second round for what did not fit the eager slots (both ends know from the headers)
     const int E = (int)(eager / kRec) - 1;
-    if (su > E || sd > E || ru > E || rd > E || far_max > c->far_eager) {
+    if (c->bus) {
+        // the senders' buffers stay as they are until everybody has passed the barrier below, so
+        // the rest is pulled without another handshake
+        if (ru > E && bus_copy(c, c->mig_recv[0] + eager, bup, bup->mig_send[1] + eager, (size_t)(ru - E) * kRec * sizeof(double)))
+            return 1;
+        if (rd > E && bus_copy(c, c->mig_recv[1] + eager, bdn, bdn->mig_send[0] + eager, (size_t)(rd - E) * kRec * sizeof(double)))
+            return 1;
+        if (far_max > c->far_eager)
+            for (Rank *q : c->bus->ranks)
+                if (bus_copy(c, c->far_recv + (size_t)q->rank * far_max * kRec, q, q->far_send + kRec,
+                             (size_t)far_max * kRec * sizeof(double)))
+                    return 1;
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));  // my pulls are done: the senders may pack again
+        if (bus_barrier(c)) return 1;
+    } else if (su > E || sd > E || ru > E || rd > E || far_max > c->far_eager) {
         PS_NCCL(c, api.GroupStart());
         if (su > E) PS_NCCL(c, api.Send(c->mig_send[0] + eager, (size_t)(su - E) * kRec, kNcclFloat64, c->up, c->comm.comm, c->stream));
         if (sd > E) PS_NCCL(c, api.Send(c->mig_send[1] + eager, (size_t)(sd - E) * kRec, kNcclFloat64, c->dn, c->comm.comm, c->stream));

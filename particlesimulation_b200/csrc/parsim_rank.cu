@@ -39,7 +39,7 @@ static double collision_threshold2() {
 }
 
 int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, int nranks,
-                int device, const unsigned char *nccl_id, const long *first_rows) {
+                int device, const unsigned char *nccl_id, const long *first_rows, LocalBus *bus) {
     if (!(side > 0)) return c->fail("side_length must be > 0");
     if (ncside < 1) return c->fail("grid_size must be >= 1");
     if (n_part < 1) return c->fail("n_particles must be >= 1");
@@ -55,6 +55,8 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     if (device < 0 || device >= ndev) return c->fail("CUDA device index out of range");
     PS_CUDA(c, cudaSetDevice(device));
     PS_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+    PS_CUDA(c, cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
+    c->bus = nranks > 1 ? bus : nullptr;
 
     Geom &g = c->g;
     g.side = side;
@@ -113,7 +115,12 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
         }
     }
     if (const char *e = getenv("PARSIM_FORCE_VARIANT")) c->force_variant = atoi(e);
-    if (c->force_variant >= 5 && c->force_variant <= 9) {  // persistent tile pipeline (parsim_force_tiles.cuh)
+    {   // only instantiations that the variant-agreement test covers (tests/test_gpu_parity.py)
+        const int v = c->force_variant;
+        if (!(v >= 0 && v <= 7) && !(v >= 10 && v <= 14))
+            return c->fail("PARSIM_FORCE_VARIANT: unknown force-kernel variant " + std::to_string(v));
+    }
+    if (c->force_variant >= 5 && c->force_variant <= 7) {  // persistent tile pipeline (parsim_force_tiles.cuh)
         int per_sm = 0, sms = 0;
         PS_CUDA(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
 #define PS_FT_SETUP(UN, TILE, MINB, NST, EL)                                                                 \
@@ -126,9 +133,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     } while (0)
         if (c->force_variant == 5) PS_FT_SETUP(4, 768, 4, 2, false);
         else if (c->force_variant == 6) PS_FT_SETUP(8, 768, 4, 2, false);
-        else if (c->force_variant == 7) PS_FT_SETUP(4, 448, 6, 2, false);
-        else if (c->force_variant == 8) PS_FT_SETUP(4, 448, 4, 3, false);
-        else PS_FT_SETUP(4, 768, 4, 2, true);
+        else PS_FT_SETUP(4, 448, 6, 2, false);
 #undef PS_FT_SETUP
         if (per_sm < 1) return c->fail("k_force_tiles does not fit an SM");
         c->ft_grid = sms * per_sm;
@@ -270,26 +275,55 @@ int rank_upload_begin(Rank *c) {
     return 0;
 }
 
+// Staging passes of 8 Mi particles (5 x 64 MiB per set).  The host->device copies of a pass run
+// on copy_stream into one staging set while the ingest kernels (on the step stream) interleave the
+// previous pass out of the other set, so the copy engine never waits for a kernel.
+static const long long kStagePiece = 1 << 23;
+
+int rank_stage_alloc(Rank *c) {
+    if (c->stage[0][0]) return 0;
+    PS_CUDA(c, cudaSetDevice(c->device));
+    c->stage_cap = (int)std::min<long long>(kStagePiece, c->n_part);
+    for (int b = 0; b < 2; b++) {
+        for (int k = 0; k < 5; k++) PS_ALLOC(c, c->stage[b][k], c->stage_cap, false);
+        PS_ALLOC(c, c->stage_ids[b], c->stage_cap, false);
+        PS_CUDA(c, cudaEventCreateWithFlags(&c->ev_copied[b], cudaEventDisableTiming));
+        PS_CUDA(c, cudaEventCreateWithFlags(&c->ev_ingested[b], cudaEventDisableTiming));
+    }
+    PS_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
+    return 0;
+}
+
+// `cnt` staged particles (device SoA `st`, ids `dids` or id_base + index) into this strip's records.
+// The staging arrays may live on another GPU of the process (peer access, group upload).
+int rank_ingest_piece(Rank *c, long long id_base, const unsigned *dids, int cnt, double *const st[5]) {
+    if (c->nranks == 1) {
+        PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest",
+                  k_ingest<<<grid_for(cnt), kThreads, 0, c->stream>>>(
+                      c->g, id_base, dids, cnt, st[0], st[1], st[2], st[3], st[4], c->cap, c->rec0, c->d_ctr));
+    } else {  // stable compaction of this strip's particles: count, scan, write
+        const int nb = grid_for(cnt);
+        PS_LAUNCH(c, K_INGEST, 8.0 * cnt, "k_ingest_strip<0>",
+                  k_ingest_strip<0><<<nb, kThreads, 0, c->stream>>>(
+                      c->g, id_base, dids, cnt, st[0], st[1], st[2], st[3], st[4],
+                      c->cap - 2 * c->mig_cap, c->sort_hist, c->rec0, c->d_ctr));
+        if (device_scan(c, c->sort_hist, nb, c->sort_hist_scan, nullptr)) return 1;
+        PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest_strip<1>",
+                  k_ingest_strip<1><<<nb, kThreads, 0, c->stream>>>(
+                      c->g, id_base, dids, cnt, st[0], st[1], st[2], st[3], st[4],
+                      c->cap - 2 * c->mig_cap, c->sort_hist_scan, c->rec0, c->d_ctr));
+        k_advance_staged<<<1, 1, 0, c->stream>>>(c->d_ctr, c->sort_hist_scan + nb);
+    }
+    return 0;
+}
+
 int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long count, const double *x,
                       const double *y, const double *vx, const double *vy, const double *m) {
     if (!c->uploading) return c->fail("parsim_upload_chunk outside upload_begin/upload_end");
     if (count < 0 || (!ids && (id_base < 0 || id_base + count > c->n_part)))
         return c->fail("upload chunk outside [0, n_part)");
     PS_CUDA(c, cudaSetDevice(c->device));
-    // Staging passes of 8 Mi particles (5 x 64 MiB per set).  The host->device copies of a pass run
-    // on copy_stream into one staging set while k_ingest (on the step stream) interleaves the
-    // previous pass out of the other set, so the copy engine never waits for a kernel.
-    const long long piece = 1 << 23;
-    if (!c->stage[0][0]) {
-        c->stage_cap = (int)std::min<long long>(piece, c->n_part);
-        for (int b = 0; b < 2; b++) {
-            for (int k = 0; k < 5; k++) PS_ALLOC(c, c->stage[b][k], c->stage_cap, false);
-            PS_ALLOC(c, c->stage_ids[b], c->stage_cap, false);
-            PS_CUDA(c, cudaEventCreateWithFlags(&c->ev_copied[b], cudaEventDisableTiming));
-            PS_CUDA(c, cudaEventCreateWithFlags(&c->ev_ingested[b], cudaEventDisableTiming));
-        }
-        PS_CUDA(c, cudaStreamCreateWithFlags(&c->copy_stream, cudaStreamNonBlocking));
-    }
+    if (rank_stage_alloc(c)) return 1;
     const double *src[5] = {x, y, vx, vy, m};
     for (long long off = 0; off < count; off += c->stage_cap) {
         const int cnt = (int)std::min<long long>(c->stage_cap, count - off);
@@ -305,25 +339,7 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
                                        cudaMemcpyHostToDevice, c->copy_stream));
         PS_CUDA(c, cudaEventRecord(c->ev_copied[b], c->copy_stream));
         PS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[b], 0));
-        const unsigned *dids = ids ? c->stage_ids[b] : nullptr;
-        if (c->nranks == 1) {
-            PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest",
-                      k_ingest<<<grid_for(cnt), kThreads, 0, c->stream>>>(
-                          c->g, id_base + off, dids, cnt, st[0], st[1], st[2], st[3], st[4], c->cap, c->rec0,
-                          c->d_ctr));
-        } else {  // stable compaction of this strip's particles: count, scan, write
-            const int nb = grid_for(cnt);
-            PS_LAUNCH(c, K_INGEST, 8.0 * cnt, "k_ingest_strip<0>",
-                      k_ingest_strip<0><<<nb, kThreads, 0, c->stream>>>(
-                          c->g, id_base + off, dids, cnt, st[0], st[1], st[2], st[3], st[4],
-                          c->cap - 2 * c->mig_cap, c->sort_hist, c->rec0, c->d_ctr));
-            if (device_scan(c, c->sort_hist, nb, c->sort_hist_scan, nullptr)) return 1;
-            PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest_strip<1>",
-                      k_ingest_strip<1><<<nb, kThreads, 0, c->stream>>>(
-                          c->g, id_base + off, dids, cnt, st[0], st[1], st[2], st[3], st[4],
-                          c->cap - 2 * c->mig_cap, c->sort_hist_scan, c->rec0, c->d_ctr));
-            k_advance_staged<<<1, 1, 0, c->stream>>>(c->d_ctr, c->sort_hist_scan + nb);
-        }
+        if (rank_ingest_piece(c, id_base + off, ids ? c->stage_ids[b] : nullptr, cnt, st)) return 1;
         PS_CUDA(c, cudaEventRecord(c->ev_ingested[b], c->stream));
         c->stage_pieces++;
     }
@@ -425,7 +441,7 @@ int rank_init_device(Rank *c, long seed) {
                        " generate on the host and upload");
     if (reset_state(c)) return 1;
     const bool strips = c->nranks > 1;
-    const int blocks = 148 * 8;
+    const int blocks = c->sm_count * 8;
     // ids a thread generates are T apart: the whole grid (one strip) or one block (several strips)
     const unsigned long long T = strips ? (unsigned long long)kThreads : (unsigned long long)blocks * kThreads;
     XsJumpTable jt;
@@ -464,7 +480,7 @@ int rank_init_device(Rank *c, long seed) {
 
 int rank_fp64_peak(Rank *c, double *tflops) {
     PS_CUDA(c, cudaSetDevice(c->device));
-    const int iters = 1 << 15, blocks = 148 * 8;
+    const int iters = 1 << 15, blocks = c->sm_count * 8;
     double *d = nullptr;
     PS_ALLOC(c, d, 1, true);
     cudaEvent_t a, b;
@@ -487,7 +503,7 @@ int rank_fp64_peak(Rank *c, double *tflops) {
 // pair interactions per second of k_pair_peak (the force loop's own instruction mix, no memory)
 int rank_pair_peak(Rank *c, double *pairs_per_s) {
     PS_CUDA(c, cudaSetDevice(c->device));
-    const int iters = 1 << 13, blocks = 148 * 8;
+    const int iters = 1 << 13, blocks = c->sm_count * 8;
     double *d = nullptr;
     PS_ALLOC(c, d, 1, true);
     cudaEvent_t a, b;

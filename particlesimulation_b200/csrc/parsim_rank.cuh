@@ -4,6 +4,8 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <condition_variable>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -27,6 +29,47 @@ static_assert(K_COUNT_ <= PARSIM_NKERNELS, "grow PARSIM_NKERNELS");
 struct TimedLaunch {
     cudaEvent_t a, b;
     int k;
+};
+
+struct Rank;
+
+// In-process transport of an oversubscribed / peer-copy group (parsim_create with more strips than
+// GPUs, or PARSIM_TRANSPORT=local): the strips of ONE process exchange by device-to-device copies
+// out of each other's send buffers instead of ncclSend/ncclRecv -- the reference's own way of
+// testing its distributed variant on one machine (mpi/run_tests.sh:9-17: oversubscribed local
+// ranks).  Only the transport differs; pack / unpack kernels and the order rules are the NCCL
+// path's.  One host thread per strip (parsim_capi.cu for_ranks) meets the others at barrier();
+// a strip that failed breaks the barrier so that nobody waits for it for ever.
+struct LocalBus {
+    std::vector<Rank *> ranks;
+    std::mutex mu;
+    std::condition_variable cv;
+    int waiting = 0;
+    unsigned long long generation = 0;
+    bool failed = false;
+
+    int barrier() {  // 0 = everybody arrived, 1 = some strip failed
+        std::unique_lock<std::mutex> lk(mu);
+        if (failed) return 1;
+        const unsigned long long gen = generation;
+        if (++waiting == (int)ranks.size()) {
+            waiting = 0;
+            generation++;
+            cv.notify_all();
+            return 0;
+        }
+        cv.wait(lk, [&] { return generation != gen || failed; });
+        return failed && generation == gen ? 1 : 0;
+    }
+    void abort() {
+        std::lock_guard<std::mutex> lk(mu);
+        failed = true;
+        cv.notify_all();
+    }
+    void rearm() {  // before the next API call (a failed call leaves the context unusable for steps anyway)
+        std::lock_guard<std::mutex> lk(mu);
+        waiting = 0;
+    }
 };
 
 struct Rank {
@@ -113,6 +156,9 @@ struct Rank {
 
     // multi-strip exchange (parsim_exchange.cuh)
     NcclComm comm;
+    LocalBus *bus = nullptr;      // non-null: device-copy transport inside one process, no NCCL
+    cudaEvent_t ev_bus = nullptr; // "my send buffers / boundary rows are ready" (local transport)
+    int sm_count = 148;           // multiprocessors of this device (persistent grids)
     int up = 0, dn = 0;          // neighbour ranks (periodic)
     int mig_cap = 0;             // records per direction
     double *mig_send[2] = {nullptr, nullptr}, *mig_recv[2] = {nullptr, nullptr};
@@ -240,11 +286,14 @@ inline void balance_rows(long ncside, int nranks, const long long *row_counts, l
 
 // first_rows == nullptr: equal-row strips (strip_rows)
 int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, int nranks,
-                int device, const unsigned char *nccl_id, const long *first_rows = nullptr);
+                int device, const unsigned char *nccl_id, const long *first_rows = nullptr,
+                LocalBus *bus = nullptr);
 void rank_destroy(Rank *c);
 int rank_upload_begin(Rank *c);
 int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long count, const double *x,
                       const double *y, const double *vx, const double *vy, const double *m);
+int rank_stage_alloc(Rank *c);
+int rank_ingest_piece(Rank *c, long long id_base, const unsigned *dids, int cnt, double *const st[5]);
 int rank_reset(Rank *c);
 int rank_download(Rank *c, long long capacity, unsigned *ids, double *x, double *y, double *vx,
                   double *vy, double *m, long long *count_out);

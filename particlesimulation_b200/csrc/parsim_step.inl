@@ -130,7 +130,7 @@ static int merge_step(Rank *c, int n_src, int n_surv, bool with_dead) {
         case 16: launch_move<16>(c, a, big); break;
         default: launch_move<32>(c, a, big); break;
         }
-        if (big) k_move_big<<<148 * 2, kThreads, 0, c->stream>>>(g, a);
+        if (big) k_move_big<<<c->sm_count * 2, kThreads, 0, c->stream>>>(g, a);
     });
     std::swap(c->vel_cur, c->vel_alt);
     std::swap(c->m_cur, c->m_alt);
@@ -212,11 +212,9 @@ static int stage_force(Rank *c) {
         case 5: PS_FORCE_TILES(4, 768, 4, 2, false); break;  // persistent tile pipeline (parsim_force_tiles.cuh; comparison)
         case 6: PS_FORCE_TILES(8, 768, 4, 2, false); break;
         case 7: PS_FORCE_TILES(4, 448, 6, 2, false); break;
-        case 8: PS_FORCE_TILES(4, 448, 4, 3, false); break;
-        case 9: PS_FORCE_TILES(4, 768, 4, 2, true); break;
         case 10: PS_FORCE_TB(64, 4, 384, 8, 16); break;   // 2-warp blocks, 16 per SM: 29.7 ms per config-3 run (default 28.8)
         case 11: PS_FORCE_TB(256, 4, 1024, 16, 4); break; // 8-warp blocks, 4 per SM: 28.9 ms
-        case 12: PS_FORCE2(2, 1024, 16, 6); break;  // two targets per thread (parsim_force_pairs2.cuh; unmeasured)
+        case 12: PS_FORCE2(2, 1024, 16, 6); break;  // two targets per thread (parsim_force_pairs2.cuh)
         case 13: PS_FORCE2(4, 1024, 16, 5); break;
         case 14: PS_FORCE2(2, 1024, 16, 8); break;
         default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
@@ -238,7 +236,7 @@ static int stage_lists(Rank *c) {
     // collision search; about 1-5 % of the particles are on it
     if (c->nranks > 1) PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 4 * sizeof(int), c->stream));
     PS_LAUNCH(c, K_CLASSIFY, 0.5 * c->n_alive, "k_classify",
-              k_classify<<<148 * 4, kThreads, 0, c->stream>>>(
+              k_classify<<<c->sm_count * 4, kThreads, 0, c->stream>>>(
                   g, c->partner, &c->d_ctr->n_movers, c->cell_cur, c->cs_cur, c->newcell, c->id_cur,
                   c->n_tomb > 0 ? c->dead_start_cur : nullptr, c->dead_id_cur, c->flags, c->arr_head,
                   c->arr_next, c->pos_alt, c->arr_cnt, c->arr_rec, &c->d_ctr->strays, c->mig_list,
@@ -287,10 +285,10 @@ static int stage_collide(Rank *c) {
         });
         a.nb = c->big_nb; a.inv_h = c->big_nb / g.cellw; a.cap = c->big_cap;
         PS_LAUNCH(c, K_COLLIDE_BIG, 0.0, "k_collide_big",
-                  k_collide_big<<<148, kThreads, staging_bytes(a.nb * a.nb, a.cap), c->stream>>>(
+                  k_collide_big<<<c->sm_count, kThreads, staging_bytes(a.nb * a.nb, a.cap), c->stream>>>(
                       a, c->huge_items, c->d_big_count + 1));
         PS_LAUNCH(c, K_COLLIDE_BIG, 0.0, "k_collide_huge",
-                  k_collide_huge<<<148 * 8, kThreads, 0, c->stream>>>(a, c->huge_items, c->d_big_count + 1));
+                  k_collide_huge<<<c->sm_count * 8, kThreads, 0, c->stream>>>(a, c->huge_items, c->d_big_count + 1));
     } else {
         PS_LAUNCH(c, K_COLLIDE, 21.0 * n_tot + 8.0 * g.ncells, "k_collide_find",
                   k_collide_find<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
@@ -300,7 +298,7 @@ static int stage_collide(Rank *c) {
     }
     if (c->nranks > 1) PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 4 * sizeof(int), c->stream));
     PS_LAUNCH(c, K_RESOLVE, 10.0 * n_tot, "k_resolve",
-              k_resolve<<<std::min(grid_for(n_tot, kThreads * kResolveRows), 148 * 8), kThreads, 0, c->stream>>>(
+              k_resolve<<<std::min(grid_for(n_tot, kThreads * kResolveRows), c->sm_count * 8), kThreads, 0, c->stream>>>(
                   g, n_tot, c->n_alive, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,
                   c->vel_cur, c->id_cur, c->fate, c->count, c->dead_new_count, c->mv_head, c->dm_head,
                   c->mv_next, c->grave_pos, c->grave_vel, c->grave_id, c->grave_cell, c->d_ctr, c->mig_list,

@@ -1,6 +1,13 @@
-"""Row-strip multi-GPU path (NCCL halos + migrants): N strips must reproduce the single-GPU run
+"""Row-strip multi-GPU path (halos + migrants): N strips must reproduce the single-GPU run
 bit for bit -- same collision count, same alive set, identical positions -- because every
-reduction has a fixed order that does not depend on the decomposition."""
+reduction has a fixed order that does not depend on the decomposition.
+
+Transport: with at least N GPUs the strips talk over NCCL (one GPU each); with fewer -- the
+driver's 1-GPU box -- the library oversubscribes the GPUs and the strips exchange by device
+copies (`LocalBus`, csrc/parsim_rank.cuh), the reference's own way of testing its distributed
+variant on one machine (mpi/run_tests.sh:9-17: local oversubscribed ranks).  Only the
+transport differs: pack / unpack kernels, order rules and results are the same.  On a
+multi-GPU box both transports run (`transport` parameter)."""
 import json
 import os
 import subprocess
@@ -20,19 +27,35 @@ def ngpu():
     return torch.cuda.device_count()
 
 
+def pick_transport(transport, n_gpus, monkeypatch):
+    """"auto" = what parsim_create picks (NCCL with enough GPUs, else device copies); "local" forces
+    the device-copy transport and only adds something where "auto" is NCCL."""
+    if ngpu() < 1:
+        pytest.skip("needs a GPU")
+    if transport == "local":
+        if ngpu() < n_gpus:
+            pytest.skip("auto is already the device-copy transport here")
+        monkeypatch.setenv("PARSIM_TRANSPORT", "local")
+    else:
+        monkeypatch.delenv("PARSIM_TRANSPORT", raising=False)
+
+
+TRANSPORTS = ["auto", "local"]
+
+
 CASES = [(1, 10, 100, 100000, 5), (5, 1, 20, 20000, 4), (-7, 10, 50, 20000, 5), (3, 1, 2, 200, 3),
          (9, 0.3, 4, 3000, 6), (1, 2, 3, 10, 3), (7, 30, 300, 2000000, 4)]
 
 
+@pytest.mark.parametrize("transport", TRANSPORTS)
 @pytest.mark.parametrize("n_gpus", [2, 3, 4, 8])
 @pytest.mark.parametrize("case", CASES, ids=lambda c: " ".join(map(str, c)))
-def test_strips_match_single_gpu(case, n_gpus):
+def test_strips_match_single_gpu(case, n_gpus, transport, monkeypatch):
     seed, side, nc, n, steps = case
-    if ngpu() < n_gpus:
-        pytest.skip(f"needs {n_gpus} GPUs")
+    pick_transport(transport, n_gpus, monkeypatch)
     if n_gpus > nc:
         pytest.skip("more strips than rows")
-    os.environ["PARSIM_CAPACITY_PCT"] = "400"  # tiny / skewed cases: generous strip capacity
+    monkeypatch.setenv("PARSIM_CAPACITY_PCT", "400")  # tiny / skewed cases: generous strip capacity
     one = ParticleSimulation(seed, side, nc, n)
     many = ParticleSimulation(seed, side, nc, n, n_gpus=n_gpus)
     for t in range(steps):
@@ -46,13 +69,13 @@ def test_strips_match_single_gpu(case, n_gpus):
     one.close(); many.close()
 
 
+@pytest.mark.parametrize("transport", TRANSPORTS)
 @pytest.mark.parametrize("n_gpus", [2, 4])
-def test_exchange_overflow_round(n_gpus, monkeypatch):
+def test_exchange_overflow_round(n_gpus, transport, monkeypatch):
     """More records than the eager slots of the one-round exchange: the second round carries the
     rest (neighbour messages and the far all-gather), same bits as one GPU."""
     import oracle_lib as ol
-    if ngpu() < n_gpus:
-        pytest.skip(f"needs {n_gpus} GPUs")
+    pick_transport(transport, n_gpus, monkeypatch)
     monkeypatch.setenv("PARSIM_CAPACITY_PCT", "400")
     monkeypatch.setenv("PARSIM_EAGER_RECS", "3")
     for case in ("dense", "far"):
@@ -75,14 +98,14 @@ def test_exchange_overflow_round(n_gpus, monkeypatch):
         one.close(); many.close()
 
 
+@pytest.mark.parametrize("transport", TRANSPORTS)
 @pytest.mark.parametrize("n_gpus", [2, 3, 4, 8])
-def test_far_jumps_cross_strips(n_gpus):
+def test_far_jumps_cross_strips(n_gpus, transport, monkeypatch):
     """Close encounters throw particles many rows away (any strip, not just the neighbour): the
     far-record exchange must keep N strips bitwise equal to one GPU."""
     import oracle_lib as ol
-    if ngpu() < n_gpus:
-        pytest.skip(f"needs {n_gpus} GPUs")
-    os.environ["PARSIM_CAPACITY_PCT"] = "400"
+    pick_transport(transport, n_gpus, monkeypatch)
+    monkeypatch.setenv("PARSIM_CAPACITY_PCT", "400")
     side, nc, arrs = ol.far_jump_case()
     n = len(arrs[0])
     one = ParticleSimulation(0, side, nc, n, arrays=arrs)
@@ -99,18 +122,18 @@ def test_far_jumps_cross_strips(n_gpus):
     one.close(); many.close()
 
 
+@pytest.mark.parametrize("transport", TRANSPORTS)
 @pytest.mark.parametrize("n_gpus", [2, 3, 4, 8])
 @pytest.mark.parametrize("case", [(-7, 10, 50, 20000, 5), (-3, 4, 40, 60000, 4), (5, 1, 20, 20000, 3)],
                          ids=lambda c: " ".join(map(str, c)))
-def test_equal_particle_strips_match_single_gpu(case, n_gpus):
+def test_equal_particle_strips_match_single_gpu(case, n_gpus, transport, monkeypatch):
     """strips cut by particle count (clustered, negative-seed inputs) instead of by
     row count -- same bits as one GPU, default strip capacity, and an even load."""
     from particlesimulation_b200 import strips
     from particlesimulation_b200.simulation import init_particles
     seed, side, nc, n, steps = case
-    if ngpu() < n_gpus:
-        pytest.skip(f"needs {n_gpus} GPUs")
-    os.environ.pop("PARSIM_CAPACITY_PCT", None)  # balanced strips must fit the default capacity
+    pick_transport(transport, n_gpus, monkeypatch)
+    monkeypatch.delenv("PARSIM_CAPACITY_PCT", raising=False)  # balanced strips must fit the default capacity
     arrs = init_particles(seed, side, nc, n)
     first = strips.balanced_rows(strips.row_counts(arrs[1], side, nc), n_gpus)
     owner = strips.strip_of_particles(arrs[1], side, nc, n_gpus, first)
@@ -131,14 +154,34 @@ def test_equal_particle_strips_match_single_gpu(case, n_gpus):
     one.close(); many.close()
 
 
+def test_group_upload_paths_agree(monkeypatch):
+    """In-process groups copy every piece host->device ONCE and all strips ingest from that copy
+    (PARSIM_SHARED_UPLOAD, the default where the GPUs can reach each other); the per-strip copy is
+    the fallback.  Same records either way."""
+    if ngpu() < 1:
+        pytest.skip("needs a GPU")
+    monkeypatch.setenv("PARSIM_CAPACITY_PCT", "400")
+    res = []
+    for shared in ("1", "0"):
+        monkeypatch.setenv("PARSIM_SHARED_UPLOAD", shared)
+        g = ParticleSimulation(-7, 10, 50, 20000, n_gpus=3)
+        g.simulate(3)
+        res.append((g.result(), g.dump()))
+        g.close()
+    assert res[0][0] == res[1][0]
+    for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+        assert np.array_equal(res[0][1][k], res[1][1][k]), k
+
+
 def test_cli_balanced_strips_match_single_gpu():
-    if ngpu() < 2:
-        pytest.skip("needs 2 GPUs")
+    if ngpu() < 1:
+        pytest.skip("needs a GPU")
     exe = os.path.join(ROOT, "particlesimulation_b200", "parsim")
     args = ["-7", "10", "50", "200000", "10"]  # golden: 5.957 6.317 / 46580 (tests/golden/reference_runs.jsonl)
     one = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300)
-    env = dict(os.environ, PARSIM_NGPU=str(min(4, ngpu())), PARSIM_BALANCE="1")
+    env = dict(os.environ, PARSIM_NGPU="4", PARSIM_BALANCE="1")  # fewer than 4 GPUs: oversubscribed
     env.pop("PARSIM_CAPACITY_PCT", None)
+    env.pop("PARSIM_TRANSPORT", None)
     many = subprocess.run([exe] + args, capture_output=True, text=True, timeout=300, env=env)
     assert one.returncode == 0 and many.returncode == 0, one.stderr + many.stderr
     assert one.stdout == many.stdout
@@ -146,8 +189,8 @@ def test_cli_balanced_strips_match_single_gpu():
 
 
 def test_bad_strip_rows_are_rejected():
-    if ngpu() < 2:
-        pytest.skip("needs 2 GPUs")
+    if ngpu() < 1:
+        pytest.skip("needs a GPU")
     from particlesimulation_b200.simulation import ParsimError
     for rows in ([0, 5, 5, 10][:3], [0, 0, 10], [1, 5, 10], [0, 5, 9]):
         with pytest.raises((ParsimError, ValueError)):

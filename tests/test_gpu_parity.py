@@ -223,23 +223,36 @@ def test_collision_search_paths_agree(case, monkeypatch):
         assert np.array_equal(res["pairs"][1][k], res["grid"][1][k]), k
 
 
+FORCE_VARIANTS = [0, 1, 2, 3, 4, 5, 6, 7, 10, 11, 12, 13, 14]  # = what rank_create accepts (csrc/parsim_rank.cu)
+
+
+def test_unknown_force_variant_is_rejected(monkeypatch):
+    from particlesimulation_b200 import ParsimError
+    for v in ("8", "9", "15", "-1"):
+        monkeypatch.setenv("PARSIM_FORCE_VARIANT", v)
+        with pytest.raises(ParsimError):
+            ParticleSimulation(1, 2, 3, 10)
+
+
 @pytest.mark.parametrize("case", [(1, 10, 100, 100000, 4), (3, 100, 1000, 800000, 3), (5, 1, 20, 200000, 2),
                                   (-7, 10, 50, 200000, 4), (9, 0.3, 4, 3000, 4), (2, 7, 3, 2, 2)],
                          ids=lambda c: " ".join(map(str, c)))
 def test_force_kernel_variants_agree(case, monkeypatch):
-    """Every instantiation of the force + integration kernel -- block per tile with or without the
-    staged neighbourhood, deep unroll, and the persistent TMA / mbarrier pipeline (k_force_tiles,
-    variants 5-7) -- sums in the same order, so the runs must agree bit for bit with the default
-    (which picks its instantiation from the occupancy)."""
+    """Every instantiation of the force + integration kernel that PARSIM_FORCE_VARIANT accepts --
+    block per tile with or without the staged neighbourhood, deep unroll, 64 / 256-thread blocks,
+    the persistent TMA / mbarrier pipeline (k_force_tiles, 5-7) and two targets per thread
+    (k_force_integrate2, 12-14) -- sums in the same order, so the runs must agree bit for bit with
+    the default (which picks its instantiation from the occupancy)."""
     seed, side, nc, n, steps = case
     res = {}
-    for variant in range(0, 8):  # variant 8 (three buffers) has not run on a GPU yet: add it once it has
+    variants = FORCE_VARIANTS
+    for variant in variants:
         monkeypatch.setenv("PARSIM_FORCE_VARIANT", str(variant))
         g = ParticleSimulation(seed, side, nc, n)
         g.simulate(steps)
         res[variant] = (g.result(), g.dump())
         g.close()
-    for variant in range(1, 8):
+    for variant in variants[1:]:
         assert res[variant][0] == res[0][0], variant
         for k in ("x", "y", "vx", "vy", "m", "alive"):
             assert np.array_equal(res[variant][1][k], res[0][1][k]), (variant, k)
