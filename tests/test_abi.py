@@ -76,6 +76,22 @@ def test_no_cpu_fallback():
         assert p.returncode == 1 and p.stderr.startswith("Error: ") and p.stdout == ""
 
 
+def test_integration_patch_is_the_compiled_one():
+    """INTEGRATION.md section 2 shows the source-level patch; oracle/Makefile compiles exactly that
+    text (oracle/simulate_b200.inc) into the reference's serial program.  No GPU here: the patched
+    program must then fail the reference's way ("Error: ...", exit 1) -- no CPU fallback."""
+    inc = open(os.path.join(ROOT, "oracle", "simulate_b200.inc")).read()
+    assert inc in open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    exe = os.path.join(ROOT, "oracle", "_ref", "parsim-patched")
+    if not os.path.exists(exe):
+        pytest.skip("reference sources not present: oracle/_ref/parsim-patched not built")
+    if not has_gpu():
+        p = subprocess.run([exe, "1", "2", "3", "10", "1"], capture_output=True, text=True)
+        assert p.returncode == 1 and p.stderr.startswith("Error: ") and p.stdout == ""
+    p = subprocess.run([exe, "1", "2", "3"], capture_output=True, text=True)
+    assert p.returncode == 1 and p.stderr.startswith("Error: Usage:")
+
+
 def test_cli_usage_error():
     cli = os.path.join(ROOT, "particlesimulation_b200", "parsim")
     if not os.path.exists(cli):

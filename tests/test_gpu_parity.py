@@ -301,6 +301,24 @@ def test_cli_matches_reference_output():
         assert p.stderr.strip().endswith("s")
 
 
+@pytest.mark.parametrize("args", ["1 2 3 10 1", "1 10 100 1000000 20", "-10 3 3 100 4", "5 1 20 20000 5"])
+def test_patched_reference_matches_reference(args):
+    """INTEGRATION.md section 2, compiled: the reference's own serial program with simulate()
+    replaced by the C-ABI calls (oracle/Makefile -> oracle/_ref/parsim-patched; constructor,
+    init_particles, print_result and main are the reference's) prints what the unmodified
+    reference prints.  BASELINE configs[0] and configs[1] and two of the reference's vectors."""
+    patched = os.path.join(ROOT, "oracle", "_ref", "parsim-patched")
+    ref = os.path.join(ROOT, "oracle", "_ref", "parsim")
+    if not (os.path.exists(patched) and os.path.exists(ref)):
+        pytest.skip("oracle/_ref not built (reference sources absent at build time)")
+    a = subprocess.run([patched] + args.split(), capture_output=True, text=True, timeout=300)
+    b = subprocess.run([ref] + args.split(), capture_output=True, text=True, timeout=300)
+    assert a.returncode == 0, a.stderr
+    assert b.returncode == 0, b.stderr
+    assert a.stdout == b.stdout
+    assert a.stderr.strip().endswith("s")
+
+
 @pytest.mark.parametrize("args", ["1 2 3 10 3", "5 1 20 2000 3", "-10 3 3 100 4"])
 def test_cli_trace_matches_oracle(args, tmp_path):
     """PARSIM_TRACE writes the dump the reference keeps commented out in simulate()
