@@ -11,6 +11,12 @@ workload is BASELINE.json configs[2] (seed=7 side=100 ncside=1000 n_part=1e8 n_s
 HBM-roofline run; configs[1] is selectable with --workload config2).  At N>1 the same density
 is weak-scaled: n_part = N*1e8, ncside = round(1000*sqrt(N)), side = ncside/10, row strips.
 
+At N=1 the default line also carries `extra`: one short device-timed sub-line for each of the other
+BASELINE configurations (configs[1], configs[3]'s density at 1e8 particles, configs[4]) with their
+collision counts and pins; at N=2/4/8 `extra.config4` is the member of SURVEY 8(d)'s config-4
+series for that GPU count (at 8 GPUs BASELINE configs[3] itself).  Expected collision counts come
+from tests/golden/bench_pins.json.
+
 value  : device-timed, initial state already resident in HBM (parsim_reset + parsim_run)
 e2e    : host-timed through the C ABI with HOST buffers: parsim_upload from pinned memory,
          parsim_run, parsim_result -- host<->device copies inside the timed region
@@ -52,7 +58,7 @@ def pinned_collisions(seed, side, nc, n, steps):
 # bounded CPU sample of the same density and cell size (config 3: ppc = 100, cell = 0.1, 1/16 of the
 # particles: 10-30 s on one host core, a few seconds with every core under OpenMP)
 CPU_SAMPLE = {"config3": "7 25 250 6250000 10", "config2": "1 10 100 1000000 20",
-              "config4w": "3 88.4 884 6250000 10"}
+              "config4w": "3 88.4 884 6250000 10", "config5": "5 1 20 100000 50"}
 
 
 def workload_for(name, n_gpus, scale):
@@ -291,23 +297,88 @@ def main_ours(a):
     value = work * a.steps / (ms_total / 1e3)
 
     # ---- end-to-end leg: host buffers through the C ABI -------------------------------------
+    upload_s = [0.0]
+
     def one_e2e():
+        t_up = time.perf_counter()
         if world == 1:
             sim.upload_ptrs([t.data_ptr() for t in pinned])
         else:
             sim.upload_strip_ptrs(cnt, pinned_ids.data_ptr(), [t.data_ptr() for t in pinned])
+        upload_s[0] += time.perf_counter() - t_up  # parsim_upload returns when the records are on the device
         sim.simulate(nstep)
         return sim.result()
 
     one_e2e()
     barrier()
+    upload_s[0] = 0.0
     t0 = time.perf_counter()
     for _ in range(a.steps):
         res = one_e2e()
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     e2e_value = work * a.steps / e2e_s
+    h2d_bytes = 40 * cnt + (4 * cnt if world > 1 else 0)
+    h2d_gbs_slowest = h2d_bytes * a.steps / max_over_ranks(upload_s[0]) / 1e9
     assert res[2] == collisions, "end-to-end run disagrees with the device-resident run"
+
+    # ---- the other BASELINE configurations, one short sub-line each (same code, same library) -----
+    def side_run(label, tup, reps=3, pin_note=None):
+        """Device-timed runs of another configuration on this rank set; returns the sub-line."""
+        sd, sside, snc, sn, sstep = tup
+        ids_kw = {}
+        if world > 1:
+            blob2 = None
+            if rank == 0:
+                buf2 = (C.c_ubyte * 128)()
+                if _lib.load().parsim_nccl_unique_id(buf2):
+                    raise SystemExit("parsim_nccl_unique_id failed")
+                blob2 = bytes(buf2)
+            ids_kw = dict(rank=rank, nranks=world, device=local, nccl_id=grp.broadcast_bytes(blob2))
+        sim2 = ParticleSimulation(sd, sside, snc, sn, device_init=True, options={"keep_initial": 1}, **ids_kw)
+        st2 = torch.cuda.ExternalStream(sim2.lib.parsim_stream(sim2._ctx), device=torch.device("cuda", local))
+        sim2.simulate(sstep)  # warm-up run
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record(st2)
+        for _ in range(reps):
+            sim2.reset()
+            sim2.simulate(sstep)
+        a1.record(st2)
+        barrier()
+        ms2 = max_over_ranks(a0.elapsed_time(a1)) / reps
+        rx, ry, rc = sim2.result()
+        sim2.close()
+        exp, src = pinned_collisions(sd, sside, snc, sn, sstep)
+        return {"workload": f"{label}: seed={sd} side={sside:g} ncside={snc} n_part={sn} n_step={sstep}",
+                "ms_per_run": ms2, "value": float(sn) * sstep / (ms2 / 1e3), "unit": "particle-steps/s",
+                "timing": f"CUDA events around {reps} reset+run repetitions, no instrumentation",
+                "result": {"x0": round(rx, 3), "y0": round(ry, 3), "collisions": rc, "reference_collisions": exp,
+                           "parity_ok": (rc == exp) if exp is not None else None,
+                           "pin": src if exp is not None else (pin_note or "no pinned count for this tuple")}}
+
+    # FP64 ceilings measured on this box (MEASURED_PEAKS.json has none): independent FMA chains, and the
+    # force loop's own 13-instruction pair mix on register operands
+    fp64_peak = sim.fp64_peak_tflops() if rank == 0 else None
+    pair_peak = sim.pair_peak() if rank == 0 else None
+    extra = {}
+    if a.workload == "config3" and a.scale == 1.0 and not a.no_extras:
+        sim.close()  # free the 24 GB of the main workload first
+        if world == 1:
+            extra["config2"] = side_run("BASELINE configs[1]", WORKLOADS["config2"], reps=5)
+            extra["config4_density"] = side_run("BASELINE configs[3] density (8 per cell) at 1e8 particles on one GPU",
+                                                WORKLOADS["config4w"])
+            extra["config5"] = side_run(
+                "BASELINE configs[4]", WORKLOADS["config5"],
+                pin_note="unavailable: the unmodified serial reference dies with SIGSEGV at this size (a close "
+                         "encounter throws a particle more than a box length, serial/parsim.cpp:171-177,:276-280); "
+                         "pinned at 1/10 and 1/100 of the particles in tests/golden/reference_runs.jsonl")
+        elif world in CONFIG4_SERIES:
+            sside, snc, sn = CONFIG4_SERIES[world]
+            extra["config4"] = side_run(
+                "BASELINE configs[3]" + ("" if world == 8 else f" weak-scaling series member for {world} GPUs"),
+                (3, sside, snc, sn, 10))
+        sim = None
 
     if rank != 0:
         return
@@ -325,13 +396,18 @@ def main_ours(a):
                     "hbm_frac": gbs / hbm_peak}
     d = kern[dom]
     achieved = d["bytes"] / (d["ms"] * 1e-3) / 1e9
-    fp64_peak = sim.fp64_peak_tflops()
     force_flops = 17.0 * st["force_pairs"] / 2 + 120.0 * st["alive_particle_steps"]
     coll_flops = 7.0 * st["collision_pairs"] / 2
     f_ms, c_ms = kern["force_integrate"]["ms"], kern["collide_find"]["ms"]
-    fp64 = {"peak_tflops_measured_fma_chain": fp64_peak,
+    # interactions the force kernel evaluates: ordered in-cell pairs + 8 centres of mass per alive particle
+    interactions = st["force_pairs"] + 8.0 * st["alive_particle_steps"]
+    pair_rate = interactions / (f_ms * 1e-3)
+    fp64 = {"peak_tflops_measured_fma_chain": fp64_peak, "pair_mix_peak_per_s": pair_peak,
+            "peaks_source": "measured live on this GPU by parsim_fp64_peak / parsim_pair_peak (the stated fallback "
+                            "for peaks MEASURED_PEAKS.json does not hold)",
             "force_integrate": {"algorithmic_tflops": force_flops / (f_ms * 1e-3) / 1e12,
                                 "frac": force_flops / (f_ms * 1e-3) / 1e12 / fp64_peak,
+                                "interactions_per_s": pair_rate, "frac_of_pair_mix_peak": pair_rate / pair_peak,
                                 "ordered_pairs_per_step": st["force_pairs"] / a.steps},
             "collide_find": {"algorithmic_tflops": coll_flops / (c_ms * 1e-3) / 1e12,
                              "frac": coll_flops / (c_ms * 1e-3) / 1e12 / fp64_peak,
@@ -344,34 +420,50 @@ def main_ours(a):
         traffic_info = json.load(open(tp)).get(a.workload, {}).get(dom)
         if traffic_info:
             traffic = traffic_info["dram_bytes_per_launch"] / 1e9  # GB per launch, like `achieved` x time
+    hbm_part = {"achieved": achieved, "peak": hbm_peak, "unit": "GB/s", "frac": achieved / hbm_peak,
+                "traffic": traffic, "traffic_unit": "GB per launch (ncu dram read+write)",
+                "algorithmic_GB_per_launch": d["bytes"] / max(d["launches"], 1) / 1e9, "ncu": traffic_info,
+                "peak_source": peak_src}
+    timing_note = ("CUDA events around every launch, on the launching stream, in a second pass over the same K runs "
+                   "(ms_per_step_instrumented); the timed pass behind `value` runs without them")
+    if dom == "force_integrate" and pair_rate / pair_peak > achieved / hbm_peak:
+        # the in-cell pair loop decides: report the kernel against the FP64 roof, HBM beside it
+        roofline = {"kernel": dom, "bound": "fp64", "achieved": pair_rate / 1e9, "peak": pair_peak / 1e9,
+                    "unit": "G pair interactions/s (13 FP64 + 1 MUFU each)", "frac": pair_rate / pair_peak,
+                    "traffic": traffic, "peak_source": "parsim_pair_peak measured live (not in MEASURED_PEAKS.json)",
+                    "hbm": hbm_part, "timing": timing_note}
+    else:
+        roofline = {"kernel": dom, "bound": "hbm", **hbm_part, "timing": timing_note}
+    wl_note = ""
+    if world > 1:
+        wl_note = (" (BASELINE configs[3] density weak-scaling series, SURVEY 8(d)" + ("; at 8 GPUs BASELINE configs[3] itself)" if world == 8 else ")")
+                   if a.workload == "config4w" else " (BASELINE configs[2] density weak-scaled by row strips)")
     out = {
         "metric": "particle-steps/s", "value": value, "unit": "particle-steps/s", "n_gpus": a.gpus,
         "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_total / a.steps,
         "ms_per_step_instrumented": ms_stats / a.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": f"synthetic (seeded init_particles, seed {seed}, generated on the device)",
-        "config": {"workload": f"{a.workload}: seed={seed} side={side:g} ncside={nc} n_part={n} n_step={nstep}"
-                               + (" (BASELINE configs[2] density weak-scaled by row strips)" if world > 1 else ""),
+        "config": {"workload": f"{a.workload}: seed={seed} side={side:g} ncside={nc} n_part={n} n_step={nstep}" + wl_note,
                    "step": f"one full run of {nstep} timesteps from the initial condition",
-                   "l2": "inputs (4.4 GB/GPU) are larger than L2; no flush needed",
+                   "l2": f"inputs ({44e-9 * n / world:.2g} GB/GPU) " + ("are larger than L2; no flush needed" if 44 * n / world > 2.6e8
+                                                                        else "fit L2: a small latency-bound case, not a bandwidth measurement"),
                    "parallelism": f"row strips x{world}" if world > 1 else "single GPU"},
         "clocks": clk,
-        "e2e": {"value": e2e_value, "unit": "particle-steps/s", "h2d_bytes_per_step": 40 * cnt + (4 * cnt if world > 1 else 0),
-                "d2h_bytes_per_step": 24, "ms_per_step": 1e3 * e2e_s / a.steps},
+        "e2e": {"value": e2e_value, "unit": "particle-steps/s", "h2d_bytes_per_step": h2d_bytes,
+                "d2h_bytes_per_step": 24, "ms_per_step": 1e3 * e2e_s / a.steps,
+                "h2d_GBps_slowest_rank": h2d_gbs_slowest,
+                "inputs": "pinned host arrays of this rank's strip (x, y, vx, vy, m" + (", id" if world > 1 else "") + ")"},
         "gpu_launches": int(sum(v["launches"] for v in kern.values())),
-        "roofline": {"kernel": dom, "bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved / hbm_peak, "traffic": traffic, "traffic_unit": "GB per launch (ncu dram read+write)",
-                     "algorithmic_GB_per_launch": d["bytes"] / max(d["launches"], 1) / 1e9,
-                     "ncu": traffic_info, "peak_source": peak_src,
-                     "timing": "CUDA events around every launch, on the launching stream, in a second pass over the "
-                               "same K runs (ms_per_step_instrumented); the timed pass behind `value` runs without them",
-                     "note": "the dominant kernel is FP64-CUDA-core bound (in-cell pair loop): ncu shows the FP64 pipe "
-                             "69-78 % busy in every launch, see fp64"},
+        "roofline": roofline,
         "fp64": fp64, "kernels": table,
         "result": {"x0": round(x0, 3), "y0": round(y0, 3), "collisions": collisions,
-                   "reference_collisions": expect, "parity_ok": (collisions == expect) if expect else None},
+                   "reference_collisions": expect, "parity_ok": (collisions == expect) if expect is not None else None,
+                   "pin": pinned_collisions(seed, side, nc, n, nstep)[1]},
         "counters": {k: st[k] / a.steps for k in ("movers", "strays", "deaths", "migrants", "alive_particle_steps")},
     }
+    if extra:
+        out["extra"] = extra
     if world == 1 and not a.no_cpu_baseline:
         # north_star: the reference's serial, OpenMP and MPI builds on this box's host cores, same run
         cb = cpu_baseline(a.workload, 1)
@@ -393,6 +485,7 @@ if __name__ == "__main__":
     ap.add_argument("--workload", default="config3", choices=sorted(WORKLOADS))
     ap.add_argument("--scale", type=float, default=1.0, help="shrink the workload (smoke tests only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the sub-lines of the other BASELINE configurations")
     a = ap.parse_args()
     if a.impl == "reference":
         main_reference(a)
