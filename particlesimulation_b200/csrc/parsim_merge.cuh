@@ -49,7 +49,7 @@ k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner, const int *
           const unsigned *__restrict__ id, unsigned char *__restrict__ fate, int *count,
           int *dead_new_count, int *mv_head, int *dm_head, int *__restrict__ mv_next,
           double2 *__restrict__ grave_pos, double2 *__restrict__ grave_vel,
-          unsigned *__restrict__ grave_id, int *__restrict__ grave_cell, Counters *ctr,
+          unsigned *__restrict__ grave_id, int *__restrict__ grave_cell, int grave_cap, Counters *ctr,
           int *__restrict__ late_list, int *late_count, int late_cap) {
     constexpr int kWarps = kThreads / 32;
     __shared__ int warp_dying[kResolveRows][kWarps];
@@ -133,6 +133,7 @@ k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner, const int *
             for (int r = 0; r < kResolveRows; r++)
                 for (int w = 0; w < kWarps; w++) { int v = warp_dying[r][w]; warp_dying[r][w] = tot; tot += v; }
             tile_base = tot ? atomicAdd(&ctr->grave_count, tot) : 0;
+            if (tile_base + tot > grave_cap) ctr->error = DE_CAPACITY;  // more deaths than this strip has slots
         }
         __syncthreads();
 #pragma unroll
@@ -141,6 +142,7 @@ k_resolve(Geom g, int n, int n_res, const int *__restrict__ partner, const int *
             if (ft == FATE_DEAD_HERE || ft == FATE_DEAD_MOVED || ft == FATE_LEFT_DEAD) {
                 const int i = (int)(t0 + (long long)r * kThreads + threadIdx.x);
                 const int slot = tile_base + warp_dying[r][warp] + __popc(dying_mask[r] & ((1u << lane) - 1u));
+                if (slot >= grave_cap) continue;  // reported through ctr->error above
                 grave_pos[slot] = pos[i];
                 grave_vel[slot] = vel[i];
                 grave_id[slot] = id[i];

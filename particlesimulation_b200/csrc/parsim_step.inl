@@ -301,7 +301,7 @@ static int stage_collide(Rank *c) {
               k_resolve<<<std::min(grid_for(n_tot, kThreads * kResolveRows), c->sm_count * 8), kThreads, 0, c->stream>>>(
                   g, n_tot, c->n_alive, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,
                   c->vel_cur, c->id_cur, c->fate, c->count, c->dead_new_count, c->mv_head, c->dm_head,
-                  c->mv_next, c->grave_pos, c->grave_vel, c->grave_id, c->grave_cell, c->d_ctr, c->mig_list,
+                  c->mv_next, c->grave_pos, c->grave_vel, c->grave_id, c->grave_cell, c->cap, c->d_ctr, c->mig_list,
                   c->nranks > 1 ? c->mig_hdr_send + 3 : nullptr, c->mig_list_cap));
     PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
@@ -316,6 +316,9 @@ static int stage_collide(Rank *c) {
     // the tombstone lists change only when somebody died or a tombstone arrived: otherwise they
     // stay where they are (no scan, no copy)
     const bool with_dead = deaths > 0 || tomb_in > 0;
+    if ((long long)c->n_tomb + deaths + tomb_in > c->cap)
+        return c->fail("strip capacity exceeded by tombstones (dead particles that lie in this strip): raise "
+                       "PARSIM_CAPACITY_PCT");
     if (merge_step(c, n_src, n_src - deaths, with_dead)) return 1;
     c->n_tomb += deaths + tomb_in;  // upper bound; exact total is dead_start[ncells]
     if (c->nranks == 1) {
