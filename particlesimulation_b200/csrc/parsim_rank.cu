@@ -117,7 +117,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     if (const char *e = getenv("PARSIM_FORCE_VARIANT")) c->force_variant = atoi(e);
     {   // only instantiations that the variant-agreement test covers (tests/test_gpu_parity.py)
         const int v = c->force_variant;
-        if (!(v >= 0 && v <= 7) && !(v >= 10 && v <= 14))
+        if (!(v >= 0 && v <= 7) && !(v >= 10 && v <= 15))
             return c->fail("PARSIM_FORCE_VARIANT: unknown force-kernel variant " + std::to_string(v));
     }
     if (c->force_variant >= 5 && c->force_variant <= 7) {  // persistent tile pipeline (parsim_force_tiles.cuh)

@@ -13,6 +13,7 @@
 #include "parsim_kernels.cuh"
 #include "parsim_force_tiles.cuh"
 #include "parsim_force_pairs2.cuh"
+#include "parsim_force_n3.cuh"
 #include "parsim_merge.cuh"
 #include "parsim_sort.cuh"
 #include "parsim_collide.cuh"

@@ -217,6 +217,20 @@ static int stage_force(Rank *c) {
         case 12: PS_FORCE2(2, 1024, 16, 6); break;  // two targets per thread (parsim_force_pairs2.cuh)
         case 13: PS_FORCE2(4, 1024, 16, 5); break;
         case 14: PS_FORCE2(2, 1024, 16, 8); break;
+        case 15: {  // Newton's third law inside the cell, warp per cell (parsim_force_n3.cuh)
+            ForceArgs fa;
+            fa.pos_in = c->pos_cur; fa.m = c->m_cur; fa.cell_start = c->cs_cur; fa.com_xy = c->com_xy; fa.com_m = c->com_m;
+            fa.pos_out = c->pos_alt; fa.posf_out = c->posf; fa.vel = c->vel_cur; fa.newcell = c->newcell; fa.flags = c->flags;
+            fa.mover_list = c->partner; fa.n_movers = &c->d_ctr->n_movers; fa.dbg_acc = c->dbg_acc;
+            const double now = (double)c->n_alive / std::max(1, c->g.ncells);
+            const double want = now + 4.0 * sqrt(now) + 2.0;  // cells above 32 KMAX entries take the slow ordered sweep
+            const int grid = grid_for(c->g.ncells, kN3Warps);
+            if (want <= 64) k_force_n3<2, 6><<<grid, kN3Warps * 32, 0, c->stream>>>(c->g, fa);
+            else if (want <= 96) k_force_n3<3, 5><<<grid, kN3Warps * 32, 0, c->stream>>>(c->g, fa);
+            else if (want <= 128) k_force_n3<4, 4><<<grid, kN3Warps * 32, 0, c->stream>>>(c->g, fa);
+            else k_force_n3<6, 3><<<grid, kN3Warps * 32, 0, c->stream>>>(c->g, fa);
+            break;
+        }
         default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
         }
     });
