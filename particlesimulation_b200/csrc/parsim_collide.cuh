@@ -19,7 +19,7 @@ namespace parsim {
 
 struct CollideArgs {
     Geom g;
-    int n_res;            // residents [0, n_res), guests from other strips behind them
+    const int *n_res_ptr; // residents [0, *n_res_ptr), guests from other strips behind them
     double thr2;          // squared-distance threshold (see k_collide_find)
     const double2 *pos;   // post-move positions
     const int *cell, *cell_start, *newcell;
@@ -38,7 +38,8 @@ struct CollideArgs {
 
 __device__ __forceinline__ unsigned long long entry_key(const CollideArgs &a, int k) {
     if (a.flags[k] & F_REMOVED) {  // an arrival: appended after the bin-time entries, by (source cell, id)
-        const int src = k < a.n_res ? a.cell[k] + a.g.cell_base : a.guest_src[k - a.n_res];
+        const int n_res = *a.n_res_ptr;
+        const int src = k < n_res ? a.cell[k] + a.g.cell_base : a.guest_src[k - n_res];
         return list_key(F_REMOVED, src, a.id[k]);
     }
     return a.id[k];

@@ -83,7 +83,7 @@ __device__ __forceinline__ void integrate_store(const Geom &g, int i, int c, dou
 // neighbourhood is staged (as in k_force_integrate)
 template <int TB, int UNROLL, int TILE, int CELLS, int MINB>
 __global__ void __launch_bounds__(TB, MINB)
-k_force_integrate2(Geom g, int n, const double2 *__restrict__ pos_in, const double *__restrict__ m,
+k_force_integrate2(Geom g, const int *__restrict__ n_ptr, const double2 *__restrict__ pos_in, const double *__restrict__ m,
                    const int *__restrict__ cell, const int *__restrict__ cell_start,
                    const double2 *__restrict__ com_xy, const double *__restrict__ com_m,
                    double2 *__restrict__ pos_out, float2 *__restrict__ posf_out, double2 *__restrict__ vel,
@@ -93,7 +93,9 @@ k_force_integrate2(Geom g, int n, const double2 *__restrict__ pos_in, const doub
     __shared__ double s_m[TILE];
     __shared__ double2 s_nxy[CELLS * 8];
     __shared__ double s_nm[CELLS * 8];
+    const int n = *n_ptr;
     const int b0 = blockIdx.x * (2 * TB);
+    if (b0 >= n) return;
     const int i0 = b0 + 2 * threadIdx.x, i1 = i0 + 1;
     const int last = min(b0 + 2 * TB, n) - 1;
     const int cf = cell[b0], cl = cell[last];

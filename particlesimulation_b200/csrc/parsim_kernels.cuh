@@ -54,7 +54,9 @@ struct Counters {  // one per context, device memory, copied to the host once pe
     int n_emigrants_dn;
     int n_late_up;       // surviving strays + tombstones sent after the collision phase
     int n_late_dn;
-    int n_next;          // alive residents after this step's rebin
+    int n_next;          // alive residents of the strip: set at upload / reset, then by every step's rebin
+                         // scan.  Kernels read the particle count from here, so a step can be enqueued
+                         // before the host knows how many particles died in the previous one
     int error;           // sticky device-side error code (capacity overflow, long jump, ...)
     int n_staged;        // upload cursor for multi-rank ingest
     int n_movers;        // particles that changed cell in this step (length of the mover list)
@@ -580,7 +582,7 @@ __global__ void k_pair_peak(int iters, double *out) {
 // occupancy (the kernel is then a chain of dependent loads per particle).
 template <int TB, int UNROLL, int TILE, int CELLS, int MINB>
 __global__ void __launch_bounds__(TB, MINB)
-k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
+k_force_integrate(Geom g, const int *__restrict__ n_ptr, const double2 *__restrict__ pos_in,
                   const double *__restrict__ m, const int *__restrict__ cell,
                   const int *__restrict__ cell_start, const double2 *__restrict__ com_xy,
                   const double *__restrict__ com_m, double2 *__restrict__ pos_out,
@@ -591,7 +593,9 @@ k_force_integrate(Geom g, int n, const double2 *__restrict__ pos_in,
     __shared__ double s_m[TILE];
     __shared__ double2 s_nxy[CELLS > 0 ? CELLS * 8 : 1];
     __shared__ double s_nm[CELLS > 0 ? CELLS * 8 : 1];
+    const int n = *n_ptr;  // the grid is sized for an upper bound (the host may lag a step or two)
     const int b0 = blockIdx.x * TB;
+    if (b0 >= n) return;
     const int i = b0 + threadIdx.x;
     const int last = min(b0 + TB, n) - 1;
     const int r0 = cell_start[cell[b0]], r1 = cell_start[cell[last] + 1];
@@ -819,19 +823,21 @@ __device__ __forceinline__ bool is_close(double2 a, double2 b, double thr2) {
     return __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)) < thr2;
 }
 
-// n = residents (+ guests that arrived from other strips, which have cell[i] = -1 and carry
-// their source cell in guest_src[i - n_res]).
+// entries = *n_res_ptr residents + n_guest guests that arrived from other strips (those have
+// cell[i] = -1 and carry their source cell in guest_src[i - n_res]).
 #ifndef PS_FIND_MINB
 #define PS_FIND_MINB 6
 #endif
 __global__ void __launch_bounds__(kThreads, PS_FIND_MINB)
-k_collide_find(Geom g, int n, int n_res, double thr2, float thrf, const double2 *__restrict__ pos,
+k_collide_find(Geom g, const int *__restrict__ n_res_ptr, int n_guest, double thr2, float thrf,
+               const double2 *__restrict__ pos,
                const float2 *__restrict__ posf,
                const int *__restrict__ cell, const int *__restrict__ cell_start,
                const int *__restrict__ newcell, const unsigned *__restrict__ id,
                const unsigned char *__restrict__ flags, const int *__restrict__ arr_head,
                const int *__restrict__ arr_next, const int *__restrict__ guest_src,
                int *__restrict__ partner, unsigned long long *collision_pairs) {
+    const int n_res = *n_res_ptr, n = n_res + n_guest;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long tested = 0;
     if (i < n) {
@@ -876,6 +882,8 @@ k_collide_find(Geom g, int n, int n_res, double thr2, float thrf, const double2 
 }
 
 // ---------------------------------------------------------------------------------------
+__global__ void k_set_int(int *dst, int v) { *dst = v; }
+
 // Tombstone counts: total per cell += this step's deaths (and the per-step array is cleared).
 __global__ void k_add_counts(int n, int *__restrict__ acc, int *__restrict__ add) {
     int c = blockIdx.x * blockDim.x + threadIdx.x;

@@ -203,6 +203,9 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     PS_ALLOC(c, c->d_found, 1, true);
     PS_CUDA(c, cudaMallocHost((void **)&c->h_ctr, sizeof(Counters)));
     memset(c->h_ctr, 0, sizeof(Counters));
+    PS_CUDA(c, cudaMallocHost((void **)&c->h_ring, kCounterRing * sizeof(Counters)));
+    for (int k = 0; k < kCounterRing; k++) PS_CUDA(c, cudaEventCreateWithFlags(&c->ev_ring[k], cudaEventDisableTiming));
+    if (const char *e = getenv("PARSIM_SYNC_STEPS")) c->defer_steps = atoi(e) == 0;
     PS_CUDA(c, cudaEventCreate(&c->run_a));
     PS_CUDA(c, cudaEventCreate(&c->run_b));
     if (nranks > 1) {
@@ -235,6 +238,8 @@ void rank_destroy(Rank *c) {
         if (c->ev_ingested[b]) cudaEventDestroy(c->ev_ingested[b]);
     }
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
+    if (c->h_ring) cudaFreeHost(c->h_ring);
+    for (int k = 0; k < kCounterRing; k++) if (c->ev_ring[k]) cudaEventDestroy(c->ev_ring[k]);
     for (auto &t : c->pending) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
     for (auto &e : c->event_pool) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
     if (c->run_a) cudaEventDestroy(c->run_a);
@@ -364,6 +369,7 @@ int rank_upload_end(Rank *c) {
     else c->n_alive = (int)c->n_part;
     c->pos_latest = c->pos_cur;
     c->n0 = c->n_alive;
+    k_set_int<<<1, 1, 0, c->stream>>>(&c->d_ctr->n_next, c->n_alive);  // the kernels' particle count
     c->slots_id_ordered = true;
     if (c->nranks > 1 && c->n_alive > 1) {  // explicit-id uploads may come in any order
         PS_CUDA(c, cudaMemsetAsync(c->d_found, 0, sizeof(int), c->stream));
@@ -383,6 +389,7 @@ int rank_reset(Rank *c) {
     const int n0 = c->n0;
     if (reset_state(c)) return 1;
     c->n_alive = c->n0 = n0;
+    k_set_int<<<1, 1, 0, c->stream>>>(&c->d_ctr->n_next, c->n_alive);
     c->n_uploaded = c->n_part;
     c->pos_latest = c->pos_cur;
     return 0;

@@ -73,6 +73,8 @@ struct LocalBus {
     }
 };
 
+constexpr int kCounterRing = 4;  // host copies of the device counters of the last steps (deferred mode)
+
 struct Rank {
     // problem
     double side = 0;
@@ -135,6 +137,11 @@ struct Rank {
     int n_grave = 0;
 
     Counters *d_ctr = nullptr, *h_ctr = nullptr;
+    // steps enqueued without waiting for the previous one (single strip, parsim_step.inl rank_run)
+    bool deferred = false, defer_steps = true;  // defer_steps: PARSIM_SYNC_STEPS=1 switches it off
+    Counters *h_ring = nullptr;                 // pinned, kCounterRing entries
+    cudaEvent_t ev_ring[kCounterRing] = {nullptr, nullptr, nullptr, nullptr};
+    long long ring_pos = 0;
     double2 *d_p0 = nullptr;
     int *d_found = nullptr;
 

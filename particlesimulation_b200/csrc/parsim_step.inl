@@ -182,13 +182,13 @@ static int stage_bin_com(Rank *c) {
 static int stage_force(Rank *c) {
 #define PS_FORCE_TB(TB, UN, TILE, CELLS, MINB)                                                      \
     k_force_integrate<TB, UN, TILE, CELLS, MINB><<<grid_for(c->n_alive, TB), TB, 0, c->stream>>>(   \
-        c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,        \
+        c->g, &c->d_ctr->n_next, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m, \
         c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
         c->dbg_acc)
 #define PS_FORCE(UN, TILE, CELLS, MINB) PS_FORCE_TB(128, UN, TILE, CELLS, MINB)
 #define PS_FORCE2(UN, TILE, CELLS, MINB)                                                            \
     k_force_integrate2<128, UN, TILE, CELLS, MINB><<<grid_for(c->n_alive, 256), 128, 0, c->stream>>>( \
-        c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,        \
+        c->g, &c->d_ctr->n_next, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,        \
         c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
         c->dbg_acc)
 #define PS_FORCE_TILES(UN, TILE, MINB, NST, EL)                                                      \
@@ -252,7 +252,7 @@ static int stage_lists(Rank *c) {
     PS_LAUNCH(c, K_CLASSIFY, 0.5 * c->n_alive, "k_classify",
               k_classify<<<c->sm_count * 4, kThreads, 0, c->stream>>>(
                   g, c->partner, &c->d_ctr->n_movers, c->cell_cur, c->cs_cur, c->newcell, c->id_cur,
-                  c->n_tomb > 0 ? c->dead_start_cur : nullptr, c->dead_id_cur, c->flags, c->arr_head,
+                  c->n_tomb > 0 || c->deferred ? c->dead_start_cur : nullptr, c->dead_id_cur, c->flags, c->arr_head,
                   c->arr_next, c->pos_alt, c->arr_cnt, c->arr_rec, &c->d_ctr->strays, c->mig_list,
                   c->nranks > 1 ? c->mig_hdr_send + 3 : nullptr, c->mig_list_cap, c->d_ctr));
     c->n_guest = 0;
@@ -273,7 +273,7 @@ static int stage_collide(Rank *c) {
     const int n_tot = c->n_alive + c->n_guest;
     if (c->collide_grid) {
         CollideArgs a;
-        a.g = g; a.n_res = c->n_alive; a.thr2 = c->thr2; a.pos = c->pos_alt;
+        a.g = g; a.n_res_ptr = &c->d_ctr->n_next; a.thr2 = c->thr2; a.pos = c->pos_alt;
         a.cell = c->cell_cur; a.cell_start = c->cs_cur; a.newcell = c->newcell; a.id = c->id_cur;
         a.flags = c->flags; a.arr_head = c->arr_head; a.arr_next = c->arr_next; a.guest_src = c->guest_src;
         a.arr_cnt = c->arr_cnt; a.arr_rec = c->arr_rec;
@@ -306,17 +306,33 @@ static int stage_collide(Rank *c) {
     } else {
         PS_LAUNCH(c, K_COLLIDE, 21.0 * n_tot + 8.0 * g.ncells, "k_collide_find",
                   k_collide_find<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
-                      g, n_tot, c->n_alive, c->thr2, c->thrf, c->pos_alt, c->posf, c->cell_cur, c->cs_cur, c->newcell,
+                      g, &c->d_ctr->n_next, c->n_guest, c->thr2, c->thrf, c->pos_alt, c->posf, c->cell_cur, c->cs_cur, c->newcell,
                       c->id_cur, c->flags, c->arr_head, c->arr_next, c->guest_src, c->partner,
                       c->opt_stats ? &c->d_ctr->collision_pairs : nullptr));
     }
     if (c->nranks > 1) PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 4 * sizeof(int), c->stream));
     PS_LAUNCH(c, K_RESOLVE, 10.0 * n_tot, "k_resolve",
               k_resolve<<<std::min(grid_for(n_tot, kThreads * kResolveRows), c->sm_count * 8), kThreads, 0, c->stream>>>(
-                  g, n_tot, c->n_alive, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,
+                  g, &c->d_ctr->n_next, c->n_guest, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,
                   c->vel_cur, c->id_cur, c->fate, c->count, c->dead_new_count, c->mv_head, c->dm_head,
                   c->mv_next, c->grave_pos, c->grave_vel, c->grave_id, c->grave_cell, c->cap, c->d_ctr, c->mig_list,
                   c->nranks > 1 ? c->mig_hdr_send + 3 : nullptr, c->mig_list_cap));
+    if (c->deferred) {
+        // Single strip, no instrumentation: the host does not wait for the step.  The kernels read the
+        // particle count from Counters::n_next, the grids above are sized for the host's (older, hence
+        // larger: a single strip only loses particles) count, the tombstone lists are rebuilt every
+        // step, and the device error flag is looked at when the run ends (rank_run).
+        if (merge_step(c, n_tot, n_tot, true)) return 1;
+        Counters *slot = c->h_ring + (c->ring_pos % kCounterRing);
+        PS_CUDA(c, cudaMemcpyAsync(slot, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+        PS_CUDA(c, cudaEventRecord(c->ev_ring[c->ring_pos % kCounterRing], c->stream));
+        c->ring_pos++;
+        c->pos_latest = c->pos_cur;
+        c->have_newcell = c->have_flags = false;
+        c->steps_done++;
+        c->stats.steps++;
+        return 0;
+    }
     PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
     if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error));
@@ -383,15 +399,47 @@ int rank_stage(Rank *c, int stage) {
     return 0;
 }
 
+// The counters of the step before last, once they have arrived: the host stays at most two steps
+// ahead of the device, and the occupancy-driven choices (kernel variants, lanes per cell) follow the
+// real particle count with that lag.  A single strip never gains particles, so the older count is
+// an upper bound for the grids.
+static int deferred_refresh(Rank *c) {
+    if (c->ring_pos < 2) return 0;
+    const long long k = c->ring_pos - 2;
+    PS_CUDA(c, cudaEventSynchronize(c->ev_ring[k % kCounterRing]));
+    const Counters &h = c->h_ring[k % kCounterRing];
+    if (h.error) return c->fail("device error code " + std::to_string(h.error));
+    c->n_alive = h.n_next;
+    c->n_grave = h.grave_count;
+    c->n_tomb = h.grave_count;  // single strip: every dead particle lies in it
+    return 0;
+}
+
 int rank_run(Rank *c, long n_steps) {
     PS_CUDA(c, cudaSetDevice(c->device));
     if (c->uploading) return c->fail("upload not finished");
     if (c->next_stage != 0) return c->fail("parsim_run in the middle of a debug-staged step");
+    // no host round trip per step on a single strip, unless per-launch statistics, per-launch error
+    // checks or the persistent force pipeline (which takes the particle count as an argument) are on
+    c->deferred = c->nranks == 1 && !c->opt_stats && !c->opt_sync_check && c->defer_steps &&
+                  !(c->force_variant >= 5 && c->force_variant <= 7);
+    c->ring_pos = 0;
     PS_CUDA(c, cudaEventRecord(c->run_a, c->stream));
     for (long t = 0; t < n_steps; t++) {
-        if (stage_bin_com(c) || stage_force(c) || stage_lists(c) || stage_collide(c)) return 1;
+        if (c->deferred && deferred_refresh(c)) { c->deferred = false; return 1; }
+        if (stage_bin_com(c) || stage_force(c) || stage_lists(c) || stage_collide(c)) { c->deferred = false; return 1; }
     }
     PS_CUDA(c, cudaEventRecord(c->run_b, c->stream));
+    if (c->deferred && n_steps > 0) {
+        PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));
+        c->deferred = false;
+        if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error));
+        c->n_alive = c->h_ctr->n_next;
+        c->n_grave = c->h_ctr->grave_count;
+        c->n_tomb = c->h_ctr->grave_count;
+    }
+    c->deferred = false;
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
     float ms = 0;
     PS_CUDA(c, cudaEventElapsedTime(&ms, c->run_a, c->run_b));

@@ -258,6 +258,28 @@ def test_force_kernel_variants_agree(case, monkeypatch):
             assert np.array_equal(res[variant][1][k], res[0][1][k]), (variant, k)
 
 
+@pytest.mark.parametrize("case", [(1, 10, 100, 100000, 6), (5, 1, 20, 200000, 4), (-7, 10, 50, 20000, 6), (3, 1, 2, 200, 5),
+                                  (1, 2, 3, 10, 4)], ids=lambda c: " ".join(map(str, c)))
+def test_deferred_steps_match_synchronised_steps(case, monkeypatch):
+    """parsim_run on a single strip enqueues its steps without a host round trip (the kernels read
+    the particle count from device memory, grids are sized for the host's older count, the error
+    flag is read at the end); PARSIM_SYNC_STEPS=1 is the step-by-step path that multi-strip runs
+    and instrumented runs use.  Same bits, also when the run is cut into several parsim_run calls."""
+    seed, side, nc, n, steps = case
+    res = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("PARSIM_SYNC_STEPS", mode)
+        g = ParticleSimulation(seed, side, nc, n)
+        g.simulate(steps)
+        g.simulate(1)
+        g.simulate(2)
+        res[mode] = (g.result(), g.dump())
+        g.close()
+    assert res["0"][0] == res["1"][0]
+    for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+        assert np.array_equal(res["0"][1][k], res["1"][1][k]), k
+
+
 def test_close_encounters_throw_particles_far():
     """Two particles a few 1e-6 apart fly tens of cells in one step; the result must still be the
     reference's (alive flags and collision count exact, positions to 1e-9 of the box side)."""
