@@ -117,29 +117,8 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     if (const char *e = getenv("PARSIM_FORCE_VARIANT")) c->force_variant = atoi(e);
     {   // only instantiations that the variant-agreement test covers (tests/test_gpu_parity.py)
         const int v = c->force_variant;
-        if (!(v >= 0 && v <= 7) && !(v >= 10 && v <= 15))
+        if (!(v >= 0 && v <= 4) && v != 10 && v != 11)
             return c->fail("PARSIM_FORCE_VARIANT: unknown force-kernel variant " + std::to_string(v));
-    }
-    if (c->force_variant >= 5 && c->force_variant <= 7) {  // persistent tile pipeline (parsim_force_tiles.cuh)
-        int per_sm = 0, sms = 0;
-        PS_CUDA(c, cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
-#define PS_FT_SETUP(UN, TILE, MINB, NST, EL)                                                                 \
-    do {                                                                                                     \
-        const int sh = (int)force_tiles_smem<TILE, NST>();                                                   \
-        PS_CUDA(c, cudaFuncSetAttribute(k_force_tiles<UN, TILE, MINB, NST, EL>,                              \
-                                        cudaFuncAttributeMaxDynamicSharedMemorySize, sh));                   \
-        PS_CUDA(c, cudaOccupancyMaxActiveBlocksPerMultiprocessor(                                            \
-                       &per_sm, k_force_tiles<UN, TILE, MINB, NST, EL>, kFtThreads, sh));                    \
-    } while (0)
-        if (c->force_variant == 5) PS_FT_SETUP(4, 768, 4, 2, false);
-        else if (c->force_variant == 6) PS_FT_SETUP(8, 768, 4, 2, false);
-        else PS_FT_SETUP(4, 448, 6, 2, false);
-#undef PS_FT_SETUP
-        if (per_sm < 1) return c->fail("k_force_tiles does not fit an SM");
-        c->ft_grid = sms * per_sm;
-        if (getenv("PARSIM_DEBUG"))
-            fprintf(stderr, "parsim_b200: k_force_tiles variant %d: %d blocks per SM, grid %d\n", c->force_variant,
-                    per_sm, c->ft_grid);
     }
     if (const char *e = getenv("PARSIM_CAPACITY_PCT")) {
         double pct = atof(e);
@@ -176,10 +155,10 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
         PS_ALLOC(c, c->huge_items, N / kThreads + 2 * C + 16, false);
         PS_ALLOC(c, c->arr_cnt, C, true); PS_ALLOC(c, c->arr_rec, C * kArrSlots, false);
     }
-    PS_ALLOC(c, c->m_cur, N + kFtPad, false);   PS_ALLOC(c, c->m_alt, N + kFtPad, false);  // + the bulk-copy windows
+    PS_ALLOC(c, c->m_cur, N, false);   PS_ALLOC(c, c->m_alt, N, false);
     PS_ALLOC(c, c->id_cur, N, false);  PS_ALLOC(c, c->id_alt, N, false);
-    PS_ALLOC(c, c->cell_cur, N + kFtPad, false); PS_ALLOC(c, c->cell_alt, N + kFtPad, false);
-    PS_ALLOC(c, c->cs_cur, C + 1 + kFtPad, true); PS_ALLOC(c, c->cs_alt, C + 1 + kFtPad, true);
+    PS_ALLOC(c, c->cell_cur, N, false); PS_ALLOC(c, c->cell_alt, N, false);
+    PS_ALLOC(c, c->cs_cur, C + 1, true); PS_ALLOC(c, c->cs_alt, C + 1, true);
     PS_ALLOC(c, c->count, C, true);
     const size_t H = (size_t)kSortMaxBins * (N / kSortTile + 1);  // radix-sort tile histograms
     PS_ALLOC(c, c->tile_sums, std::max(C, H) / kScanTile + 2, true);

@@ -11,9 +11,6 @@
 
 #include "../../include/parsim_b200.h"
 #include "parsim_kernels.cuh"
-#include "parsim_force_tiles.cuh"
-#include "parsim_force_pairs2.cuh"
-#include "parsim_force_n3.cuh"
 #include "parsim_merge.cuh"
 #include "parsim_sort.cuh"
 #include "parsim_collide.cuh"
@@ -85,7 +82,6 @@ struct Rank {
     double thr2 = 0;    // collision threshold on the squared distance (see k_collide_find)
     int com_lanes = 32; // lanes per cell in k_com, from the GLOBAL particles-per-cell
     int force_variant = 0; // k_force_integrate instantiation (PARSIM_FORCE_VARIANT; 0: by occupancy)
-    int ft_grid = 0;       // resident blocks of the persistent k_force_tiles (variants 5, 6)
 
     // particle storage: alive residents [0, n_alive), guests after them until the rebin
     int cap = 0;

@@ -186,17 +186,6 @@ static int stage_force(Rank *c) {
         c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
         c->dbg_acc)
 #define PS_FORCE(UN, TILE, CELLS, MINB) PS_FORCE_TB(128, UN, TILE, CELLS, MINB)
-#define PS_FORCE2(UN, TILE, CELLS, MINB)                                                            \
-    k_force_integrate2<128, UN, TILE, CELLS, MINB><<<grid_for(c->n_alive, 256), 128, 0, c->stream>>>( \
-        c->g, &c->d_ctr->n_next, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,        \
-        c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
-        c->dbg_acc)
-#define PS_FORCE_TILES(UN, TILE, MINB, NST, EL)                                                      \
-    k_force_tiles<UN, TILE, MINB, NST, EL><<<std::min(c->ft_grid, grid_for(c->n_alive, kFtTargets)), \
-                                             kFtThreads, force_tiles_smem<TILE, NST>(), c->stream>>>( \
-        c->g, c->n_alive, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m,         \
-        c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,      \
-        c->dbg_acc)
     PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->n_movers, 0, sizeof(int), c->stream));
     // variant by current occupancy (cells fill up or empty out as the run goes on)
     int v = c->force_variant;
@@ -209,35 +198,13 @@ static int stage_force(Rank *c) {
         case 1: PS_FORCE(2, 256, 0, 16); break;   // sparse cells: neighbourhood through L1, 32 registers, full occupancy
         case 3: PS_FORCE(8, 1280, 16, 5); break;  // deep unroll, 96 registers (comparison)
         case 4: PS_FORCE(2, 256, 0, 8); break;    // sparse cells at 64 registers (comparison)
-        case 5: PS_FORCE_TILES(4, 768, 4, 2, false); break;  // persistent tile pipeline (parsim_force_tiles.cuh; comparison)
-        case 6: PS_FORCE_TILES(8, 768, 4, 2, false); break;
-        case 7: PS_FORCE_TILES(4, 448, 6, 2, false); break;
         case 10: PS_FORCE_TB(64, 4, 384, 8, 16); break;   // 2-warp blocks, 16 per SM: 29.7 ms per config-3 run (default 28.8)
         case 11: PS_FORCE_TB(256, 4, 1024, 16, 4); break; // 8-warp blocks, 4 per SM: 28.9 ms
-        case 12: PS_FORCE2(2, 1024, 16, 6); break;  // two targets per thread (parsim_force_pairs2.cuh)
-        case 13: PS_FORCE2(4, 1024, 16, 5); break;
-        case 14: PS_FORCE2(2, 1024, 16, 8); break;
-        case 15: {  // Newton's third law inside the cell, warp per cell (parsim_force_n3.cuh)
-            ForceArgs fa;
-            fa.pos_in = c->pos_cur; fa.m = c->m_cur; fa.cell_start = c->cs_cur; fa.com_xy = c->com_xy; fa.com_m = c->com_m;
-            fa.pos_out = c->pos_alt; fa.posf_out = c->posf; fa.vel = c->vel_cur; fa.newcell = c->newcell; fa.flags = c->flags;
-            fa.mover_list = c->partner; fa.n_movers = &c->d_ctr->n_movers; fa.dbg_acc = c->dbg_acc;
-            const double now = (double)c->n_alive / std::max(1, c->g.ncells);
-            const double want = now + 4.0 * sqrt(now) + 2.0;  // cells above 32 KMAX entries take the slow ordered sweep
-            const int grid = grid_for(c->g.ncells, kN3Warps);
-            if (want <= 64) k_force_n3<2, 6><<<grid, kN3Warps * 32, 0, c->stream>>>(c->g, fa);
-            else if (want <= 96) k_force_n3<3, 5><<<grid, kN3Warps * 32, 0, c->stream>>>(c->g, fa);
-            else if (want <= 128) k_force_n3<4, 4><<<grid, kN3Warps * 32, 0, c->stream>>>(c->g, fa);
-            else k_force_n3<6, 3><<<grid, kN3Warps * 32, 0, c->stream>>>(c->g, fa);
-            break;
-        }
         default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
         }
     });
 #undef PS_FORCE
 #undef PS_FORCE_TB
-#undef PS_FORCE2
-#undef PS_FORCE_TILES
     c->pos_latest = c->pos_alt;
     c->have_newcell = true;
     return 0;
@@ -419,10 +386,9 @@ int rank_run(Rank *c, long n_steps) {
     PS_CUDA(c, cudaSetDevice(c->device));
     if (c->uploading) return c->fail("upload not finished");
     if (c->next_stage != 0) return c->fail("parsim_run in the middle of a debug-staged step");
-    // no host round trip per step on a single strip, unless per-launch statistics, per-launch error
-    // checks or the persistent force pipeline (which takes the particle count as an argument) are on
-    c->deferred = c->nranks == 1 && !c->opt_stats && !c->opt_sync_check && c->defer_steps &&
-                  !(c->force_variant >= 5 && c->force_variant <= 7);
+    // no host round trip per step on a single strip, unless per-launch statistics or per-launch
+    // error checks are on
+    c->deferred = c->nranks == 1 && !c->opt_stats && !c->opt_sync_check && c->defer_steps;
     c->ring_pos = 0;
     PS_CUDA(c, cudaEventRecord(c->run_a, c->stream));
     for (long t = 0; t < n_steps; t++) {

@@ -223,12 +223,12 @@ def test_collision_search_paths_agree(case, monkeypatch):
         assert np.array_equal(res["pairs"][1][k], res["grid"][1][k]), k
 
 
-FORCE_VARIANTS = [0, 1, 2, 3, 4, 5, 6, 7, 10, 11, 12, 13, 14]  # = what rank_create accepts (csrc/parsim_rank.cu)
+FORCE_VARIANTS = [0, 1, 2, 3, 4, 10, 11]  # = what rank_create accepts (csrc/parsim_rank.cu)
 
 
 def test_unknown_force_variant_is_rejected(monkeypatch):
     from particlesimulation_b200 import ParsimError
-    for v in ("8", "9", "15", "-1"):
+    for v in ("5", "9", "12", "15", "-1"):
         monkeypatch.setenv("PARSIM_FORCE_VARIANT", v)
         with pytest.raises(ParsimError):
             ParticleSimulation(1, 2, 3, 10)
@@ -239,9 +239,8 @@ def test_unknown_force_variant_is_rejected(monkeypatch):
                          ids=lambda c: " ".join(map(str, c)))
 def test_force_kernel_variants_agree(case, monkeypatch):
     """Every instantiation of the force + integration kernel that PARSIM_FORCE_VARIANT accepts --
-    block per tile with or without the staged neighbourhood, deep unroll, 64 / 256-thread blocks,
-    the persistent TMA / mbarrier pipeline (k_force_tiles, 5-7) and two targets per thread
-    (k_force_integrate2, 12-14) -- sums in the same order, so the runs must agree bit for bit with
+    block per tile with or without the staged neighbourhood, deep unroll, 64 / 256-thread blocks --
+    sums in the same order, so the runs must agree bit for bit with
     the default (which picks its instantiation from the occupancy)."""
     seed, side, nc, n, steps = case
     res = {}
