@@ -823,6 +823,53 @@ __device__ __forceinline__ bool is_close(double2 a, double2 b, double thr2) {
     return __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)) < thr2;
 }
 
+// The first list entry (by list key) that is close to entry i, or -1: first(i) of the mutual-first
+// rule.  Entry i's list L is the cell it was binned in, or -- for a removed mover -- the cell it
+// moved to.  `tested` counts the candidates looked at (stats).
+__device__ __forceinline__ int find_first_partner(const Geom &g, int i, int n_res, double thr2, float thrf,
+                                                  const double2 *__restrict__ pos, const float2 *__restrict__ posf,
+                                                  const int *__restrict__ cell, const int *__restrict__ cell_start,
+                                                  const int *__restrict__ newcell, const unsigned *__restrict__ id,
+                                                  const unsigned char *__restrict__ flags,
+                                                  const int *__restrict__ arr_head, const int *__restrict__ arr_next,
+                                                  const int *__restrict__ guest_src, unsigned long long &tested) {
+    const unsigned char f = flags[i];
+    int best_idx = -1;
+    if (f & F_EMIGRANT) return -1;  // emigrants are checked on the strip they moved to
+    const int L = (f & F_REMOVED) ? newcell[i] - g.cell_base : cell[i];
+    const double2 p = pos[i];
+    const float2 pf = posf[i];
+    unsigned long long best = ~0ull;
+    const int s = cell_start[L], e = cell_start[L + 1];
+    // residents of L that are still listed there (stayers and strays), key = id, id-sorted.
+    // FP32 pre-filter: thrf over-covers the rounding of the float copies, so every pair
+    // that is close in FP64 passes it; the decision itself is the exact FP64 test.
+#pragma unroll 4
+    for (int k = s; k < e; k++) {
+        float2 qf = __ldg(&posf[k]);
+        float fx = qf.x - pf.x, fy = qf.y - pf.y;
+        if (fmaf(fx, fx, fy * fy) < thrf) {
+            if (k != i && !(flags[k] & F_REMOVED) && is_close(p, pos[k], thr2)) {
+                unsigned long long key = id[k];
+                if (key < best) { best = key; best_idx = k; }
+            }
+        }
+    }
+    // arrivals appended to L's list
+    int walked = 0;
+    for (int k = arr_head[L]; k >= 0; k = arr_next[k]) {
+        walked++;
+        if (k == i) continue;
+        if (is_close(p, pos[k], thr2)) {
+            int src = k < n_res ? cell[k] + g.cell_base : guest_src[k - n_res];
+            unsigned long long key = list_key(F_REMOVED, src, id[k]);
+            if (key < best) { best = key; best_idx = k; }
+        }
+    }
+    tested += (unsigned long long)(e - s + walked);
+    return best_idx;
+}
+
 // entries = *n_res_ptr residents + n_guest guests that arrived from other strips (those have
 // cell[i] = -1 and carry their source cell in guest_src[i - n_res]).
 #ifndef PS_FIND_MINB
@@ -840,44 +887,9 @@ k_collide_find(Geom g, const int *__restrict__ n_res_ptr, int n_guest, double th
     const int n_res = *n_res_ptr, n = n_res + n_guest;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long tested = 0;
-    if (i < n) {
-        const unsigned char f = flags[i];
-        int best_idx = -1;
-        if (!(f & F_EMIGRANT)) {  // emigrants are checked on the strip they moved to
-            const int L = (f & F_REMOVED) ? newcell[i] - g.cell_base : cell[i];
-            const double2 p = pos[i];
-            const float2 pf = posf[i];
-            unsigned long long best = ~0ull;
-            const int s = cell_start[L], e = cell_start[L + 1];
-            // residents of L that are still listed there (stayers and strays), key = id, id-sorted.
-            // FP32 pre-filter: thrf over-covers the rounding of the float copies, so every pair
-            // that is close in FP64 passes it; the decision itself is the exact FP64 test.
-#pragma unroll 4
-            for (int k = s; k < e; k++) {
-                float2 qf = __ldg(&posf[k]);
-                float fx = qf.x - pf.x, fy = qf.y - pf.y;
-                if (fmaf(fx, fx, fy * fy) < thrf) {
-                    if (k != i && !(flags[k] & F_REMOVED) && is_close(p, pos[k], thr2)) {
-                        unsigned long long key = id[k];
-                        if (key < best) { best = key; best_idx = k; }
-                    }
-                }
-            }
-            // arrivals appended to L's list
-            int walked = 0;
-            for (int k = arr_head[L]; k >= 0; k = arr_next[k]) {
-                walked++;
-                if (k == i) continue;
-                if (is_close(p, pos[k], thr2)) {
-                    int src = k < n_res ? cell[k] + g.cell_base : guest_src[k - n_res];
-                    unsigned long long key = list_key(F_REMOVED, src, id[k]);
-                    if (key < best) { best = key; best_idx = k; }
-                }
-            }
-            tested = (unsigned long long)(e - s + walked);
-        }
-        partner[i] = best_idx;
-    }
+    if (i < n)
+        partner[i] = find_first_partner(g, i, n_res, thr2, thrf, pos, posf, cell, cell_start, newcell, id, flags,
+                                        arr_head, arr_next, guest_src, tested);
     if (collision_pairs) block_add_u64(tested, collision_pairs);  // stats only (uniform branch)
 }
 

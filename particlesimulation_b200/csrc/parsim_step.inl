@@ -57,12 +57,12 @@ static int sort_initial(Rank *c) {
     int *srcA = c->arr_next, *srcB = c->mv_next;
     const int cell_bits = bits_for((unsigned long long)std::max(g.ncells - 1, 1));
     if (c->slots_id_ordered) {
-        PS_LAUNCH(c, K_BIN_KEYS, 68.0 * n, "k_sort_cell_of",
+        PS_LAUNCH(c, K_BIN_KEYS, 36.0 * n, "k_sort_cell_of",
                   k_sort_cell_of<<<grid_for(n), kThreads, 0, c->stream>>>(g, n, c->rec0, keyA));
         if (sort_passes(c, n, cell_bits, keyA, keyB, srcA, srcB, true)) return 1;
     } else {
         // slots are not in id order: sort by id first (LSD), then by cell
-        PS_LAUNCH(c, K_BIN_KEYS, 68.0 * n, "k_sort_cell_of",
+        PS_LAUNCH(c, K_BIN_KEYS, 36.0 * n, "k_sort_cell_of",
                   k_sort_cell_of<<<grid_for(n), kThreads, 0, c->stream>>>(g, n, c->rec0, c->tmp_id));
         PS_LAUNCH(c, K_SORT_PASS, 68.0 * n, "k_sort_id_keys",
                   k_sort_id_keys<<<grid_for(n), kThreads, 0, c->stream>>>(n, nullptr, c->rec0, keyA));
