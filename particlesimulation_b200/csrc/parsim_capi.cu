@@ -454,6 +454,9 @@ int parsim_set_option(parsim_ctx *ctx, const char *name, long long value) {
     std::string n(name);
     for (auto &rp : ctx->ranks) {
         Rank *c = rp.get();
+        // captured steps bake the options in (kernel arguments): drop them
+        for (auto &sg : c->graphs) cudaGraphExecDestroy(sg.exec);
+        c->graphs.clear();
         if (n == "stats") c->opt_stats = value != 0;
         else if (n == "sync_check") c->opt_sync_check = value != 0;
         else if (n == "keep_initial") c->opt_keep_initial = value != 0;

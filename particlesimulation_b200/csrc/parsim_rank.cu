@@ -103,6 +103,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
             if (!strcmp(e, "pairs")) c->collide_grid = false;
             else if (!strcmp(e, "grid")) c->collide_grid = true;
         }
+        if (const char *e = getenv("PARSIM_FUSE_SEARCH")) c->fuse_search = atoi(e) != 0;
         if (c->collide_grid) {
 #define PS_COLLIDE_ATTR(IT)                                                                              \
     PS_CUDA(c, cudaFuncSetAttribute(k_collide_cells<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
@@ -117,7 +118,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     if (const char *e = getenv("PARSIM_FORCE_VARIANT")) c->force_variant = atoi(e);
     {   // only instantiations that the variant-agreement test covers (tests/test_gpu_parity.py)
         const int v = c->force_variant;
-        if (!(v >= 0 && v <= 4) && v != 10 && v != 11)
+        if (!(v >= 0 && v <= 7) && v != 10 && v != 11)
             return c->fail("PARSIM_FORCE_VARIANT: unknown force-kernel variant " + std::to_string(v));
     }
     if (const char *e = getenv("PARSIM_CAPACITY_PCT")) {
@@ -185,6 +186,8 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     PS_CUDA(c, cudaMallocHost((void **)&c->h_ring, kCounterRing * sizeof(Counters)));
     for (int k = 0; k < kCounterRing; k++) PS_CUDA(c, cudaEventCreateWithFlags(&c->ev_ring[k], cudaEventDisableTiming));
     if (const char *e = getenv("PARSIM_SYNC_STEPS")) c->defer_steps = atoi(e) == 0;
+    c->use_graphs = n_part <= 4000000;  // above that a step is milliseconds of kernels: nothing to gain
+    if (const char *e = getenv("PARSIM_GRAPHS")) c->use_graphs = atoi(e) != 0;
     PS_CUDA(c, cudaEventCreate(&c->run_a));
     PS_CUDA(c, cudaEventCreate(&c->run_b));
     if (nranks > 1) {
@@ -217,6 +220,8 @@ void rank_destroy(Rank *c) {
         if (c->ev_ingested[b]) cudaEventDestroy(c->ev_ingested[b]);
     }
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
+    for (auto &sg : c->graphs) cudaGraphExecDestroy(sg.exec);
+    c->graphs.clear();
     if (c->h_ring) cudaFreeHost(c->h_ring);
     for (int k = 0; k < kCounterRing; k++) if (c->ev_ring[k]) cudaEventDestroy(c->ev_ring[k]);
     for (auto &t : c->pending) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }

@@ -70,7 +70,7 @@ struct LocalBus {
     }
 };
 
-constexpr int kCounterRing = 4;  // host copies of the device counters of the last steps (deferred mode)
+constexpr int kCounterRing = 2;  // host copies of the device counters of the last two steps (deferred mode)
 
 struct Rank {
     // problem
@@ -100,6 +100,7 @@ struct Rank {
     float thrf = 0;                            // pre-filter threshold on the FP32 squared distance
     // cell-centric collision search (parsim_collide.cuh); off: per-particle all-pairs k_collide_find
     bool collide_grid = false;
+    bool fuse_search = true;  // sparse regime: search inside k_resolve (PARSIM_FUSE_SEARCH=0: separate k_collide_find)
     int grid_nb = 1, grid_cap = 0, grid_it = 2, big_nb = 1, big_cap = 0;
     int *big_cells = nullptr, *d_big_count = nullptr;  // d_big_count[0]: big cells, [1]: huge-cell slices
     int2 *huge_items = nullptr;
@@ -136,8 +137,13 @@ struct Rank {
     // steps enqueued without waiting for the previous one (single strip, parsim_step.inl rank_run)
     bool deferred = false, defer_steps = true;  // defer_steps: PARSIM_SYNC_STEPS=1 switches it off
     Counters *h_ring = nullptr;                 // pinned, kCounterRing entries
-    cudaEvent_t ev_ring[kCounterRing] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_ring[kCounterRing] = {nullptr, nullptr};
     long long ring_pos = 0;
+    // Small problems are launch-bound (BASELINE configs[1]: about 20 launches per 100 us step): a
+    // deferred step is captured once per (buffer parity, kernel choice) as a CUDA graph and replayed.
+    struct StepGraph { unsigned long long key; int n_cap; cudaGraphExec_t exec; };
+    std::vector<StepGraph> graphs;
+    bool use_graphs = false, capturing = false;
     double2 *d_p0 = nullptr;
     int *d_found = nullptr;
 

@@ -180,8 +180,8 @@ static int stage_bin_com(Rank *c) {
 
 // stage 1: forces + integration
 static int stage_force(Rank *c) {
-#define PS_FORCE_TB(TB, UN, TILE, CELLS, MINB)                                                      \
-    k_force_integrate<TB, UN, TILE, CELLS, MINB><<<grid_for(c->n_alive, TB), TB, 0, c->stream>>>(   \
+#define PS_FORCE_TB(TB, UN, TILE, CELLS, MINB, ...)                                                 \
+    k_force_integrate<TB, UN, TILE, CELLS, MINB, ##__VA_ARGS__><<<grid_for(c->n_alive, TB), TB, 0, c->stream>>>( \
         c->g, &c->d_ctr->n_next, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m, \
         c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
         c->dbg_acc)
@@ -198,6 +198,9 @@ static int stage_force(Rank *c) {
         case 1: PS_FORCE(2, 256, 0, 16); break;   // sparse cells: neighbourhood through L1, 32 registers, full occupancy
         case 3: PS_FORCE(8, 1280, 16, 5); break;  // deep unroll, 96 registers (comparison)
         case 4: PS_FORCE(2, 256, 0, 8); break;    // sparse cells at 64 registers (comparison)
+        case 5: PS_FORCE_TB(128, 4, 768, 0, 8, true); break;  // asynchronous staging, neighbours before the barrier
+        case 6: PS_FORCE_TB(128, 4, 1024, 0, 7, true); break;
+        case 7: PS_FORCE_TB(256, 4, 1536, 0, 4, true); break;
         case 10: PS_FORCE_TB(64, 4, 384, 8, 16); break;   // 2-warp blocks, 16 per SM: 29.7 ms per config-3 run (default 28.8)
         case 11: PS_FORCE_TB(256, 4, 1024, 16, 4); break; // 8-warp blocks, 4 per SM: 28.9 ms
         default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
@@ -270,7 +273,7 @@ static int stage_collide(Rank *c) {
                       a, c->huge_items, c->d_big_count + 1));
         PS_LAUNCH(c, K_COLLIDE_BIG, 0.0, "k_collide_huge",
                   k_collide_huge<<<c->sm_count * 8, kThreads, 0, c->stream>>>(a, c->huge_items, c->d_big_count + 1));
-    } else {
+    } else if (!c->fuse_search) {
         PS_LAUNCH(c, K_COLLIDE, 21.0 * n_tot + 8.0 * g.ncells, "k_collide_find",
                   k_collide_find<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
                       g, &c->d_ctr->n_next, c->n_guest, c->thr2, c->thrf, c->pos_alt, c->posf, c->cell_cur, c->cs_cur, c->newcell,
@@ -278,12 +281,26 @@ static int stage_collide(Rank *c) {
                       c->opt_stats ? &c->d_ctr->collision_pairs : nullptr));
     }
     if (c->nranks > 1) PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 4 * sizeof(int), c->stream));
-    PS_LAUNCH(c, K_RESOLVE, 10.0 * n_tot, "k_resolve",
-              k_resolve<<<std::min(grid_for(n_tot, kThreads * kResolveRows), c->sm_count * 8), kThreads, 0, c->stream>>>(
-                  g, &c->d_ctr->n_next, c->n_guest, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,
-                  c->vel_cur, c->id_cur, c->fate, c->count, c->dead_new_count, c->mv_head, c->dm_head,
-                  c->mv_next, c->grave_pos, c->grave_vel, c->grave_id, c->grave_cell, c->cap, c->d_ctr, c->mig_list,
-                  c->nranks > 1 ? c->mig_hdr_send + 3 : nullptr, c->mig_list_cap));
+    SearchArgs sa;
+    sa.thr2 = c->thr2; sa.thrf = c->thrf; sa.posf = c->posf; sa.cell_start = c->cs_cur; sa.arr_head = c->arr_head;
+    sa.arr_next = c->arr_next; sa.guest_src = c->guest_src;
+    sa.collision_pairs = c->opt_stats ? &c->d_ctr->collision_pairs : nullptr;
+#define PS_RESOLVE_ARGS                                                                                      \
+    g, &c->d_ctr->n_next, c->n_guest, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt, c->vel_cur,   \
+        c->id_cur, c->fate, c->count, c->dead_new_count, c->mv_head, c->dm_head, c->mv_next, c->grave_pos,     \
+        c->grave_vel, c->grave_id, c->grave_cell, c->cap, c->d_ctr, c->mig_list,                               \
+        c->nranks > 1 ? c->mig_hdr_send + 3 : nullptr, c->mig_list_cap, sa
+    if (!c->collide_grid && c->fuse_search) {
+        // sparse cells: search and resolve in ONE pass over the particles (parsim_merge.cuh)
+        PS_LAUNCH(c, K_COLLIDE, 31.0 * n_tot + 8.0 * g.ncells, "k_resolve<search>",
+                  k_resolve<true, kSearchRows, 6><<<std::min(grid_for(n_tot, kThreads * kSearchRows), c->sm_count * 6),
+                                                    kThreads, 0, c->stream>>>(PS_RESOLVE_ARGS));
+    } else {
+        PS_LAUNCH(c, K_RESOLVE, 10.0 * n_tot, "k_resolve",
+                  k_resolve<false, kResolveRows, PS_RESOLVE_MINB><<<std::min(grid_for(n_tot, kThreads * kResolveRows), c->sm_count * 8),
+                                                                    kThreads, 0, c->stream>>>(PS_RESOLVE_ARGS));
+    }
+#undef PS_RESOLVE_ARGS
     if (c->deferred) {
         // Single strip, no instrumentation: the host does not wait for the step.  The kernels read the
         // particle count from Counters::n_next, the grids above are sized for the host's (older, hence
@@ -292,7 +309,7 @@ static int stage_collide(Rank *c) {
         if (merge_step(c, n_tot, n_tot, true)) return 1;
         Counters *slot = c->h_ring + (c->ring_pos % kCounterRing);
         PS_CUDA(c, cudaMemcpyAsync(slot, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
-        PS_CUDA(c, cudaEventRecord(c->ev_ring[c->ring_pos % kCounterRing], c->stream));
+        if (!c->capturing) PS_CUDA(c, cudaEventRecord(c->ev_ring[c->ring_pos % kCounterRing], c->stream));
         c->ring_pos++;
         c->pos_latest = c->pos_cur;
         c->have_newcell = c->have_flags = false;
@@ -382,6 +399,69 @@ static int deferred_refresh(Rank *c) {
     return 0;
 }
 
+static int deferred_step_eager(Rank *c) {
+    return stage_bin_com(c) || stage_force(c) || stage_lists(c) || stage_collide(c);
+}
+
+// What a replayed graph does NOT do: the host-side bookkeeping of the four stages (buffer roles
+// after the merge, counters).  Must mirror merge_step and the deferred branch of stage_collide.
+static void deferred_host_advance(Rank *c) {
+    std::swap(c->vel_cur, c->vel_alt);
+    std::swap(c->m_cur, c->m_alt);
+    std::swap(c->id_cur, c->id_alt);
+    std::swap(c->cell_cur, c->cell_alt);
+    std::swap(c->cs_cur, c->cs_alt);
+    std::swap(c->dead_start_cur, c->dead_start_alt);
+    std::swap(c->dead_id_cur, c->dead_id_alt);
+    c->n_guest = 0;
+    c->ring_pos++;
+    c->pos_latest = c->pos_cur;
+    c->have_newcell = c->have_flags = false;
+    c->steps_done++;
+    c->stats.steps++;
+}
+
+// One deferred step through a CUDA graph.  The graph bakes in pointers, grids and kernel choices:
+// the key holds the roles of the ping-pong buffers, the counter slot and the occupancy class the
+// choices are made from; the grids were sized for n_cap particles and stay valid while the bound on
+// the particle count is not larger.  Whatever the key misses can only change WHICH equivalent kernel
+// instantiation runs, never the result (tests/test_gpu_parity.py::test_force_kernel_variants_agree).
+static int deferred_step_graph(Rank *c) {
+    const double occ = (double)c->n_alive / std::max(1, c->g.ncells);
+    const unsigned long long occ_class = (unsigned long long)std::min(63.0, std::max(0.0, 4.0 * log2(occ + 1.0)));
+    const unsigned long long key = (c->pos_cur < c->pos_alt ? 1ull : 0) | (c->vel_cur < c->vel_alt ? 2ull : 0) |
+                                   (c->dead_start_cur < c->dead_start_alt ? 4ull : 0) |
+                                   ((unsigned long long)(c->ring_pos % kCounterRing) << 3) | (occ_class << 8);
+    cudaGraphExec_t exec = nullptr;
+    for (auto &sg : c->graphs)
+        if (sg.key == key && sg.n_cap >= c->n_alive) { exec = sg.exec; break; }
+    if (!exec) {
+        const int n_cap = c->n_alive;
+        PS_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
+        c->capturing = true;
+        const int rc = deferred_step_eager(c);  // records the launches, advances the host state
+        c->capturing = false;
+        cudaGraph_t graph = nullptr;
+        const cudaError_t e = cudaStreamEndCapture(c->stream, &graph);
+        if (rc) { if (graph) cudaGraphDestroy(graph); return 1; }
+        if (e != cudaSuccess) return c->fail(std::string("cudaStreamEndCapture: ") + cudaGetErrorString(e));
+        PS_CUDA(c, cudaGraphInstantiate(&exec, graph, 0));
+        cudaGraphDestroy(graph);
+        if (c->graphs.size() >= 64) {  // bounded cache (long runs through many occupancy classes)
+            cudaGraphExecDestroy(c->graphs.front().exec);
+            c->graphs.erase(c->graphs.begin());
+        }
+        c->graphs.push_back({key, n_cap, exec});
+        PS_CUDA(c, cudaGraphLaunch(exec, c->stream));
+        PS_CUDA(c, cudaEventRecord(c->ev_ring[(c->ring_pos - 1) % kCounterRing], c->stream));
+        return 0;
+    }
+    PS_CUDA(c, cudaGraphLaunch(exec, c->stream));
+    PS_CUDA(c, cudaEventRecord(c->ev_ring[c->ring_pos % kCounterRing], c->stream));
+    deferred_host_advance(c);
+    return 0;
+}
+
 int rank_run(Rank *c, long n_steps) {
     PS_CUDA(c, cudaSetDevice(c->device));
     if (c->uploading) return c->fail("upload not finished");
@@ -392,8 +472,15 @@ int rank_run(Rank *c, long n_steps) {
     c->ring_pos = 0;
     PS_CUDA(c, cudaEventRecord(c->run_a, c->stream));
     for (long t = 0; t < n_steps; t++) {
-        if (c->deferred && deferred_refresh(c)) { c->deferred = false; return 1; }
-        if (stage_bin_com(c) || stage_force(c) || stage_lists(c) || stage_collide(c)) { c->deferred = false; return 1; }
+        int rc;
+        if (c->deferred) {
+            rc = deferred_refresh(c);
+            // the first step of a run may have to sort (eager); graphs only where a step is launch-bound
+            if (!rc) rc = (c->use_graphs && c->sorted) ? deferred_step_graph(c) : deferred_step_eager(c);
+        } else {
+            rc = deferred_step_eager(c);
+        }
+        if (rc) { c->deferred = false; return 1; }
     }
     PS_CUDA(c, cudaEventRecord(c->run_b, c->stream));
     if (c->deferred && n_steps > 0) {

@@ -209,26 +209,30 @@ def test_run_is_deterministic_and_matches_staged():
                          ids=lambda c: " ".join(map(str, c)))
 def test_collision_search_paths_agree(case, monkeypatch):
     """The sub-grid collision search (warp per cell, block per big cell, all-pairs fallback for
-    lists beyond the staging area) must give exactly the result of the per-particle all-pairs sweep."""
+    lists beyond the staging area) must give exactly the result of the per-particle all-pairs sweep,
+    whether that sweep runs inside the resolve kernel (the default of the sparse regime) or as a
+    kernel of its own that writes the partner array (PARSIM_FUSE_SEARCH=0)."""
     seed, side, nc, n, steps = case
     res = {}
-    for mode in ("pairs", "grid"):
-        monkeypatch.setenv("PARSIM_COLLIDE", mode)
+    for mode in ("pairs", "pairs-unfused", "grid"):
+        monkeypatch.setenv("PARSIM_COLLIDE", mode.split("-")[0])
+        monkeypatch.setenv("PARSIM_FUSE_SEARCH", "0" if mode.endswith("unfused") else "1")
         g = ParticleSimulation(seed, side, nc, n)
         g.simulate(steps)
         res[mode] = (g.result(), g.dump())
         g.close()
-    assert res["pairs"][0] == res["grid"][0]
-    for k in ("x", "y", "vx", "vy", "m", "alive"):
-        assert np.array_equal(res["pairs"][1][k], res["grid"][1][k]), k
+    for mode in ("pairs-unfused", "grid"):
+        assert res["pairs"][0] == res[mode][0], mode
+        for k in ("x", "y", "vx", "vy", "m", "alive"):
+            assert np.array_equal(res["pairs"][1][k], res[mode][1][k]), (mode, k)
 
 
-FORCE_VARIANTS = [0, 1, 2, 3, 4, 10, 11]  # = what rank_create accepts (csrc/parsim_rank.cu)
+FORCE_VARIANTS = [0, 1, 2, 3, 4, 5, 6, 7, 10, 11]  # = what rank_create accepts (csrc/parsim_rank.cu)
 
 
 def test_unknown_force_variant_is_rejected(monkeypatch):
     from particlesimulation_b200 import ParsimError
-    for v in ("5", "9", "12", "15", "-1"):
+    for v in ("8", "9", "12", "15", "-1"):
         monkeypatch.setenv("PARSIM_FORCE_VARIANT", v)
         with pytest.raises(ParsimError):
             ParticleSimulation(1, 2, 3, 10)
@@ -266,17 +270,25 @@ def test_deferred_steps_match_synchronised_steps(case, monkeypatch):
     and instrumented runs use.  Same bits, also when the run is cut into several parsim_run calls."""
     seed, side, nc, n, steps = case
     res = {}
-    for mode in ("0", "1"):
-        monkeypatch.setenv("PARSIM_SYNC_STEPS", mode)
-        g = ParticleSimulation(seed, side, nc, n)
-        g.simulate(steps)
-        g.simulate(1)
-        g.simulate(2)
+    # step by step / deferred, launch by launch / deferred, replayed as CUDA graphs (what problems of
+    # this size get by default) -- the latter twice over, so that the second run replays cached graphs
+    for mode, env in (("sync", {"PARSIM_SYNC_STEPS": "1"}), ("eager", {"PARSIM_SYNC_STEPS": "0", "PARSIM_GRAPHS": "0"}),
+                      ("graphs", {"PARSIM_SYNC_STEPS": "0", "PARSIM_GRAPHS": "1"})):
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        g = ParticleSimulation(seed, side, nc, n, options={"keep_initial": 1})
+        for rep in range(2 if mode == "graphs" else 1):
+            if rep:
+                g.reset()
+            g.simulate(steps)
+            g.simulate(1)
+            g.simulate(2)
         res[mode] = (g.result(), g.dump())
         g.close()
-    assert res["0"][0] == res["1"][0]
-    for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
-        assert np.array_equal(res["0"][1][k], res["1"][1][k]), k
+    for mode in ("eager", "graphs"):
+        assert res[mode][0] == res["sync"][0], mode
+        for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+            assert np.array_equal(res[mode][1][k], res["sync"][1][k]), (mode, k)
 
 
 def test_close_encounters_throw_particles_far():
