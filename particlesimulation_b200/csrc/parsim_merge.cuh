@@ -41,22 +41,8 @@ enum Fate : unsigned char {
 #define PS_RESOLVE_MINB 8
 #endif
 constexpr int kResolveRows = PS_RESOLVE_ROWS;
-constexpr int kSearchRows = 2;  // rows per thread of the fused search + resolve kernel
 
-// SEARCH: the collision search of the sparse regime (find_first_partner, parsim_kernels.cuh) runs
-// here instead of in a kernel of its own: first(i) is searched, and for the few entries that have a
-// partner first(partner) is searched again for the mutual-first test (both are entries of the same
-// list) -- no partner array is written or read, one pass less over the particles.
-struct SearchArgs {
-    double thr2;
-    float thrf;
-    const float2 *posf;
-    const int *cell_start, *arr_head, *arr_next, *guest_src;
-    unsigned long long *collision_pairs;
-};
-
-template <bool SEARCH, int ROWS, int MINB>
-__global__ void __launch_bounds__(kThreads, MINB)
+__global__ void __launch_bounds__(kThreads, PS_RESOLVE_MINB)
 k_resolve(Geom g, const int *__restrict__ n_res_ptr, int n_guest, const int *__restrict__ partner, const int *__restrict__ cell,
           const int *__restrict__ newcell, const unsigned char *__restrict__ flags,
           const double2 *__restrict__ pos, const double2 *__restrict__ vel,
@@ -64,10 +50,8 @@ k_resolve(Geom g, const int *__restrict__ n_res_ptr, int n_guest, const int *__r
           int *dead_new_count, int *mv_head, int *dm_head, int *__restrict__ mv_next,
           double2 *__restrict__ grave_pos, double2 *__restrict__ grave_vel,
           unsigned *__restrict__ grave_id, int *__restrict__ grave_cell, int grave_cap, Counters *ctr,
-          int *__restrict__ late_list, int *late_count, int late_cap, SearchArgs sa) {
+          int *__restrict__ late_list, int *late_count, int late_cap) {
     constexpr int kWarps = kThreads / 32;
-    constexpr int kResolveRows = ROWS;
-    unsigned long long tested = 0;
     const int n_res = *n_res_ptr, n = n_res + n_guest;
     __shared__ int warp_dying[kResolveRows][kWarps];
     __shared__ int tile_base;
@@ -90,22 +74,10 @@ k_resolve(Geom g, const int *__restrict__ n_res_ptr, int n_guest, const int *__r
             cc[r] = in && i < n_res ? cell[i] : -1;
             nn[r] = in ? newcell[i] : 0;
             ff[r] = in ? flags[i] : (unsigned char)0;
-            if (SEARCH)
-                pp[r] = in ? find_first_partner(g, i, n_res, sa.thr2, sa.thrf, pos, sa.posf, cell, sa.cell_start, newcell,
-                                                id, flags, sa.arr_head, sa.arr_next, sa.guest_src, tested)
-                           : -1;
-            else
-                pp[r] = in ? partner[i] : -1;
+            pp[r] = in ? partner[i] : -1;
         }
 #pragma unroll
-        for (int r = 0; r < kResolveRows; r++) {
-            if (SEARCH)
-                qq[r] = pp[r] >= 0 ? find_first_partner(g, pp[r], n_res, sa.thr2, sa.thrf, pos, sa.posf, cell, sa.cell_start,
-                                                        newcell, id, flags, sa.arr_head, sa.arr_next, sa.guest_src, tested)
-                                   : -1;
-            else
-                qq[r] = pp[r] >= 0 ? partner[pp[r]] : -1;
-        }
+        for (int r = 0; r < kResolveRows; r++) qq[r] = pp[r] >= 0 ? partner[pp[r]] : -1;
 #pragma unroll
         for (int r = 0; r < kResolveRows; r++) {
             const long long ii = t0 + (long long)r * kThreads + threadIdx.x;
@@ -189,7 +161,6 @@ k_resolve(Geom g, const int *__restrict__ n_res_ptr, int n_guest, const int *__r
         for (int k = 0; k < kWarps; k++) tot += warp_cnt[k];
         if (tot) atomicAdd(&ctr->collisions, (unsigned long long)tot);
     }
-    if (SEARCH && sa.collision_pairs) block_add_u64(tested, sa.collision_pairs);  // stats only (uniform branch)
 }
 
 struct MoveArgs {

@@ -103,7 +103,6 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
             if (!strcmp(e, "pairs")) c->collide_grid = false;
             else if (!strcmp(e, "grid")) c->collide_grid = true;
         }
-        if (const char *e = getenv("PARSIM_FUSE_SEARCH")) c->fuse_search = atoi(e) != 0;
         if (c->collide_grid) {
 #define PS_COLLIDE_ATTR(IT)                                                                              \
     PS_CUDA(c, cudaFuncSetAttribute(k_collide_cells<IT>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
@@ -118,7 +117,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     if (const char *e = getenv("PARSIM_FORCE_VARIANT")) c->force_variant = atoi(e);
     {   // only instantiations that the variant-agreement test covers (tests/test_gpu_parity.py)
         const int v = c->force_variant;
-        if (!(v >= 0 && v <= 7) && v != 10 && v != 11)
+        if (!(v >= 0 && v <= 6) && v != 10 && v != 11)
             return c->fail("PARSIM_FORCE_VARIANT: unknown force-kernel variant " + std::to_string(v));
     }
     if (const char *e = getenv("PARSIM_CAPACITY_PCT")) {

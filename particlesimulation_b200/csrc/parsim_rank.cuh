@@ -100,7 +100,6 @@ struct Rank {
     float thrf = 0;                            // pre-filter threshold on the FP32 squared distance
     // cell-centric collision search (parsim_collide.cuh); off: per-particle all-pairs k_collide_find
     bool collide_grid = false;
-    bool fuse_search = true;  // sparse regime: search inside k_resolve (PARSIM_FUSE_SEARCH=0: separate k_collide_find)
     int grid_nb = 1, grid_cap = 0, grid_it = 2, big_nb = 1, big_cap = 0;
     int *big_cells = nullptr, *d_big_count = nullptr;  // d_big_count[0]: big cells, [1]: huge-cell slices
     int2 *huge_items = nullptr;

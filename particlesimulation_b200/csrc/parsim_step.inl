@@ -198,9 +198,8 @@ static int stage_force(Rank *c) {
         case 1: PS_FORCE(2, 256, 0, 16); break;   // sparse cells: neighbourhood through L1, 32 registers, full occupancy
         case 3: PS_FORCE(8, 1280, 16, 5); break;  // deep unroll, 96 registers (comparison)
         case 4: PS_FORCE(2, 256, 0, 8); break;    // sparse cells at 64 registers (comparison)
-        case 5: PS_FORCE_TB(128, 4, 768, 0, 8, true); break;  // asynchronous staging, neighbours before the barrier
-        case 6: PS_FORCE_TB(128, 4, 1024, 0, 7, true); break;
-        case 7: PS_FORCE_TB(256, 4, 1536, 0, 4, true); break;
+        case 5: PS_FORCE_TB(128, 2, 256, 0, 16, true); break;  // sparse cells, neighbours before the barrier
+        case 6: PS_FORCE_TB(128, 2, 256, 0, 12, true); break;  // the same at 40 registers
         case 10: PS_FORCE_TB(64, 4, 384, 8, 16); break;   // 2-warp blocks, 16 per SM: 29.7 ms per config-3 run (default 28.8)
         case 11: PS_FORCE_TB(256, 4, 1024, 16, 4); break; // 8-warp blocks, 4 per SM: 28.9 ms
         default: PS_FORCE(4, 768, 16, 8); break;  // 64 registers, 8 blocks per SM
@@ -273,7 +272,7 @@ static int stage_collide(Rank *c) {
                       a, c->huge_items, c->d_big_count + 1));
         PS_LAUNCH(c, K_COLLIDE_BIG, 0.0, "k_collide_huge",
                   k_collide_huge<<<c->sm_count * 8, kThreads, 0, c->stream>>>(a, c->huge_items, c->d_big_count + 1));
-    } else if (!c->fuse_search) {
+    } else {
         PS_LAUNCH(c, K_COLLIDE, 21.0 * n_tot + 8.0 * g.ncells, "k_collide_find",
                   k_collide_find<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
                       g, &c->d_ctr->n_next, c->n_guest, c->thr2, c->thrf, c->pos_alt, c->posf, c->cell_cur, c->cs_cur, c->newcell,
@@ -281,26 +280,12 @@ static int stage_collide(Rank *c) {
                       c->opt_stats ? &c->d_ctr->collision_pairs : nullptr));
     }
     if (c->nranks > 1) PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 4 * sizeof(int), c->stream));
-    SearchArgs sa;
-    sa.thr2 = c->thr2; sa.thrf = c->thrf; sa.posf = c->posf; sa.cell_start = c->cs_cur; sa.arr_head = c->arr_head;
-    sa.arr_next = c->arr_next; sa.guest_src = c->guest_src;
-    sa.collision_pairs = c->opt_stats ? &c->d_ctr->collision_pairs : nullptr;
-#define PS_RESOLVE_ARGS                                                                                      \
-    g, &c->d_ctr->n_next, c->n_guest, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt, c->vel_cur,   \
-        c->id_cur, c->fate, c->count, c->dead_new_count, c->mv_head, c->dm_head, c->mv_next, c->grave_pos,     \
-        c->grave_vel, c->grave_id, c->grave_cell, c->cap, c->d_ctr, c->mig_list,                               \
-        c->nranks > 1 ? c->mig_hdr_send + 3 : nullptr, c->mig_list_cap, sa
-    if (!c->collide_grid && c->fuse_search) {
-        // sparse cells: search and resolve in ONE pass over the particles (parsim_merge.cuh)
-        PS_LAUNCH(c, K_COLLIDE, 31.0 * n_tot + 8.0 * g.ncells, "k_resolve<search>",
-                  k_resolve<true, kSearchRows, 6><<<std::min(grid_for(n_tot, kThreads * kSearchRows), c->sm_count * 6),
-                                                    kThreads, 0, c->stream>>>(PS_RESOLVE_ARGS));
-    } else {
-        PS_LAUNCH(c, K_RESOLVE, 10.0 * n_tot, "k_resolve",
-                  k_resolve<false, kResolveRows, PS_RESOLVE_MINB><<<std::min(grid_for(n_tot, kThreads * kResolveRows), c->sm_count * 8),
-                                                                    kThreads, 0, c->stream>>>(PS_RESOLVE_ARGS));
-    }
-#undef PS_RESOLVE_ARGS
+    PS_LAUNCH(c, K_RESOLVE, 10.0 * n_tot, "k_resolve",
+              k_resolve<<<std::min(grid_for(n_tot, kThreads * kResolveRows), c->sm_count * 8), kThreads, 0, c->stream>>>(
+                  g, &c->d_ctr->n_next, c->n_guest, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,
+                  c->vel_cur, c->id_cur, c->fate, c->count, c->dead_new_count, c->mv_head, c->dm_head,
+                  c->mv_next, c->grave_pos, c->grave_vel, c->grave_id, c->grave_cell, c->cap, c->d_ctr, c->mig_list,
+                  c->nranks > 1 ? c->mig_hdr_send + 3 : nullptr, c->mig_list_cap));
     if (c->deferred) {
         // Single strip, no instrumentation: the host does not wait for the step.  The kernels read the
         // particle count from Counters::n_next, the grids above are sized for the host's (older, hence

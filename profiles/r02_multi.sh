@@ -10,6 +10,10 @@ mkdir -p $out
 nvidia-smi --query-gpu=index,name --format=csv,noheader
 ( timeout -s KILL 600 python -m pytest tests/test_gpu_multi.py -m gpu -x -q ) > $out/pytest_multi_$tag.log 2>&1
 echo "pytest multi rc=$?"; tail -n 4 $out/pytest_multi_$tag.log
+for v in 1 5 6; do  # sparse-cell force variants at config 4's density (one GPU)
+    FORCE_STEPS_WORKLOAD="3 354 3536 100000000" PARSIM_FORCE_VARIANT=$v timeout -s KILL 60 python tools/force_steps.py 2>> $out/force_steps_$tag.err
+done | tee $out/force_steps_${tag}_config4w.txt
+nvidia-smi topo -m > $out/topo_$tag.txt 2>&1; (numactl -H || lscpu | grep -i numa) >> $out/topo_$tag.txt 2>&1
 pins=$out/pins_$tag.jsonl
 : > $pins
 run() { timeout -s KILL 300 python tools/pin_run.py "$@" >> $pins 2>> $out/pins_$tag.err; tail -n 1 $pins; }

@@ -209,30 +209,26 @@ def test_run_is_deterministic_and_matches_staged():
                          ids=lambda c: " ".join(map(str, c)))
 def test_collision_search_paths_agree(case, monkeypatch):
     """The sub-grid collision search (warp per cell, block per big cell, all-pairs fallback for
-    lists beyond the staging area) must give exactly the result of the per-particle all-pairs sweep,
-    whether that sweep runs inside the resolve kernel (the default of the sparse regime) or as a
-    kernel of its own that writes the partner array (PARSIM_FUSE_SEARCH=0)."""
+    lists beyond the staging area) must give exactly the result of the per-particle all-pairs sweep."""
     seed, side, nc, n, steps = case
     res = {}
-    for mode in ("pairs", "pairs-unfused", "grid"):
-        monkeypatch.setenv("PARSIM_COLLIDE", mode.split("-")[0])
-        monkeypatch.setenv("PARSIM_FUSE_SEARCH", "0" if mode.endswith("unfused") else "1")
+    for mode in ("pairs", "grid"):
+        monkeypatch.setenv("PARSIM_COLLIDE", mode)
         g = ParticleSimulation(seed, side, nc, n)
         g.simulate(steps)
         res[mode] = (g.result(), g.dump())
         g.close()
-    for mode in ("pairs-unfused", "grid"):
-        assert res["pairs"][0] == res[mode][0], mode
-        for k in ("x", "y", "vx", "vy", "m", "alive"):
-            assert np.array_equal(res["pairs"][1][k], res[mode][1][k]), (mode, k)
+    assert res["pairs"][0] == res["grid"][0]
+    for k in ("x", "y", "vx", "vy", "m", "alive"):
+        assert np.array_equal(res["pairs"][1][k], res["grid"][1][k]), k
 
 
-FORCE_VARIANTS = [0, 1, 2, 3, 4, 5, 6, 7, 10, 11]  # = what rank_create accepts (csrc/parsim_rank.cu)
+FORCE_VARIANTS = [0, 1, 2, 3, 4, 5, 6, 10, 11]  # = what rank_create accepts (csrc/parsim_rank.cu)
 
 
 def test_unknown_force_variant_is_rejected(monkeypatch):
     from particlesimulation_b200 import ParsimError
-    for v in ("8", "9", "12", "15", "-1"):
+    for v in ("7", "9", "12", "-1"):
         monkeypatch.setenv("PARSIM_FORCE_VARIANT", v)
         with pytest.raises(ParsimError):
             ParticleSimulation(1, 2, 3, 10)

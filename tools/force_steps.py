@@ -9,7 +9,9 @@ import sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from particlesimulation_b200 import ParticleSimulation  # noqa: E402
 
-sim = ParticleSimulation(7, 100.0, 1000, 100_000_000, device_init=True, options={"keep_initial": 1})
+# FORCE_STEPS_WORKLOAD="<seed> <side> <ncside> <n_part>" picks another workload (default: config 3)
+w = os.environ.get("FORCE_STEPS_WORKLOAD", "7 100 1000 100000000").split()
+sim = ParticleSimulation(int(w[0]), float(w[1]), int(w[2]), int(w[3]), device_init=True, options={"keep_initial": 1})
 sim.simulate(10)  # warm-up
 sim.reset()
 sim.set_option("stats", 1)
@@ -19,5 +21,5 @@ for _ in range(10):
     sim.simulate(1)
     k = sim.stats()["kernels"]
     out.append(round(k["force_integrate"]["ms"], 3))
-print(json.dumps({"variant": os.environ.get("PARSIM_FORCE_VARIANT", "default"), "force_ms_per_step": out,
+print(json.dumps({"variant": os.environ.get("PARSIM_FORCE_VARIANT", "default"), "workload": " ".join(w), "force_ms_per_step": out,
                   "total": round(sum(out), 2), "collisions": sim.result()[2]}))
