@@ -929,10 +929,84 @@ k_collide_find(Geom g, const int *__restrict__ n_res_ptr, int n_guest, double th
 // ---------------------------------------------------------------------------------------
 __global__ void k_set_int(int *dst, int v) { *dst = v; }
 
-// Tombstone counts: total per cell += this step's deaths (and the per-step array is cleared).
-__global__ void k_add_counts(int n, int *__restrict__ acc, int *__restrict__ add) {
-    int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c < n) { acc[c] += add[c]; add[c] = 0; }
+// start of a step: the three work-list counters of the step in one launch (instead of three memsets)
+__global__ void k_step_reset(Counters *ctr, int *big_count, int *move_big_count) {
+    ctr->n_movers = 0;
+    if (big_count) { big_count[0] = 0; big_count[1] = 0; }
+    *move_big_count = 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// Two scans in one pass (the end of a step needs the new cell_start AND the new tombstone_start):
+// A is scanned as it is; B is (acc + add), and acc += add, add = 0 is done on the way (the running
+// tombstone count per cell takes up this step's deaths).  tile_sums holds 2 * ntiles entries.
+__global__ void k_scan2_tile_sums(const int *__restrict__ a, const int *__restrict__ acc, const int *__restrict__ add,
+                                  int N, int ntiles, int *tile_sums) {
+    __shared__ int ws[33];
+    int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    int sa = 0, sb = 0;
+#pragma unroll
+    for (int j = 0; j < kScanItems; j++) {
+        int k = base + j;
+        if (k < N) { sa += a[k]; sb += acc[k] + add[k]; }
+    }
+    int tot;
+    block_exclusive_scan(sa, ws, tot);
+    if (threadIdx.x == 0) tile_sums[blockIdx.x] = tot;
+    block_exclusive_scan(sb, ws, tot);
+    if (threadIdx.x == 0) tile_sums[ntiles + blockIdx.x] = tot;
+}
+
+__global__ void k_scan2_top(int *tile_sums, int ntiles, int *total_a, int *total_a2, int *total_b) {
+    __shared__ int ws[33];
+    for (int half = 0; half < 2; half++) {
+        int *ts = tile_sums + half * ntiles;
+        int carry = 0;
+        for (int base = 0; base < ntiles; base += kThreads) {
+            int k = base + threadIdx.x;
+            int v = k < ntiles ? ts[k] : 0;
+            int tot;
+            int ex = block_exclusive_scan(v, ws, tot);
+            if (k < ntiles) ts[k] = carry + ex;
+            carry += tot;
+        }
+        if (threadIdx.x == 0) {
+            if (half == 0) { *total_a = carry; if (total_a2) *total_a2 = carry; }
+            else *total_b = carry;
+        }
+        __syncthreads();
+    }
+}
+
+__global__ void k_scan2_apply(const int *__restrict__ a, int *__restrict__ acc, int *__restrict__ add, int N, int ntiles,
+                              const int *__restrict__ tile_sums, int *__restrict__ out_a, int *__restrict__ out_b) {
+    __shared__ int ws[33];
+    int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    int va[kScanItems], vb[kScanItems];
+    int sa = 0, sb = 0;
+#pragma unroll
+    for (int j = 0; j < kScanItems; j++) {
+        int k = base + j;
+        va[j] = k < N ? a[k] : 0;
+        vb[j] = k < N ? acc[k] + add[k] : 0;
+        sa += va[j];
+        sb += vb[j];
+    }
+    int tot;
+    int ea = block_exclusive_scan(sa, ws, tot) + tile_sums[blockIdx.x];
+    int eb = block_exclusive_scan(sb, ws, tot) + tile_sums[ntiles + blockIdx.x];
+#pragma unroll
+    for (int j = 0; j < kScanItems; j++) {
+        int k = base + j;
+        if (k < N) {
+            out_a[k] = ea;
+            out_b[k] = eb;
+            acc[k] = vb[j];
+            add[k] = 0;
+        }
+        ea += va[j];
+        eb += vb[j];
+    }
 }
 
 // ---------------------------------------------------------------------------------------

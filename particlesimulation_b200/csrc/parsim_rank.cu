@@ -161,7 +161,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     PS_ALLOC(c, c->cs_cur, C + 1, true); PS_ALLOC(c, c->cs_alt, C + 1, true);
     PS_ALLOC(c, c->count, C, true);
     const size_t H = (size_t)kSortMaxBins * (N / kSortTile + 1);  // radix-sort tile histograms
-    PS_ALLOC(c, c->tile_sums, std::max(C, H) / kScanTile + 2, true);
+    PS_ALLOC(c, c->tile_sums, 2 * (std::max(C, H) / kScanTile + 2), true);
     PS_ALLOC(c, c->sort_hist, H, false); PS_ALLOC(c, c->sort_hist_scan, H + 1, false);
     PS_ALLOC(c, c->newcell, N, false);
     PS_ALLOC(c, c->partner, N, false);

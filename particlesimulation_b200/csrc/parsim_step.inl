@@ -14,6 +14,19 @@ static int device_scan(Rank *c, const int *in, int N, int *out, int *total2) {
     return 0;
 }
 
+// both scans of the end of a step in three launches (k_scan2_*): a -> out_a (total also to *total_a2),
+// acc + add -> out_b with acc += add, add = 0
+static int device_scan2(Rank *c, const int *a, int *acc, int *add, int N, int *out_a, int *total_a2, int *out_b) {
+    int ntiles = (N + kScanTile - 1) / kScanTile;
+    PS_LAUNCH(c, K_SCAN, 32.0 * N, "k_scan2", {
+        k_scan2_tile_sums<<<ntiles, kThreads, 0, c->stream>>>(a, acc, add, N, ntiles, c->tile_sums);
+        k_scan2_top<<<1, kThreads, 0, c->stream>>>(c->tile_sums, ntiles, out_a + N, total_a2, out_b + N);
+        k_scan2_apply<<<ntiles, kThreads, 0, c->stream>>>(a, acc, add, N, ntiles, c->tile_sums, out_a, out_b);
+    });
+    if (c->opt_stats) c->stats.kernel_launches[K_SCAN] += 2;
+    return 0;
+}
+
 // One stable radix pass over `bits` key bits starting at bit 0 of keyA (digits of <= 8 bits).
 // Entries are (keyA, srcA); srcA == nullptr means source = index.  Results end in (keyA, srcA).
 static int sort_passes(Rank *c, int n, int bits, unsigned *&keyA, unsigned *&keyB, int *&srcA, int *&srcB,
@@ -97,12 +110,12 @@ static void launch_move(Rank *c, const MoveArgs &a, bool big) {
 // Sources are entries [0, n_src) of (pos_alt, vel_cur, m_cur, id_cur) with their fate byte.
 static int merge_step(Rank *c, int n_src, int n_surv, bool with_dead) {
     const Geom &g = c->g;
-    if (device_scan(c, c->count, g.ncells, c->cs_alt, &c->d_ctr->n_next)) return 1;
-    if (with_dead) {
-        PS_LAUNCH(c, K_TOMBSTONES, 12.0 * g.ncells, "k_add_counts",
-                  k_add_counts<<<grid_for(g.ncells), kThreads, 0, c->stream>>>(g.ncells, c->dead_count,
-                                                                               c->dead_new_count));
-        if (device_scan(c, c->dead_count, g.ncells, c->dead_start_alt, nullptr)) return 1;
+    if (with_dead) {  // new cell_start and new tombstone_start (running tombstone counts += this step's) together
+        if (device_scan2(c, c->count, c->dead_count, c->dead_new_count, g.ncells, c->cs_alt, &c->d_ctr->n_next,
+                         c->dead_start_alt))
+            return 1;
+    } else if (device_scan(c, c->count, g.ncells, c->cs_alt, &c->d_ctr->n_next)) {
+        return 1;
     }
     MoveArgs a;
     a.cs_old = c->cs_cur; a.cs_new = c->cs_alt;
@@ -115,7 +128,6 @@ static int merge_step(Rank *c, int n_src, int n_surv, bool with_dead) {
     a.pos_out = c->pos_cur; a.vel_out = c->vel_alt; a.m_out = c->m_alt; a.id_out = c->id_alt;
     a.cell_out = c->cell_alt;
     a.big_list = c->move_big_list; a.big_count = c->d_move_big_count; a.big_min = c->move_big_min;
-    PS_CUDA(c, cudaMemsetAsync(c->d_move_big_count, 0, sizeof(int), c->stream));
     // 1 fate + 4 id read per source entry, 40 read + 48 written per survivor, 8 B per tombstone
     PS_LAUNCH(c, K_MOVE, 5.0 * n_src + 88.0 * n_surv + 16.0 * g.ncells + (with_dead ? 8.0 * c->n_tomb : 0.0), "k_move", {
         // lanes per cell from the CURRENT occupancy (the result does not depend on it)
@@ -159,6 +171,7 @@ static int stage_bin_com(Rank *c) {
         if (sort_initial(c)) return 1;
         c->sorted = true;
     }
+    k_step_reset<<<1, 1, 0, c->stream>>>(c->d_ctr, c->d_big_count, c->d_move_big_count);  // work-list counters of this step
     PS_LAUNCH(c, K_COM, 24.0 * c->n_alive + 24.0 * g.ncells, "k_com", {
         switch (c->com_lanes) {
         case 4: launch_com<4>(c); break;
@@ -186,7 +199,6 @@ static int stage_force(Rank *c) {
         c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
         c->dbg_acc)
 #define PS_FORCE(UN, TILE, CELLS, MINB) PS_FORCE_TB(128, UN, TILE, CELLS, MINB)
-    PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->n_movers, 0, sizeof(int), c->stream));
     // variant by current occupancy (cells fill up or empty out as the run goes on)
     int v = c->force_variant;
     if (v <= 0) v = (double)c->n_alive < 28.0 * c->g.ncells ? 1 : 2;  // measured crossover: about 30 per cell
@@ -249,7 +261,6 @@ static int stage_collide(Rank *c) {
         a.partner = c->partner;
         a.collision_pairs = c->opt_stats ? &c->d_ctr->collision_pairs : nullptr;
         a.worklist = c->big_cells; a.work_count = c->d_big_count;
-        PS_CUDA(c, cudaMemsetAsync(c->d_big_count, 0, 2 * sizeof(int), c->stream));
         a.nb = c->grid_nb; a.inv_h = c->grid_nb / g.cellw; a.cap = c->grid_cap;
         PS_LAUNCH(c, K_COLLIDE, 29.0 * n_tot + 8.0 * g.ncells, "k_collide_cells", {
             // entries per lane from the CURRENT occupancy (+2 sigma); fuller cells go to k_collide_big
