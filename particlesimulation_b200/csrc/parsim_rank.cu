@@ -115,6 +115,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
         }
     }
     if (const char *e = getenv("PARSIM_FORCE_VARIANT")) c->force_variant = atoi(e);
+    if (const char *e = getenv("PARSIM_SPARSE_VARIANT")) c->sparse_variant = atoi(e) == 1 ? 1 : 5;
     {   // only instantiations that the variant-agreement test covers (tests/test_gpu_parity.py)
         const int v = c->force_variant;
         if (!(v >= 0 && v <= 6) && v != 10 && v != 11)

@@ -82,6 +82,7 @@ struct Rank {
     double thr2 = 0;    // collision threshold on the squared distance (see k_collide_find)
     int com_lanes = 32; // lanes per cell in k_com, from the GLOBAL particles-per-cell
     int force_variant = 0; // k_force_integrate instantiation (PARSIM_FORCE_VARIANT; 0: by occupancy)
+    int sparse_variant = 5; // the instantiation for sparse cells (PARSIM_SPARSE_VARIANT: 1 or 5)
 
     // particle storage: alive residents [0, n_alive), guests after them until the rebin
     int cap = 0;

@@ -201,7 +201,7 @@ static int stage_force(Rank *c) {
 #define PS_FORCE(UN, TILE, CELLS, MINB) PS_FORCE_TB(128, UN, TILE, CELLS, MINB)
     // variant by current occupancy (cells fill up or empty out as the run goes on)
     int v = c->force_variant;
-    if (v <= 0) v = (double)c->n_alive < 28.0 * c->g.ncells ? 1 : 2;  // measured crossover: about 30 per cell
+    if (v <= 0) v = (double)c->n_alive < 28.0 * c->g.ncells ? c->sparse_variant : 2;  // measured crossover: about 30 per cell
     // an empty strip (everybody dead, or a strip the cloud does not reach) has nothing to move; the
     // kernels read cell[first] / cell[last] of their block unconditionally, so they are not launched
     if (c->n_alive > 0)
