@@ -19,7 +19,8 @@ namespace parsim {
 
 struct CollideArgs {
     Geom g;
-    const int *n_res_ptr; // residents [0, *n_res_ptr), guests from other strips behind them
+    int n_res_val;        // residents [0, n_res), guests from other strips behind them;
+    const int *n_res_ptr; // n_res = *n_res_ptr when non-null (deferred steps), else n_res_val
     double thr2;          // squared-distance threshold (see k_collide_find)
     const double2 *pos;   // post-move positions
     const int *cell, *cell_start, *newcell;
@@ -38,7 +39,7 @@ struct CollideArgs {
 
 __device__ __forceinline__ unsigned long long entry_key(const CollideArgs &a, int k) {
     if (a.flags[k] & F_REMOVED) {  // an arrival: appended after the bin-time entries, by (source cell, id)
-        const int n_res = *a.n_res_ptr;
+        const int n_res = a.n_res_ptr ? *a.n_res_ptr : a.n_res_val;
         const int src = k < n_res ? a.cell[k] + a.g.cell_base : a.guest_src[k - n_res];
         return list_key(F_REMOVED, src, a.id[k]);
     }

@@ -599,7 +599,7 @@ __device__ __forceinline__ void cp_async_wait_all() {
 // operations in the same order per target: bit-identical results.
 template <int TB, int UNROLL, int TILE, int CELLS, int MINB, bool EARLY = false>
 __global__ void __launch_bounds__(TB, MINB)
-k_force_integrate(Geom g, const int *__restrict__ n_ptr, const double2 *__restrict__ pos_in,
+k_force_integrate(Geom g, int n_val, const int *__restrict__ n_ptr, const double2 *__restrict__ pos_in,
                   const double *__restrict__ m, const int *__restrict__ cell,
                   const int *__restrict__ cell_start, const double2 *__restrict__ com_xy,
                   const double *__restrict__ com_m, double2 *__restrict__ pos_out,
@@ -610,7 +610,10 @@ k_force_integrate(Geom g, const int *__restrict__ n_ptr, const double2 *__restri
     __shared__ double s_m[TILE];
     __shared__ double2 s_nxy[CELLS > 0 ? CELLS * 8 : 1];
     __shared__ double s_nm[CELLS > 0 ? CELLS * 8 : 1];
-    const int n = *n_ptr;  // the grid is sized for an upper bound (the host may lag a step or two)
+    // deferred steps (small problems): the count comes from device memory and the grid is sized for an
+    // upper bound; otherwise the host knows it (the extra dependent load costs latency-bound kernels
+    // up to a third of their time at 1e8 particles, profiles/bench_r02_v5_config4w.json)
+    const int n = n_ptr ? *n_ptr : n_val;
     const int b0 = blockIdx.x * TB;
     if (b0 >= n) return;
     const int i = b0 + threadIdx.x;
@@ -909,7 +912,7 @@ __device__ __forceinline__ int find_first_partner(const Geom &g, int i, int n_re
 #define PS_FIND_MINB 6
 #endif
 __global__ void __launch_bounds__(kThreads, PS_FIND_MINB)
-k_collide_find(Geom g, const int *__restrict__ n_res_ptr, int n_guest, double thr2, float thrf,
+k_collide_find(Geom g, int n_res_val, const int *__restrict__ n_res_ptr, int n_guest, double thr2, float thrf,
                const double2 *__restrict__ pos,
                const float2 *__restrict__ posf,
                const int *__restrict__ cell, const int *__restrict__ cell_start,
@@ -917,7 +920,7 @@ k_collide_find(Geom g, const int *__restrict__ n_res_ptr, int n_guest, double th
                const unsigned char *__restrict__ flags, const int *__restrict__ arr_head,
                const int *__restrict__ arr_next, const int *__restrict__ guest_src,
                int *__restrict__ partner, unsigned long long *collision_pairs) {
-    const int n_res = *n_res_ptr, n = n_res + n_guest;
+    const int n_res = n_res_ptr ? *n_res_ptr : n_res_val, n = n_res + n_guest;
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long tested = 0;
     if (i < n)

@@ -43,7 +43,7 @@ enum Fate : unsigned char {
 constexpr int kResolveRows = PS_RESOLVE_ROWS;
 
 __global__ void __launch_bounds__(kThreads, PS_RESOLVE_MINB)
-k_resolve(Geom g, const int *__restrict__ n_res_ptr, int n_guest, const int *__restrict__ partner, const int *__restrict__ cell,
+k_resolve(Geom g, int n_res_val, const int *__restrict__ n_res_ptr, int n_guest, const int *__restrict__ partner, const int *__restrict__ cell,
           const int *__restrict__ newcell, const unsigned char *__restrict__ flags,
           const double2 *__restrict__ pos, const double2 *__restrict__ vel,
           const unsigned *__restrict__ id, unsigned char *__restrict__ fate, int *count,
@@ -52,7 +52,7 @@ k_resolve(Geom g, const int *__restrict__ n_res_ptr, int n_guest, const int *__r
           unsigned *__restrict__ grave_id, int *__restrict__ grave_cell, int grave_cap, Counters *ctr,
           int *__restrict__ late_list, int *late_count, int late_cap) {
     constexpr int kWarps = kThreads / 32;
-    const int n_res = *n_res_ptr, n = n_res + n_guest;
+    const int n_res = n_res_ptr ? *n_res_ptr : n_res_val, n = n_res + n_guest;
     __shared__ int warp_dying[kResolveRows][kWarps];
     __shared__ int tile_base;
     __shared__ unsigned warp_cnt[kWarps];

@@ -185,8 +185,8 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     memset(c->h_ctr, 0, sizeof(Counters));
     PS_CUDA(c, cudaMallocHost((void **)&c->h_ring, kCounterRing * sizeof(Counters)));
     for (int k = 0; k < kCounterRing; k++) PS_CUDA(c, cudaEventCreateWithFlags(&c->ev_ring[k], cudaEventDisableTiming));
+    c->defer_steps = c->use_graphs = n_part <= 4000000;  // above that a step is milliseconds of kernels: nothing to gain
     if (const char *e = getenv("PARSIM_SYNC_STEPS")) c->defer_steps = atoi(e) == 0;
-    c->use_graphs = n_part <= 4000000;  // above that a step is milliseconds of kernels: nothing to gain
     if (const char *e = getenv("PARSIM_GRAPHS")) c->use_graphs = atoi(e) != 0;
     PS_CUDA(c, cudaEventCreate(&c->run_a));
     PS_CUDA(c, cudaEventCreate(&c->run_b));

@@ -195,7 +195,7 @@ static int stage_bin_com(Rank *c) {
 static int stage_force(Rank *c) {
 #define PS_FORCE_TB(TB, UN, TILE, CELLS, MINB, ...)                                                 \
     k_force_integrate<TB, UN, TILE, CELLS, MINB, ##__VA_ARGS__><<<grid_for(c->n_alive, TB), TB, 0, c->stream>>>( \
-        c->g, &c->d_ctr->n_next, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m, \
+        c->g, c->n_alive, c->deferred ? &c->d_ctr->n_next : nullptr, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m, \
         c->pos_alt, c->posf, c->vel_cur, c->newcell, c->flags, c->partner, &c->d_ctr->n_movers,     \
         c->dbg_acc)
 #define PS_FORCE(UN, TILE, CELLS, MINB) PS_FORCE_TB(128, UN, TILE, CELLS, MINB)
@@ -254,7 +254,7 @@ static int stage_collide(Rank *c) {
     const int n_tot = c->n_alive + c->n_guest;
     if (c->collide_grid) {
         CollideArgs a;
-        a.g = g; a.n_res_ptr = &c->d_ctr->n_next; a.thr2 = c->thr2; a.pos = c->pos_alt;
+        a.g = g; a.n_res_val = c->n_alive; a.n_res_ptr = c->deferred ? &c->d_ctr->n_next : nullptr; a.thr2 = c->thr2; a.pos = c->pos_alt;
         a.cell = c->cell_cur; a.cell_start = c->cs_cur; a.newcell = c->newcell; a.id = c->id_cur;
         a.flags = c->flags; a.arr_head = c->arr_head; a.arr_next = c->arr_next; a.guest_src = c->guest_src;
         a.arr_cnt = c->arr_cnt; a.arr_rec = c->arr_rec;
@@ -286,14 +286,14 @@ static int stage_collide(Rank *c) {
     } else {
         PS_LAUNCH(c, K_COLLIDE, 21.0 * n_tot + 8.0 * g.ncells, "k_collide_find",
                   k_collide_find<<<grid_for(n_tot), kThreads, 0, c->stream>>>(
-                      g, &c->d_ctr->n_next, c->n_guest, c->thr2, c->thrf, c->pos_alt, c->posf, c->cell_cur, c->cs_cur, c->newcell,
+                      g, c->n_alive, c->deferred ? &c->d_ctr->n_next : nullptr, c->n_guest, c->thr2, c->thrf, c->pos_alt, c->posf, c->cell_cur, c->cs_cur, c->newcell,
                       c->id_cur, c->flags, c->arr_head, c->arr_next, c->guest_src, c->partner,
                       c->opt_stats ? &c->d_ctr->collision_pairs : nullptr));
     }
     if (c->nranks > 1) PS_CUDA(c, cudaMemsetAsync(c->mig_hdr_send, 0, 4 * sizeof(int), c->stream));
     PS_LAUNCH(c, K_RESOLVE, 10.0 * n_tot, "k_resolve",
               k_resolve<<<std::min(grid_for(n_tot, kThreads * kResolveRows), c->sm_count * 8), kThreads, 0, c->stream>>>(
-                  g, &c->d_ctr->n_next, c->n_guest, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,
+                  g, c->n_alive, c->deferred ? &c->d_ctr->n_next : nullptr, c->n_guest, c->partner, c->cell_cur, c->newcell, c->flags, c->pos_alt,
                   c->vel_cur, c->id_cur, c->fate, c->count, c->dead_new_count, c->mv_head, c->dm_head,
                   c->mv_next, c->grave_pos, c->grave_vel, c->grave_id, c->grave_cell, c->cap, c->d_ctr, c->mig_list,
                   c->nranks > 1 ? c->mig_hdr_send + 3 : nullptr, c->mig_list_cap));
@@ -462,8 +462,11 @@ int rank_run(Rank *c, long n_steps) {
     PS_CUDA(c, cudaSetDevice(c->device));
     if (c->uploading) return c->fail("upload not finished");
     if (c->next_stage != 0) return c->fail("parsim_run in the middle of a debug-staged step");
-    // no host round trip per step on a single strip, unless per-launch statistics or per-launch
-    // error checks are on
+    // No host round trip per step on a single strip whose steps are launch-bound (small problems),
+    // unless per-launch statistics or per-launch error checks are on.  At 1e8 particles a step is
+    // milliseconds of kernels, the round trip is 0.03 ms of it, and reading the particle count from
+    // device memory costs the latency-bound kernels more than that (measured: 63.9 against 63.5 ms per
+    // config-3 run, collision search +35 % at 8 per cell), so large problems keep the host in the loop.
     c->deferred = c->nranks == 1 && !c->opt_stats && !c->opt_sync_check && c->defer_steps;
     c->ring_pos = 0;
     PS_CUDA(c, cudaEventRecord(c->run_a, c->stream));
