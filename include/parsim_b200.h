@@ -28,9 +28,13 @@ int parsim_abi_version(void);
 /* ---- life cycle -------------------------------------------------------------------------
  * Replaces the ParticleSimulation constructor's allocations (serial/parsim.cpp:209-216:
  * particles(n_part), cellParticles(ncside^2), cells(ncside^2)).  `n_gpus` > 1 splits the
- * grid into row strips over devices 0..n_gpus-1 of this process (one host thread per
- * device inside parsim_run, NCCL halos/migrants; mpi/parsim-mpi.cpp:338-342,:371-372 is
- * the reference's equivalent decomposition). */
+ * grid into n_gpus row strips inside this process (one host thread per strip inside
+ * parsim_run; mpi/parsim-mpi.cpp:338-342,:371-372 is the reference's equivalent
+ * decomposition).  With at least n_gpus devices every strip gets its own GPU and the strips
+ * exchange halos / migrants over NCCL; with fewer devices the strips share the GPUs
+ * round-robin and exchange by device-to-device copies -- the reference's own way of testing
+ * its distributed variant on one machine (mpi/run_tests.sh:9-17).  Results do not depend on
+ * n_gpus or on the transport (environment PARSIM_TRANSPORT=local|nccl overrides the choice). */
 int parsim_create(parsim_ctx **out, double side, long ncside, long long n_part, int n_gpus);
 
 /* One strip of a multi-process job (one process per GPU, e.g. under torchrun): this process
@@ -64,7 +68,10 @@ const char *parsim_last_error(const parsim_ctx *ctx); /* ctx may be NULL: last c
  * Replaces the state that init_particles leaves in `particles` (serial/parsim.cpp:220-232).
  * Arrays are host memory, length n_part, particle id = array index; they are copied.
  * Every mass must be > 0 (true for every seed of the reference generator).  In a
- * multi-rank job every rank passes the same full arrays and keeps its own strip. */
+ * multi-rank job every rank passes the same full arrays and keeps its own strip; an
+ * in-process group (parsim_create, n_gpus > 1) copies every piece to ONE of its GPUs and all
+ * strips ingest from there (peer access), i.e. the host->device volume does not grow with
+ * the number of strips. */
 int parsim_upload(parsim_ctx *ctx, const double *x, const double *y, const double *vx,
                   const double *vy, const double *m);
 /* Same, in pieces: particles [id_base, id_base+count).  Call parsim_upload_begin first and
@@ -81,8 +88,8 @@ int parsim_upload_chunk_ids(parsim_ctx *ctx, long long count, const unsigned *id
  * `capacity` elements; *count = how many.  One strip per context. */
 int parsim_download(parsim_ctx *ctx, long long capacity, unsigned *ids, double *x, double *y,
                     double *vx, double *vy, double *m, long long *count);
-/* Restart from the state last uploaded, using a device-resident copy (option "keep_initial"
- * must be 1 before the upload): no host traffic. */
+/* Restart from the state last uploaded (the uploaded records stay in device memory untouched
+ * by the step loop): no host traffic.  The option "keep_initial" is accepted and ignored. */
 int parsim_reset(parsim_ctx *ctx);
 /* Host-side (C++) restatement of RandomGenerator + init_particles (serial/parsim.cpp:18-48,
  * :220-232): fills particles [first, first+count) of the seeded stream into host arrays of

@@ -86,6 +86,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     }
     double ppc = (double)n_part / ((double)ncside * (double)ncside);
     c->com_lanes = ppc <= 6 ? 4 : ppc <= 12 ? 8 : ppc <= 24 ? 16 : 32;
+    if (const char *e = getenv("PARSIM_COM_LANES")) { int v = atoi(e); if (v == 4 || v == 8 || v == 16 || v == 32) c->com_phys = v; }
 
     {   // sub-grid of the collision search: pitch >= EPSILON (with a margin for the binning arithmetic)
         const double hmin = kEpsilon * (1.0 + 1e-6);

@@ -164,6 +164,36 @@ static void launch_com(Rank *c) {
         c->opt_stats ? &c->d_ctr->force_pairs : nullptr);
 }
 
+template <int W, int P>
+static void launch_com_v(Rank *c) {
+    long long threads = ((long long)c->g.ncells + kComCells - 1) / kComCells * P;
+    k_com_v<W, P><<<grid_for(threads), kThreads, 0, c->stream>>>(
+        c->g, c->pos_cur, c->m_cur, c->cs_cur, c->com_xy, c->com_m,
+        c->opt_stats ? &c->d_ctr->force_pairs : nullptr);
+}
+
+// W = c->com_lanes fixes the summation order (from the GLOBAL initial density, the same on every
+// strip); the lanes that do the work follow the strip's CURRENT occupancy (k_com_v: same bits)
+static void launch_com_any(Rank *c) {
+    const int W = c->com_lanes;
+    const double occ = (double)c->n_alive / std::max(1, c->g.ncells);
+    int P = occ <= 6 ? 4 : occ <= 12 ? 8 : occ <= 24 ? 16 : 32;
+    if (c->com_phys > 0) P = c->com_phys;  // PARSIM_COM_LANES (tests)
+    P = std::min(P, W);
+    switch (W * 100 + P) {
+    case 3216: launch_com_v<32, 16>(c); break;
+    case 3208: launch_com_v<32, 8>(c); break;
+    case 3204: launch_com_v<32, 4>(c); break;
+    case 1608: launch_com_v<16, 8>(c); break;
+    case 1604: launch_com_v<16, 4>(c); break;
+    case 804: launch_com_v<8, 4>(c); break;
+    case 404: launch_com<4>(c); break;
+    case 808: launch_com<8>(c); break;
+    case 1616: launch_com<16>(c); break;
+    default: launch_com<32>(c); break;
+    }
+}
+
 // stage 0: binning (only when the cell order is not valid yet) + centre of mass + ghost rows
 static int stage_bin_com(Rank *c) {
     const Geom &g = c->g;
@@ -172,14 +202,7 @@ static int stage_bin_com(Rank *c) {
         c->sorted = true;
     }
     k_step_reset<<<1, 1, 0, c->stream>>>(c->d_ctr, c->d_big_count, c->d_move_big_count);  // work-list counters of this step
-    PS_LAUNCH(c, K_COM, 24.0 * c->n_alive + 24.0 * g.ncells, "k_com", {
-        switch (c->com_lanes) {
-        case 4: launch_com<4>(c); break;
-        case 8: launch_com<8>(c); break;
-        case 16: launch_com<16>(c); break;
-        default: launch_com<32>(c); break;
-        }
-    });
+    PS_LAUNCH(c, K_COM, 24.0 * c->n_alive + 24.0 * g.ncells, "k_com", launch_com_any(c));
     if (c->nranks == 1) {
         PS_LAUNCH(c, K_GHOST, 96.0 * g.nc, "k_ghost_wrap",
                   k_ghost_wrap<<<grid_for(g.nc), kThreads, 0, c->stream>>>(g, c->com_xy, c->com_m));
