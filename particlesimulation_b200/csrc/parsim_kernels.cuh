@@ -485,7 +485,7 @@ __global__ void __launch_bounds__(kThreads, LANES <= 8 ? 8 : PS_COM_MINB) k_com(
 // occupancy (cells thin out as particles collide) without the result depending on it -- on one GPU,
 // on N strips, at any point of the run.
 template <int W, int P>
-__global__ void __launch_bounds__(kThreads, 8) k_com_v(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
+__global__ void __launch_bounds__(kThreads, W / P >= 8 ? 2 : 4) k_com_v(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
                                                        const int *__restrict__ cell_start, double2 *__restrict__ com_xy,
                                                        double *__restrict__ com_m, unsigned long long *force_pairs) {
     static_assert(P >= 4 && P < W && W <= 32, "k_com_v: 4 <= P < W <= 32");
@@ -985,7 +985,7 @@ __device__ __forceinline__ int find_first_partner(const Geom &g, int i, int n_re
 // entries = *n_res_ptr residents + n_guest guests that arrived from other strips (those have
 // cell[i] = -1 and carry their source cell in guest_src[i - n_res]).
 #ifndef PS_FIND_MINB
-#define PS_FIND_MINB 6
+#define PS_FIND_MINB 8  // 32 registers: the search is a chain of dependent loads, occupancy decides (6 blocks: +35 %, profiles/gpurun_r02_v7.log)
 #endif
 __global__ void __launch_bounds__(kThreads, PS_FIND_MINB)
 k_collide_find(Geom g, int n_res_val, const int *__restrict__ n_res_ptr, int n_guest, double thr2, float thrf,
@@ -1007,6 +1007,12 @@ k_collide_find(Geom g, int n_res_val, const int *__restrict__ n_res_ptr, int n_g
 
 // ---------------------------------------------------------------------------------------
 __global__ void k_set_int(int *dst, int v) { *dst = v; }
+
+// Tombstone counts: total per cell += this step's deaths (and the per-step array is cleared).
+__global__ void k_add_counts(int n, int *__restrict__ acc, int *__restrict__ add) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c < n) { acc[c] += add[c]; add[c] = 0; }
+}
 
 // start of a step: the three work-list counters of the step in one launch (instead of three memsets)
 __global__ void k_step_reset(Counters *ctr, int *big_count, int *move_big_count) {
