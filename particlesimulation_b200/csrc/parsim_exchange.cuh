@@ -52,10 +52,16 @@ __device__ __forceinline__ void write_record(double *buf, int slot, double2 p, d
 }
 
 // counts into the header record of the three send buffers
-__global__ void k_seal_headers(const int *__restrict__ hdr, double *send_up, double *send_dn, double *send_far) {
+// The far header is all-gathered, so its second slot tells EVERY strip this strip's sticky device
+// error code: all strips leave the step together instead of waiting for a strip that gave up.
+__global__ void k_seal_headers(const int *__restrict__ hdr, double *send_up, double *send_dn, double *send_far,
+                               const Counters *__restrict__ ctr) {
     if (threadIdx.x == 0) send_up[0] = pack_u64((unsigned long long)(unsigned)hdr[0]);
     if (threadIdx.x == 1) send_dn[0] = pack_u64((unsigned long long)(unsigned)hdr[1]);
-    if (threadIdx.x == 2) send_far[0] = pack_u64((unsigned long long)(unsigned)hdr[2]);
+    if (threadIdx.x == 2) {
+        send_far[0] = pack_u64((unsigned long long)(unsigned)hdr[2]);
+        send_far[1] = pack_u64((unsigned long long)(unsigned)ctr->error);
+    }
 }
 
 // hdr[0] / hdr[1] = records for the strip above / below
@@ -217,7 +223,7 @@ inline int exchange_create(Rank *c, const unsigned char *nccl_id) {
     if (cudaMalloc((void **)&c->mig_list, sizeof(int) * (size_t)c->mig_list_cap) != cudaSuccess)
         return c->fail("cudaMalloc failed");
     if (cudaMallocHost((void **)&c->h_mig_hdr, (8 + c->nranks) * sizeof(int)) != cudaSuccess ||
-        cudaMallocHost((void **)&c->h_hdr64, (2 + c->nranks) * sizeof(unsigned long long)) != cudaSuccess)
+        cudaMallocHost((void **)&c->h_hdr64, (2 + 2 * (size_t)c->nranks) * sizeof(unsigned long long)) != cudaSuccess)
         return c->fail("cudaMallocHost failed");
     return 0;
 }
@@ -308,6 +314,30 @@ inline int exchange_halo(Rank *c) {
     return 0;
 }
 
+// Error codes of all strips as they were when the headers were sealed (h_hdr64[2 + 2r + 1]).
+inline int exchange_check_errors(Rank *c) {
+    for (int r = 0; r < c->nranks; r++) {
+        const int code = (int)c->h_hdr64[2 + 2 * r + 1];
+        if (!code) continue;
+        if (r == c->rank)
+            return c->fail(!c->soft_err.empty() ? c->soft_err
+                                                : "device error code " + std::to_string(code) +
+                                                      " (1 = capacity, 3 = migrant buffer overflow; 22 / 24 = a record for another strip arrived)");
+        return c->fail("strip " + std::to_string(r) + " reported device error code " + std::to_string(code));
+    }
+    return 0;
+}
+
+// A failure only THIS strip knows about (arrivals that do not fit): it becomes the strip's sticky
+// device error, the strip carries on without the offending records, and the next exchange (or the
+// check at the end of the run) tells everybody -- returning here would leave the other strips
+// waiting in their next collective.
+inline int exchange_soft_fail(Rank *c, const std::string &what) {
+    if (c->soft_err.empty()) c->soft_err = what;
+    k_set_int<<<1, 1, 0, c->stream>>>(&c->d_ctr->error, DE_CAPACITY);
+    return 0;
+}
+
 // Ship hdr_send[0] records up, hdr_send[1] down and all-gather the hdr_send[2] far records, in ONE
 // NCCL round (header + eager slots; see kEagerRecs).  On return mig_recv[0] / mig_recv[1] hold the
 // header and then *from_up / *from_dn records from above / below, and far_base[r] points at the
@@ -317,7 +347,7 @@ inline int exchange_records(Rank *c, int *from_up, int *from_dn, const double **
     NcclApi &api = nccl_api();
     const size_t eager = (size_t)(1 + std::min(c->mig_cap, c->eager_recs)) * kRec;
     const size_t far_eager = (size_t)(1 + c->far_eager) * kRec;
-    k_seal_headers<<<1, 32, 0, c->stream>>>(c->mig_hdr_send, c->mig_send[0], c->mig_send[1], c->far_send);
+    k_seal_headers<<<1, 32, 0, c->stream>>>(c->mig_hdr_send, c->mig_send[0], c->mig_send[1], c->far_send, c->d_ctr);
     PS_CUDA(c, cudaMemcpyAsync(c->h_mig_hdr, c->mig_hdr_send, 3 * sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     Rank *bup = c->bus ? c->bus->ranks[c->up] : nullptr, *bdn = c->bus ? c->bus->ranks[c->dn] : nullptr;
     if (c->bus) {
@@ -342,12 +372,11 @@ inline int exchange_records(Rank *c, int *from_up, int *from_dn, const double **
     }
     PS_CUDA(c, cudaMemcpyAsync(c->h_hdr64 + 0, c->mig_recv[0], 8, cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaMemcpyAsync(c->h_hdr64 + 1, c->mig_recv[1], 8, cudaMemcpyDeviceToHost, c->stream));
-    PS_CUDA(c, cudaMemcpy2DAsync(c->h_hdr64 + 2, 8, c->far_eager_recv, far_eager * sizeof(double), 8, c->nranks,
-                                 cudaMemcpyDeviceToHost, c->stream));
+    PS_CUDA(c, cudaMemcpy2DAsync(c->h_hdr64 + 2, 16, c->far_eager_recv, far_eager * sizeof(double), 16, c->nranks,
+                                 cudaMemcpyDeviceToHost, c->stream));  // (count, error code) of every strip
     PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
-    if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error) +
-                                        " (3 = migrant buffer overflow; 22 / 24 = a record for another strip arrived)");
+    if (exchange_check_errors(c)) return 1;  // the same verdict on every strip
     const int su = c->h_mig_hdr[0], sd = c->h_mig_hdr[1];
     const int ru = (int)c->h_hdr64[0], rd = (int)c->h_hdr64[1];
     c->h_mig_hdr[4] = ru;
@@ -355,7 +384,7 @@ inline int exchange_records(Rank *c, int *from_up, int *from_dn, const double **
     if (ru > c->mig_cap || rd > c->mig_cap) return c->fail("migrant buffer overflow on receive");
     int far_max = 0;  // the same on every strip: everybody sees all the counts
     for (int r = 0; r < c->nranks; r++) {
-        c->h_mig_hdr[8 + r] = (int)c->h_hdr64[2 + r];
+        c->h_mig_hdr[8 + r] = (int)c->h_hdr64[2 + 2 * r];
         far_max = std::max(far_max, c->h_mig_hdr[8 + r]);
     }
     if (far_max > kFarCap) return c->fail("far-record buffer overflow");
@@ -406,7 +435,12 @@ inline int exchange_emigrants(Rank *c) {
     if (exchange_records(c, &ru, &rd, far_base.data())) return 1;
     int n_far = 0;
     for (int r = 0; r < c->nranks; r++) if (r != c->rank) n_far += c->h_mig_hdr[8 + r];
-    if (c->n_alive + ru + rd + n_far > c->cap) return c->fail("strip capacity exceeded by arriving particles");
+    if (c->n_alive + ru + rd + n_far > c->cap) {
+        exchange_soft_fail(c, "strip capacity exceeded by arriving particles: raise PARSIM_CAPACITY_PCT");
+        ru = rd = 0;
+        for (int r = 0; r < c->nranks; r++) c->h_mig_hdr[8 + r] = 0;
+        n_far = 0;
+    }
     int first = c->n_alive, gfirst = 0;
     auto unpack = [&](int cnt, const double *buf, int filter) {
         if (!cnt) return;
@@ -438,7 +472,12 @@ inline int exchange_late(Rank *c, int *n_src, int *n_tombstones_in) {
     if (exchange_records(c, &ru, &rd, far_base.data())) return 1;
     int n_far = 0;
     for (int r = 0; r < c->nranks; r++) if (r != c->rank) n_far += c->h_mig_hdr[8 + r];
-    if (n_tot + ru + rd + n_far > c->cap) return c->fail("strip capacity exceeded by arriving particles");
+    if (n_tot + ru + rd + n_far > c->cap) {
+        exchange_soft_fail(c, "strip capacity exceeded by arriving particles: raise PARSIM_CAPACITY_PCT");
+        ru = rd = 0;
+        for (int r = 0; r < c->nranks; r++) c->h_mig_hdr[8 + r] = 0;
+        n_far = 0;
+    }
     int first = n_tot;
     auto unpack = [&](int cnt, const double *buf, int filter) {
         if (!cnt) return;
@@ -455,6 +494,29 @@ inline int exchange_late(Rank *c, int *n_src, int *n_tombstones_in) {
     *n_src = first;
     *n_tombstones_in = ru + rd + n_far;  // upper bound
     return check_launch(c, "exchange_late");
+}
+
+// End of a run: do all strips agree that nothing went wrong?  (An error raised after the last
+// exchange of the run -- by an unpack kernel, by the merge -- would otherwise surface on one strip
+// only, and the others would wait for it in parsim_result's reduction.)
+inline int exchange_final_check(Rank *c) {
+    if (c->bus) {
+        PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (bus_barrier(c)) return 1;
+        for (int r = 0; r < c->nranks; r++) c->h_hdr64[2 + 2 * r + 1] = (unsigned long long)(unsigned)c->bus->ranks[r]->h_ctr->error;
+        if (bus_barrier(c)) return 1;
+    } else {
+        NcclApi &api = nccl_api();
+        int *mine = c->mig_hdr_send + 4, *all = c->tile_sums;  // 1 int in, nranks ints out
+        PS_CUDA(c, cudaMemcpyAsync(mine, &c->d_ctr->error, sizeof(int), cudaMemcpyDeviceToDevice, c->stream));
+        PS_NCCL(c, api.AllGather(mine, all, 1, kNcclInt32, c->comm.comm, c->stream));
+        std::vector<int> codes(c->nranks);
+        PS_CUDA(c, cudaMemcpyAsync(codes.data(), all, sizeof(int) * c->nranks, cudaMemcpyDeviceToHost, c->stream));
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));
+        for (int r = 0; r < c->nranks; r++) c->h_hdr64[2 + 2 * r + 1] = (unsigned long long)(unsigned)codes[r];
+    }
+    return exchange_check_errors(c);
 }
 
 // sum of 4 doubles over all strips (particle 0 position, found flag, collisions)

@@ -476,82 +476,6 @@ __global__ void __launch_bounds__(kThreads, LANES <= 8 ? 8 : PS_COM_MINB) k_com(
     if (force_pairs) block_add_u64(pairs, force_pairs);  // stats only (uniform branch)
 }
 
-// The same sums with FEWER physical lanes than the order was defined for: W = the lane count that
-// fixes the summation order (k_com<W>: lane v sums entries v, v + W, ... and an xor butterfly joins
-// the W partial sums), P < W = the lanes that actually work on a pair of cells.  Lane p plays the
-// virtual lanes p, p + P, ..., each with its own accumulators; the butterfly levels >= P join
-// accumulators of the same lane, the levels below P are shuffles as before.  Same operands, same
-// operations, same order per cell: bit-identical to k_com<W>, so the lanes can follow the CURRENT
-// occupancy (cells thin out as particles collide) without the result depending on it -- on one GPU,
-// on N strips, at any point of the run.
-template <int W, int P>
-__global__ void __launch_bounds__(kThreads, W / P >= 8 ? 2 : 4) k_com_v(Geom g, const double2 *__restrict__ pos, const double *__restrict__ m,
-                                                       const int *__restrict__ cell_start, double2 *__restrict__ com_xy,
-                                                       double *__restrict__ com_m, unsigned long long *force_pairs) {
-    static_assert(P >= 4 && P < W && W <= 32, "k_com_v: 4 <= P < W <= 32");
-    constexpr int R = W / P;  // virtual lanes per physical lane
-    const int t = blockIdx.x * blockDim.x + threadIdx.x;
-    const int c0 = (t / P) * kComCells, lane = t % P;
-    int b[kComCells + 1];
-#pragma unroll
-    for (int q = 0; q <= kComCells; q++) b[q] = cell_start[min(c0 + q, g.ncells)];
-    unsigned long long pairs = 0;
-    double Ms[kComCells], Mxs[kComCells], Mys[kComCells];
-#pragma unroll
-    for (int q = 0; q < kComCells; q++) {
-        const int s = b[q], e = b[q + 1];
-        double M[R], Mx[R], My[R];
-#pragma unroll
-        for (int r = 0; r < R; r++) {
-            M[r] = 0; Mx[r] = 0; My[r] = 0;
-            for (int k = s + lane + r * P; k < e; k += W) {
-                const double mv = m[k];
-                const double2 p = pos[k];
-                M[r] += mv;
-                Mx[r] = fma(mv, p.x, Mx[r]);
-                My[r] = fma(mv, p.y, My[r]);
-            }
-        }
-#pragma unroll
-        for (int o = W / 2; o >= P; o >>= 1) {  // butterfly levels that stay inside the lane
-            const int d = o / P;
-            double nM[R], nMx[R], nMy[R];
-#pragma unroll
-            for (int r = 0; r < R; r++) {
-                nM[r] = M[r] + M[r ^ d];
-                nMx[r] = Mx[r] + Mx[r ^ d];
-                nMy[r] = My[r] + My[r ^ d];
-            }
-#pragma unroll
-            for (int r = 0; r < R; r++) { M[r] = nM[r]; Mx[r] = nMx[r]; My[r] = nMy[r]; }
-        }
-        double tM = M[0], tMx = Mx[0], tMy = My[0];
-#pragma unroll
-        for (int o = P / 2; o > 0; o >>= 1) {
-            tM += __shfl_xor_sync(0xffffffffu, tM, o);
-            tMx += __shfl_xor_sync(0xffffffffu, tMx, o);
-            tMy += __shfl_xor_sync(0xffffffffu, tMy, o);
-        }
-        Ms[q] = tM; Mxs[q] = tMx; Mys[q] = tMy;
-    }
-    {   // the four divisions of the two cells in one pass, as in k_com
-        const int q = (lane >> 1) & 1;
-        const double num = (lane & 1) ? (q ? Mys[1] : Mys[0]) : (q ? Mxs[1] : Mxs[0]);
-        const double den = q ? Ms[1] : Ms[0];
-        double val = 0.0;
-        if (lane < 4 && den > 0) val = num / den;
-        const double other = __shfl_down_sync(0xffffffffu, val, 1);
-        const int c = c0 + q;
-        if (lane < 4 && (lane & 1) == 0 && c < g.ncells) {
-            com_xy[c + g.nc] = make_double2(val, other);
-            com_m[c + g.nc] = den;
-            unsigned long long a = (unsigned long long)(q ? b[2] - b[1] : b[1] - b[0]);
-            pairs += a * (a - 1);
-        }
-    }
-    if (force_pairs) block_add_u64(pairs, force_pairs);  // stats only (uniform branch)
-}
-
 // Single strip: the ghost rows are the strip's own last / first row (periodic wrap,
 // serial/parsim.cpp:332-333).  Multi-strip runs fill them over NCCL instead.
 __global__ void k_ghost_wrap(Geom g, double2 *com_xy, double *com_m) {

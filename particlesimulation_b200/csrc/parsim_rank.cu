@@ -86,7 +86,6 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     }
     double ppc = (double)n_part / ((double)ncside * (double)ncside);
     c->com_lanes = ppc <= 6 ? 4 : ppc <= 12 ? 8 : ppc <= 24 ? 16 : 32;
-    if (const char *e = getenv("PARSIM_COM_LANES")) { int v = atoi(e); if (v == 4 || v == 8 || v == 16 || v == 32) c->com_phys = v; }
 
     {   // sub-grid of the collision search: pitch >= EPSILON (with a margin for the binning arithmetic)
         const double hmin = kEpsilon * (1.0 + 1e-6);
@@ -134,6 +133,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
         long long per_row = n_part / ncside + 1;
         long long mc = std::max<long long>(65536, 2 * per_row);
         c->mig_cap = (int)std::min<long long>(mc, n_part);
+        if (const char *e = getenv("PARSIM_MIG_CAP")) c->mig_cap = std::max(1, atoi(e));  // tests: force an overflow
         cap = (long long)((double)n_part / nranks * c->capacity_factor) + 4LL * c->mig_cap + 1024 +
               2LL * nranks * kFarCap;
         cap = std::min<long long>(cap, n_part + 2LL * c->mig_cap + 2LL * nranks * kFarCap);
@@ -241,6 +241,7 @@ static int reset_state(Rank *c) {
     c->n_tomb = 0; c->n_grave = 0; c->steps_done = 0; c->collisions_total = 0;
     c->have_newcell = c->have_flags = false;
     c->pos_latest = c->pos_cur;
+    c->soft_err.clear();
     // everything but the four statistics counters (parsim_stats_reset clears those)
     PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->collisions, 0, sizeof(unsigned long long), c->stream));
     PS_CUDA(c, cudaMemsetAsync(&c->d_ctr->deaths_step, 0, sizeof(Counters) - offsetof(Counters, deaths_step),

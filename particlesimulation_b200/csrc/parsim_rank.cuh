@@ -80,8 +80,7 @@ struct Rank {
     int rank = 0, nranks = 1, device = 0;
     Geom g{};
     double thr2 = 0;    // collision threshold on the squared distance (see k_collide_find)
-    int com_lanes = 32; // lanes per cell in k_com that fix the summation order, from the GLOBAL particles-per-cell
-    int com_phys = 0;   // PARSIM_COM_LANES: force the working lanes of k_com_v (0: from the current occupancy)
+    int com_lanes = 32; // lanes per cell in k_com, from the GLOBAL particles-per-cell
     int force_variant = 0; // k_force_integrate instantiation (PARSIM_FORCE_VARIANT; 0: by occupancy)
     int sparse_variant = 5; // the instantiation for sparse cells (PARSIM_SPARSE_VARIANT: 1 or 5)
 
@@ -184,6 +183,7 @@ struct Rank {
 
     cudaStream_t stream = nullptr;
     std::string err;
+    std::string soft_err;  // a failure only this strip knows about, until the next exchange tells the others
 
     // options / stats
     bool opt_stats = false, opt_sync_check = false;

@@ -173,32 +173,15 @@ static void launch_com(Rank *c) {
         c->opt_stats ? &c->d_ctr->force_pairs : nullptr);
 }
 
-template <int W, int P>
-static void launch_com_v(Rank *c) {
-    long long threads = ((long long)c->g.ncells + kComCells - 1) / kComCells * P;
-    k_com_v<W, P><<<grid_for(threads), kThreads, 0, c->stream>>>(
-        c->g, c->pos_cur, c->m_cur, c->cs_cur, c->com_xy, c->com_m,
-        c->opt_stats ? &c->d_ctr->force_pairs : nullptr);
-}
-
-// W = c->com_lanes fixes the summation order (from the GLOBAL initial density, the same on every
-// strip); the lanes that do the work follow the strip's CURRENT occupancy (k_com_v: same bits)
+// lanes per cell from the GLOBAL initial density (the same on every strip: the lane count fixes the
+// summation order).  Letting the working lanes follow the current occupancy with the order kept
+// (virtual lanes) was built and measured in round 2: 3.57 against 3.50 ms per config-3 run with 16
+// lanes, no gain from the automatic choice (profiles/gpurun_r02_v8.log) -- removed again.
 static void launch_com_any(Rank *c) {
-    const int W = c->com_lanes;
-    const double occ = (double)c->n_alive / std::max(1, c->g.ncells);
-    int P = occ <= 6 ? 4 : occ <= 12 ? 8 : occ <= 24 ? 16 : 32;
-    if (c->com_phys > 0) P = c->com_phys;  // PARSIM_COM_LANES (tests)
-    P = std::min(P, W);
-    switch (W * 100 + P) {
-    case 3216: launch_com_v<32, 16>(c); break;
-    case 3208: launch_com_v<32, 8>(c); break;
-    case 3204: launch_com_v<32, 4>(c); break;
-    case 1608: launch_com_v<16, 8>(c); break;
-    case 1604: launch_com_v<16, 4>(c); break;
-    case 804: launch_com_v<8, 4>(c); break;
-    case 404: launch_com<4>(c); break;
-    case 808: launch_com<8>(c); break;
-    case 1616: launch_com<16>(c); break;
+    switch (c->com_lanes) {
+    case 4: launch_com<4>(c); break;
+    case 8: launch_com<8>(c); break;
+    case 16: launch_com<16>(c); break;
     default: launch_com<32>(c); break;
     }
 }
@@ -347,7 +330,9 @@ static int stage_collide(Rank *c) {
     }
     PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
-    if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error));
+    // several strips: a device error is not reported here but through the next exchange, which lets
+    // every strip leave together (parsim_exchange.cuh)
+    if (c->h_ctr->error && c->nranks == 1) return c->fail("device error code " + std::to_string(c->h_ctr->error));
     const int grave_first = c->n_grave;
     const int deaths = c->h_ctr->grave_count - grave_first;
     c->n_grave = c->h_ctr->grave_count;
@@ -358,9 +343,13 @@ static int stage_collide(Rank *c) {
     // the tombstone lists change only when somebody died or a tombstone arrived: otherwise they
     // stay where they are (no scan, no copy)
     const bool with_dead = deaths > 0 || tomb_in > 0;
-    if ((long long)c->n_tomb + deaths + tomb_in > c->cap)
-        return c->fail("strip capacity exceeded by tombstones (dead particles that lie in this strip): raise "
-                       "PARSIM_CAPACITY_PCT");
+    if ((long long)c->n_tomb + deaths + tomb_in > c->cap) {
+        const char *what = "strip capacity exceeded by tombstones (dead particles that lie in this strip): raise "
+                           "PARSIM_CAPACITY_PCT";
+        if (c->nranks == 1) return c->fail(what);
+        exchange_soft_fail(c, what);
+        c->n_tomb = 0;  // the tombstone lists are garbage from here on; the run ends at the next exchange
+    }
     if (merge_step(c, n_src, n_src - deaths, with_dead)) return 1;
     c->n_tomb += deaths + tomb_in;  // upper bound; exact total is dead_start[ncells]
     if (c->nranks == 1) {
@@ -524,6 +513,7 @@ int rank_run(Rank *c, long n_steps) {
         c->n_tomb = c->h_ctr->grave_count;
     }
     c->deferred = false;
+    if (c->nranks > 1 && n_steps > 0 && exchange_final_check(c)) return 1;
     PS_CUDA(c, cudaStreamSynchronize(c->stream));
     float ms = 0;
     PS_CUDA(c, cudaEventElapsedTime(&ms, c->run_a, c->run_b));

@@ -173,6 +173,22 @@ def test_group_upload_paths_agree(monkeypatch):
         assert np.array_equal(res[0][1][k], res[1][1][k]), k
 
 
+@pytest.mark.timeout(180)
+@pytest.mark.parametrize("transport", TRANSPORTS)
+def test_a_failing_strip_takes_the_others_with_it(transport, monkeypatch):
+    """A strip whose migrant buffer overflows (forced: one record of capacity) reports it through
+    the exchanged headers, so EVERY strip leaves the step with an error -- nobody is left waiting in
+    a collective for a strip that gave up (the reference's MPI variant simply aborts the job)."""
+    from particlesimulation_b200.simulation import ParsimError
+    pick_transport(transport, 2, monkeypatch)
+    monkeypatch.setenv("PARSIM_CAPACITY_PCT", "400")
+    monkeypatch.setenv("PARSIM_MIG_CAP", "1")
+    g = ParticleSimulation(1, 10, 100, 100000, n_gpus=2)
+    with pytest.raises(ParsimError, match="error code 3|overflow"):
+        g.simulate(3)
+    g.close()
+
+
 def test_cli_balanced_strips_match_single_gpu():
     if ngpu() < 1:
         pytest.skip("needs a GPU")

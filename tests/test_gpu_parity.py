@@ -223,35 +223,6 @@ def test_collision_search_paths_agree(case, monkeypatch):
         assert np.array_equal(res["pairs"][1][k], res["grid"][1][k]), k
 
 
-@pytest.mark.parametrize("case", [(1, 10, 100, 100000, 4), (7, 30, 300, 2000000, 3), (5, 1, 20, 200000, 2), (-7, 10, 50, 200000, 4),
-                                  (3, 100, 300, 1500000, 3)], ids=lambda c: " ".join(map(str, c)))
-def test_centre_of_mass_lanes_do_not_change_the_sums(case, monkeypatch):
-    """The summation order of a cell's centre of mass is fixed by the global initial density (W
-    lanes); the lanes that do the work follow the current occupancy (k_com_v, P <= W).  Forcing
-    P = 4, 8, 16, 32 must give the same bits -- centres of mass after stage 0 and the whole run."""
-    seed, side, nc, n, steps = case
-    res = {}
-    for lanes in ("auto", "4", "8", "16", "32"):
-        if lanes == "auto":
-            monkeypatch.delenv("PARSIM_COM_LANES", raising=False)
-        else:
-            monkeypatch.setenv("PARSIM_COM_LANES", lanes)
-        g = ParticleSimulation(seed, side, nc, n)
-        g.debug_stage(0)
-        cells = g.dump_cells()
-        for st in (1, 2, 3):
-            g.debug_stage(st)
-        g.simulate(steps)
-        res[lanes] = (cells, g.result(), g.dump())
-        g.close()
-    for lanes in ("4", "8", "16", "32"):
-        for a, b in zip(res[lanes][0], res["auto"][0]):
-            assert np.array_equal(a, b), lanes
-        assert res[lanes][1] == res["auto"][1], lanes
-        for k in ("x", "y", "vx", "vy", "m", "alive"):
-            assert np.array_equal(res[lanes][2][k], res["auto"][2][k]), (lanes, k)
-
-
 FORCE_VARIANTS = [0, 1, 2, 3, 4, 5, 6, 10, 11]  # = what rank_create accepts (csrc/parsim_rank.cu)
 
 
