@@ -13,6 +13,7 @@
 namespace parsim {
 
 static int device_scan(Rank *c, const int *in, int N, int *out, int *total2);  // parsim_step.inl
+static int sort_piece(Rank *c, int first, int cnt, int piece);                  // parsim_step.inl
 
 template <typename T>
 static int dev_alloc(Rank *c, T **p, size_t count, bool zero = false) {
@@ -189,6 +190,8 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     c->defer_steps = c->use_graphs = n_part <= 4000000;  // above that a step is milliseconds of kernels: nothing to gain
     if (const char *e = getenv("PARSIM_SYNC_STEPS")) c->defer_steps = atoi(e) == 0;
     if (const char *e = getenv("PARSIM_GRAPHS")) c->use_graphs = atoi(e) != 0;
+    if (const char *e = getenv("PARSIM_PIECE_SORT")) c->opt_piece_sort = atoi(e) != 0;
+    if (const char *e = getenv("PARSIM_STAGE_PIECE")) c->stage_piece_len = std::max(64, atoi(e));
     PS_CUDA(c, cudaEventCreate(&c->run_a));
     PS_CUDA(c, cudaEventCreate(&c->run_b));
     if (nranks > 1) {
@@ -211,6 +214,7 @@ void rank_destroy(Rank *c) {
                     c->mv_head, c->dm_head, c->mv_next, c->fate, c->grave_pos, c->grave_vel, c->grave_id,
                     c->grave_cell, c->d_ctr, c->d_p0, c->d_found, c->guest_src, c->posf, c->rec0,
                     c->big_cells, c->d_big_count, c->huge_items, c->move_big_list, c->d_move_big_count, c->arr_cnt, c->arr_rec,
+                    c->cs_pieces, c->d_piece_first,
                     c->stage_ids[0], c->stage_ids[1], c->stage[0][0], c->stage[0][1], c->stage[0][2],
                     c->stage[0][3], c->stage[0][4], c->stage[1][0], c->stage[1][1], c->stage[1][2],
                     c->stage[1][3], c->stage[1][4]};
@@ -238,6 +242,7 @@ static int reset_state(Rank *c) {
     c->n_uploaded = 0;
     const size_t C = (size_t)c->g.ncells;
     c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->next_stage = 0;
+    c->piece_sorted = false;
     c->n_tomb = 0; c->n_grave = 0; c->steps_done = 0; c->collisions_total = 0;
     c->have_newcell = c->have_flags = false;
     c->pos_latest = c->pos_cur;
@@ -263,18 +268,29 @@ int rank_upload_begin(Rank *c) {
     if (reset_state(c)) return 1;
     c->uploading = true;
     c->stage_pieces = 0;
+    c->piece_first.clear();
+    c->pieces_ok = false;
+    if (c->nranks == 1 && c->opt_piece_sort) {
+        // room for the pieces' cell_start tables (at most 64 pieces and 1 GiB: else the full sort at step 0)
+        const long long pieces = std::min<long long>(64, (c->n_part + c->stage_piece_len - 1) / c->stage_piece_len + 1);
+        const size_t need = (size_t)pieces * ((size_t)c->g.ncells + 1);
+        if (!c->cs_pieces && need * sizeof(int) <= ((size_t)1 << 30)) {
+            PS_ALLOC(c, c->cs_pieces, need, false);
+            PS_ALLOC(c, c->d_piece_first, 64, false);
+            c->cs_pieces_cap = (int)pieces;
+        }
+        c->pieces_ok = c->cs_pieces != nullptr;
+    }
     return 0;
 }
 
 // Staging passes of 8 Mi particles (5 x 64 MiB per set).  The host->device copies of a pass run
 // on copy_stream into one staging set while the ingest kernels (on the step stream) interleave the
 // previous pass out of the other set, so the copy engine never waits for a kernel.
-static const long long kStagePiece = 1 << 23;
-
 int rank_stage_alloc(Rank *c) {
     if (c->stage[0][0]) return 0;
     PS_CUDA(c, cudaSetDevice(c->device));
-    c->stage_cap = (int)std::min<long long>(kStagePiece, c->n_part);
+    c->stage_cap = (int)std::min<long long>(c->stage_piece_len, c->n_part);
     for (int b = 0; b < 2; b++) {
         for (int k = 0; k < 5; k++) PS_ALLOC(c, c->stage[b][k], c->stage_cap, false);
         PS_ALLOC(c, c->stage_ids[b], c->stage_cap, false);
@@ -333,6 +349,15 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
         if (rank_ingest_piece(c, id_base + off, ids ? c->stage_ids[b] : nullptr, cnt, st)) return 1;
         PS_CUDA(c, cudaEventRecord(c->ev_ingested[b], c->stream));
         c->stage_pieces++;
+        // sort the piece now, under the shadow of the next piece's copy (parsim_step.inl sort_piece):
+        // only while the pieces arrive in id order, one after the other, and their tables fit
+        if (c->pieces_ok && (ids || id_base + off != c->n_uploaded + off)) c->pieces_ok = false;
+        if (c->pieces_ok && (int)c->piece_first.size() >= c->cs_pieces_cap) c->pieces_ok = false;
+        if (c->pieces_ok) {
+            const int piece = (int)c->piece_first.size();
+            c->piece_first.push_back((int)(id_base + off));
+            if (sort_piece(c, (int)(id_base + off), cnt, piece)) return 1;
+        }
     }
     // the caller's arrays are free again when this returns ("they are copied"); the ingest kernels
     // may still be running -- parsim_upload_end waits for them
@@ -355,6 +380,7 @@ int rank_upload_end(Rank *c) {
     else c->n_alive = (int)c->n_part;
     c->pos_latest = c->pos_cur;
     c->n0 = c->n_alive;
+    c->piece_sorted = c->pieces_ok && !c->piece_first.empty() && c->n_uploaded == c->n_part;
     k_set_int<<<1, 1, 0, c->stream>>>(&c->d_ctr->n_next, c->n_alive);  // the kernels' particle count
     c->slots_id_ordered = true;
     if (c->nranks > 1 && c->n_alive > 1) {  // explicit-id uploads may come in any order

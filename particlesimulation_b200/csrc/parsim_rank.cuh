@@ -163,6 +163,13 @@ struct Rank {
     bool slots_id_ordered = true;  // slot order == id order (single strip); else ids are sorted too
     bool opt_keep_initial = false; // accepted for compatibility: reset is always possible now
     bool uploading = false;
+    // pieces of the current upload that were sorted as they arrived (single strip, ids in order)
+    bool pieces_ok = false, piece_sorted = false, opt_piece_sort = true;
+    std::vector<int> piece_first;         // first record of every sorted piece
+    int *cs_pieces = nullptr;             // per piece: cell_start[ncells + 1] relative to the piece
+    int *d_piece_first = nullptr;
+    int cs_pieces_cap = 0;                // pieces cs_pieces has room for
+    long long stage_piece_len = 1 << 23;  // particles per staging pass (PARSIM_STAGE_PIECE, tests)
 
     // multi-strip exchange (parsim_exchange.cuh)
     NcclComm comm;

@@ -186,4 +186,49 @@ k_sort_gather(int n, int ncells, const unsigned *__restrict__ keys, const int *_
         for (int k = c + 1; k <= ncells; k++) cell_start[k] = n;
 }
 
+// ---------------------------------------------------------------------------------------
+// Upload pieces sorted under the copy's shadow (parsim_step.inl sort_piece / merge_pieces): every
+// piece of the upload is already in (cell, id) order inside itself, pieces hold increasing id
+// ranges, so the (cell, id) order of the whole is, per cell, piece 0's segment, then piece 1's, ...
+// cs_pieces[p * (ncells + 1) + c] = start of cell c inside piece p (relative to piece_first[p]).
+__global__ void k_piece_counts(int ncells, int npieces, const int *__restrict__ cs_pieces, int *__restrict__ count) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= ncells) return;
+    int tot = 0;
+    for (int p = 0; p < npieces; p++) {
+        const int *cs = cs_pieces + (size_t)p * (ncells + 1);
+        tot += cs[c + 1] - cs[c];
+    }
+    count[c] = tot;
+}
+
+template <int LANES>
+__global__ void __launch_bounds__(kThreads, 8)
+k_merge_pieces(int ncells, int npieces, const int *__restrict__ piece_first, const int *__restrict__ cs_pieces,
+               const int *__restrict__ cs_new, const double2 *__restrict__ pos_in, const double2 *__restrict__ vel_in,
+               const double *__restrict__ m_in, const unsigned *__restrict__ id_in, double2 *__restrict__ pos_out,
+               double2 *__restrict__ vel_out, double *__restrict__ m_out, unsigned *__restrict__ id_out,
+               int *__restrict__ cell_out) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    const int c = t / LANES, lane = t % LANES;
+    if (c >= ncells) return;
+    int dst = cs_new[c];
+    for (int p = 0; p < npieces; p++) {
+        const int *cs = cs_pieces + (size_t)p * (ncells + 1);
+        const int s = cs[c], e = cs[c + 1], base = piece_first[p];
+        for (int k = s + lane; k < e; k += LANES) {
+            const int i = base + k, o = dst + (k - s);
+            const double2 pp = pos_in[i], vv = vel_in[i];
+            const double mm = m_in[i];
+            const unsigned id = id_in[i];
+            pos_out[o] = pp;
+            vel_out[o] = vv;
+            m_out[o] = mm;
+            id_out[o] = id;
+            cell_out[o] = c;
+        }
+        dst += e - s;
+    }
+}
+
 }  // namespace parsim

@@ -99,6 +99,71 @@ static int sort_initial(Rank *c) {
     return 0;
 }
 
+// ---- binning under the upload's shadow (host-buffer callers) ----------------------------------
+// A single strip that receives its particles piece by piece in id order (parsim_upload) sorts every
+// piece into (cell, id) order as soon as it is ingested -- on the step stream, while the copy engine
+// brings the next piece over PCIe (6 ms per 8 Mi particles against 0.7 ms of sorting) -- and the
+// first timestep only MERGES the pieces: per cell, the pieces' segments one after the other.  Same
+// layout as sort_initial, bit for bit (tests/test_gpu_parity.py::test_upload_pieces_match_full_sort);
+// parsim_reset and device-side init keep the full sort of the records.
+static int sort_piece(Rank *c, int first, int cnt, int piece) {
+    if (cnt <= 0) return 0;
+    const Geom &g = c->g;
+    unsigned *keyA = (unsigned *)c->newcell + first, *keyB = (unsigned *)c->partner + first;
+    int *srcA = c->arr_next + first, *srcB = c->mv_next + first;
+    const int cell_bits = bits_for((unsigned long long)std::max(g.ncells - 1, 1));
+    PS_LAUNCH(c, K_BIN_KEYS, 36.0 * cnt, "k_sort_cell_of",
+              k_sort_cell_of<<<grid_for(cnt), kThreads, 0, c->stream>>>(g, cnt, c->rec0 + first, keyA));
+    if (sort_passes(c, cnt, cell_bits, keyA, keyB, srcA, srcB, true)) return 1;
+    PS_LAUNCH(c, K_SORT_GATHER, 120.0 * cnt + 4.0 * g.ncells, "k_sort_gather",
+              k_sort_gather<<<grid_for(cnt), kThreads, 0, c->stream>>>(
+                  cnt, g.ncells, keyA, srcA, c->rec0 + first, c->pos_alt + first, c->vel_alt + first, c->m_alt + first,
+                  c->id_alt + first, c->cell_alt + first, c->cs_pieces + (size_t)piece * ((size_t)g.ncells + 1)));
+    return 0;
+}
+
+static int merge_pieces(Rank *c) {
+    const Geom &g = c->g;
+    const int P = (int)c->piece_first.size();
+    if (P == 1) {  // one piece: it IS the sorted state
+        PS_CUDA(c, cudaMemcpyAsync(c->cs_alt, c->cs_pieces, sizeof(int) * ((size_t)g.ncells + 1), cudaMemcpyDeviceToDevice,
+                                   c->stream));
+        std::swap(c->cs_cur, c->cs_alt);
+    } else {
+        PS_CUDA(c, cudaMemcpyAsync(c->d_piece_first, c->piece_first.data(), sizeof(int) * P, cudaMemcpyHostToDevice, c->stream));
+        PS_LAUNCH(c, K_SORT_PASS, 8.0 * P * g.ncells, "k_piece_counts",
+                  k_piece_counts<<<grid_for(g.ncells), kThreads, 0, c->stream>>>(g.ncells, P, c->cs_pieces, c->count));
+        if (device_scan(c, c->count, g.ncells, c->cs_alt, nullptr)) return 1;
+        PS_CUDA(c, cudaMemsetAsync(c->count, 0, sizeof(int) * (size_t)g.ncells, c->stream));  // the step loop expects zeros
+        const double occ = (double)c->n_alive / std::max(1, g.ncells) / P;
+#define PS_MERGE(L)                                                                                                  \
+    k_merge_pieces<L><<<grid_for((long long)g.ncells * L), kThreads, 0, c->stream>>>(                                \
+        g.ncells, P, c->d_piece_first, c->cs_pieces, c->cs_alt, c->pos_alt, c->vel_alt, c->m_alt, c->id_alt, c->pos_cur, \
+        c->vel_cur, c->m_cur, c->id_cur, c->cell_cur)
+        PS_LAUNCH(c, K_SORT_GATHER, 92.0 * c->n_alive + 8.0 * P * g.ncells, "k_merge_pieces", {
+            if (occ <= 6) PS_MERGE(4); else if (occ <= 12) PS_MERGE(8); else if (occ <= 24) PS_MERGE(16); else PS_MERGE(32);
+        });
+#undef PS_MERGE
+        std::swap(c->cs_cur, c->cs_alt);
+        return 0;  // the merged state is already in the *_cur arrays
+    }
+    std::swap(c->pos_cur, c->pos_alt);
+    std::swap(c->vel_cur, c->vel_alt);
+    std::swap(c->m_cur, c->m_alt);
+    std::swap(c->id_cur, c->id_alt);
+    std::swap(c->cell_cur, c->cell_alt);
+    return 0;
+}
+
+// step-0 binning: merge of the pre-sorted upload pieces when there are any, else the full sort
+static int bin_initial(Rank *c) {
+    if (c->piece_sorted && !c->piece_first.empty()) {
+        c->piece_sorted = false;  // the piece arrays are consumed (they are the step loop's scratch)
+        return merge_pieces(c);
+    }
+    return sort_initial(c);
+}
+
 template <int LANES>
 static void launch_move(Rank *c, const MoveArgs &a, bool big) {
     long long threads = (long long)c->g.ncells * LANES;
@@ -190,7 +255,7 @@ static void launch_com_any(Rank *c) {
 static int stage_bin_com(Rank *c) {
     const Geom &g = c->g;
     if (!c->sorted) {
-        if (sort_initial(c)) return 1;
+        if (bin_initial(c)) return 1;
         c->sorted = true;
     }
     k_step_reset<<<1, 1, 0, c->stream>>>(c->d_ctr, c->d_big_count, c->d_move_big_count);  // work-list counters of this step
@@ -376,7 +441,7 @@ static int stage_collide(Rank *c) {
 int rank_ensure_sorted(Rank *c) {
     PS_CUDA(c, cudaSetDevice(c->device));
     if (c->sorted || c->uploading) return 0;
-    if (sort_initial(c)) return 1;
+    if (bin_initial(c)) return 1;
     c->sorted = true;
     c->pos_latest = c->pos_cur;
     return 0;

@@ -287,6 +287,40 @@ def test_deferred_steps_match_synchronised_steps(case, monkeypatch):
             assert np.array_equal(res[mode][1][k], res["sync"][1][k]), (mode, k)
 
 
+@pytest.mark.parametrize("case", [(1, 10, 100, 100000, 4, 20000), (5, 1, 20, 200000, 3, 30000), (-7, 10, 50, 20000, 5, 3000),
+                                  (3, 1, 2, 200, 4, 64), (1, 2, 3, 10, 3, 64), (7, 30, 300, 2000000, 2, 1 << 19)],
+                         ids=lambda c: " ".join(map(str, c)))
+def test_upload_pieces_match_full_sort(case, monkeypatch):
+    """Host-buffer uploads are sorted piece by piece while the next piece is still on its way over
+    PCIe, and the first timestep only merges the pieces (csrc/parsim_step.inl sort_piece /
+    merge_pieces).  The layout must be the one the full step-0 sort of the records gives
+    (PARSIM_PIECE_SORT=0, and what parsim_reset and the device-side init use): same cell lists,
+    same bits after the run -- with several pieces, with one piece, and after a reset."""
+    seed, side, nc, n, steps, piece = case
+    monkeypatch.setenv("PARSIM_STAGE_PIECE", str(piece))
+    res = {}
+    for mode in ("pieces", "full"):
+        monkeypatch.setenv("PARSIM_PIECE_SORT", "1" if mode == "pieces" else "0")
+        g = ParticleSimulation(seed, side, nc, n, options={"keep_initial": 1})
+        g.debug_stage(0)
+        first = g.dump()
+        for st in (1, 2, 3):
+            g.debug_stage(st)
+        g.simulate(steps)
+        res[mode] = (first, g.result(), g.dump())
+        if mode == "pieces":  # the reset path restarts from the records, not from the pieces
+            g.reset()
+            g.simulate(steps + 1)
+            res["reset"] = (first, g.result(), g.dump())
+        g.close()
+    for mode in ("pieces", "reset"):
+        assert res[mode][1] == res["full"][1], mode
+        for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+            assert np.array_equal(res[mode][2][k], res["full"][2][k]), (mode, k)
+    for k in ("x", "y", "vx", "vy", "m", "cell", "list_rank"):
+        assert np.array_equal(res["pieces"][0][k], res["full"][0][k]), k
+
+
 def test_close_encounters_throw_particles_far():
     """Two particles a few 1e-6 apart fly tens of cells in one step; the result must still be the
     reference's (alive flags and collision count exact, positions to 1e-9 of the box side)."""
