@@ -181,6 +181,31 @@ int parsim_set_option(parsim_ctx *ctx, const char *name, long long value);
  * want to record their own events. */
 void *parsim_stream(parsim_ctx *ctx);
 
+/* Centre of mass of every cell (the result of stage 0: cell masses and mass-weighted mean
+ * positions, as parsim_debug_stage(ctx, 0) + parsim_dump_cells give them) WITHOUT ANY ALLOCATION,
+ * for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it.  This entry point has no counterpart in the
+ * reference.
+ *   d_x, d_y, d_m      DEVICE pointers, n_part doubles each (particle i = index i, as parsim_upload)
+ *   d_mx, d_my, d_mass DEVICE pointers, ncside * ncside doubles each (cell = row * ncside + column;
+ *                      an empty cell gets 0, 0, 0)
+ *   stream             cudaStream_t to launch on (NULL = the legacy default stream); the call is
+ *                      stream-ordered and returns without synchronising
+ * All pointers must belong to the CURRENT device.  The binning scratch is a fixed device array
+ * inside the library (about 4 MiB, held by every GPU that loads the library until the process
+ * exits), hence the limits: n_part <= PARSIM_STATIC_MAX_PARTICLES and ncside * ncside <=
+ * PARSIM_STATIC_MAX_CELLS; anything larger is rejected (returns 1, text in parsim_last_error(NULL))
+ * -- use a parsim_ctx there.  No cudaMalloc / cudaFree / allocating library routine is called.
+ * Every call on a device shares the array: calls that overlap on the GPU (two streams, two
+ * threads) race -- serialise them.  The first call on a device looks the array's address up
+ * (cudaGetSymbolAddress); make one call (n_part = 0 will do) before starting a stream capture.
+ * Results equal the context path's bit for bit (same per-cell order, same summation tree). */
+#define PARSIM_STATIC_MAX_PARTICLES 262144
+#define PARSIM_STATIC_MAX_CELLS 262144
+int parsim_cell_com_static(double side, long ncside, long long n_part, const double *d_x,
+                           const double *d_y, const double *d_m, double *d_mx, double *d_my,
+                           double *d_mass, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -65,6 +65,8 @@ SIGNATURES = {
     "parsim_stats_reset": (C.c_int, [_ctx]),
     "parsim_set_option": (C.c_int, [_ctx, C.c_char_p, C.c_longlong]),
     "parsim_stream": (C.c_void_p, [_ctx]),
+    "parsim_cell_com_static": (C.c_int, [C.c_double, C.c_long, C.c_longlong, C.c_void_p, C.c_void_p, C.c_void_p,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
 }
 
 _lib = None

@@ -2,3 +2,4 @@
 // headers, so the host-side files are compiled together).
 #include "parsim_rank.cu"
 #include "parsim_capi.cu"
+#include "parsim_noalloc.cu"
