@@ -476,6 +476,17 @@ __global__ void __launch_bounds__(kThreads, LANES <= 8 ? 8 : PS_COM_MINB) k_com(
     if (force_pairs) block_add_u64(pairs, force_pairs);  // stats only (uniform branch)
 }
 
+// stats only: the ordered pairs of the force phase, when k_com (which counts them) did not run
+__global__ void k_count_pairs(int ncells, const int *__restrict__ cell_start, unsigned long long *force_pairs) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    unsigned long long pairs = 0;
+    if (c < ncells) {
+        const unsigned long long a = (unsigned long long)(cell_start[c + 1] - cell_start[c]);
+        pairs = a * (a - 1);
+    }
+    block_add_u64(pairs, force_pairs);
+}
+
 // Single strip: the ghost rows are the strip's own last / first row (periodic wrap,
 // serial/parsim.cpp:332-333).  Multi-strip runs fill them over NCCL instead.
 __global__ void k_ghost_wrap(Geom g, double2 *com_xy, double *com_m) {

@@ -182,12 +182,20 @@ struct MoveArgs {
     unsigned *dead_new;
     int *big_list, *big_count;           // cells with more than big_min old entries: left to k_move_big
     int big_min;
+    double2 *com_xy;                     // COM variants only: next step's centres of mass, already
+    double *com_m;                       // offset past the ghost row (index = local cell)
 };
 
 // BIG: leave cells (or tombstone lists) above a.big_min entries to k_move_big.  The test costs the
 // ordinary case about 5 % (this kernel is a chain of dependent loads per cell), so the host asks
 // for it only when the cells are huge on average.
-template <int LANES, bool BIG>
+//
+// COM: the lane group also leaves the cell's centre of mass for the NEXT step (k_com's job, saved
+// with its 24 B per particle of DRAM reads): it reads its own freshly written list back from L2
+// and sums it in exactly k_com<LANES>'s order -- lane l takes entries l, l + LANES, ... with the
+// same fma chain, then the same xor tree and divisions -- so the result is k_com's bit for bit.
+// The host uses it only when LANES is the context's com_lanes (the lane count fixes the order).
+template <int LANES, bool BIG, bool COM>
 __device__ __forceinline__ void move_cell(const Geom &g, const MoveArgs &a, int c) {
     auto tile = cg::tiled_partition<LANES>(cg::this_thread_block());
     const int lane = tile.thread_rank();
@@ -307,16 +315,43 @@ __device__ __forceinline__ void move_cell(const Geom &g, const MoveArgs &a, int 
         if (a.arr_cnt) a.arr_cnt[c] = 0;
         a.count[c] = 0;
     }
+    if (COM) {
+        // tile.sync() above ordered the lanes' stores before these loads; .cg reads L2, where the
+        // stores went (lines shared with a neighbouring cell may be stale in L1 for ITS part only)
+        const int ne = a.cs_new[c + 1];
+        double M = 0, Mx = 0, My = 0;
+        for (int k = ns + lane; k < ne; k += LANES) {
+            const double mv = __ldcg(a.m_out + k);
+            const double2 p = __ldcg(a.pos_out + k);
+            M += mv;
+            Mx = fma(mv, p.x, Mx);
+            My = fma(mv, p.y, My);
+        }
+#pragma unroll
+        for (int o = LANES / 2; o > 0; o >>= 1) {
+            M += tile.shfl_xor(M, o);
+            Mx += tile.shfl_xor(Mx, o);
+            My += tile.shfl_xor(My, o);
+        }
+        // lanes 0 and 1 divide one component each (an FP64 division is ~40 instructions)
+        double val = 0.0;
+        if (lane < 2 && M > 0) val = (lane ? My : Mx) / M;
+        const double other = tile.shfl_down(val, 1);
+        if (lane == 0) {
+            a.com_xy[c] = make_double2(val, other);
+            a.com_m[c] = M;
+        }
+    }
 }
 
-template <int LANES, bool BIG>
+template <int LANES, bool BIG, bool COM>
 __global__ void __launch_bounds__(kThreads, 8) k_move(Geom g, MoveArgs a) {
     const int c = (blockIdx.x * blockDim.x + threadIdx.x) / LANES;
     if (c >= g.ncells) return;  // whole tiles leave together
-    move_cell<LANES, BIG>(g, a, c);
+    move_cell<LANES, BIG, COM>(g, a, c);
 }
 
-__device__ __noinline__ void move_cell_lanes32(const Geom &g, const MoveArgs &a, int c) { move_cell<32, false>(g, a, c); }
+__device__ __noinline__ void move_cell_lanes32(const Geom &g, const MoveArgs &a, int c) { move_cell<32, false, false>(g, a, c); }
 
 // Huge cells (tens of thousands of entries, BASELINE config 5): one BLOCK per cell.  The arrivals
 // (<= kMoveBigArr, else the block falls back to a single lane group's generic loop) are sorted by

@@ -58,6 +58,13 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     PS_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     PS_CUDA(c, cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
     c->bus = nranks > 1 ? bus : nullptr;
+    if (const char *e = getenv("PARSIM_L2_FETCH")) {  // experiment: L2 fetch granularity hint (32 / 64 / 128 bytes)
+        size_t before = 0, after = 0;
+        cudaDeviceGetLimit(&before, cudaLimitMaxL2FetchGranularity);
+        cudaError_t rc = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));
+        cudaDeviceGetLimit(&after, cudaLimitMaxL2FetchGranularity);
+        fprintf(stderr, "parsim: L2 fetch granularity %zu -> %zu (%s)\n", before, after, cudaGetErrorString(rc));
+    }
 
     Geom &g = c->g;
     g.side = side;
@@ -191,6 +198,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     if (const char *e = getenv("PARSIM_SYNC_STEPS")) c->defer_steps = atoi(e) == 0;
     if (const char *e = getenv("PARSIM_GRAPHS")) c->use_graphs = atoi(e) != 0;
     if (const char *e = getenv("PARSIM_PIECE_SORT")) c->opt_piece_sort = atoi(e) != 0;
+    if (const char *e = getenv("PARSIM_FUSE_COM")) c->fuse_com = atoi(e) != 0;
     if (const char *e = getenv("PARSIM_STAGE_PIECE")) c->stage_piece_len = std::max(64, atoi(e));
     PS_CUDA(c, cudaEventCreate(&c->run_a));
     PS_CUDA(c, cudaEventCreate(&c->run_b));
@@ -241,7 +249,7 @@ void rank_destroy(Rank *c) {
 static int reset_state(Rank *c) {
     c->n_uploaded = 0;
     const size_t C = (size_t)c->g.ncells;
-    c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->next_stage = 0;
+    c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->com_valid = false; c->next_stage = 0;
     c->piece_sorted = false;
     c->n_tomb = 0; c->n_grave = 0; c->steps_done = 0; c->collisions_total = 0;
     c->have_newcell = c->have_flags = false;

@@ -89,6 +89,8 @@ struct Rank {
     int n_alive = 0;
     int n_guest = 0;
     bool sorted = false;   // cell order valid for the coming step
+    bool com_valid = false;  // the merge of the last step already left this step's centres of mass (k_move<.., COM>)
+    bool fuse_com = true;    // PARSIM_FUSE_COM=0: always k_com (A/B)
     int next_stage = 0;    // debug stepping
     double2 *pos_cur = nullptr, *pos_alt = nullptr;  // cur: pre-move (sorted); alt: post-move
     double2 *vel_cur = nullptr, *vel_alt = nullptr;
@@ -141,7 +143,7 @@ struct Rank {
     long long ring_pos = 0;
     // Small problems are launch-bound (BASELINE configs[1]: about 20 launches per 100 us step): a
     // deferred step is captured once per (buffer parity, kernel choice) as a CUDA graph and replayed.
-    struct StepGraph { unsigned long long key; int n_cap; cudaGraphExec_t exec; };
+    struct StepGraph { unsigned long long key; int n_cap; cudaGraphExec_t exec; bool com_after; };
     std::vector<StepGraph> graphs;
     bool use_graphs = false, capturing = false;
     double2 *d_p0 = nullptr;

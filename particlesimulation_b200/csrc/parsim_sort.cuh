@@ -202,8 +202,10 @@ __global__ void k_piece_counts(int ncells, int npieces, const int *__restrict__ 
     count[c] = tot;
 }
 
-template <int LANES>
-__global__ void __launch_bounds__(kThreads, 8)
+// MAXP > 0: at most MAXP pieces; all segment bounds of the cell are loaded before the first copy
+// (2 * npieces independent loads in flight instead of a dependent pair per piece).
+template <int LANES, int MAXP>
+__global__ void __launch_bounds__(kThreads, MAXP > 0 ? 5 : 8)
 k_merge_pieces(int ncells, int npieces, const int *__restrict__ piece_first, const int *__restrict__ cs_pieces,
                const int *__restrict__ cs_new, const double2 *__restrict__ pos_in, const double2 *__restrict__ vel_in,
                const double *__restrict__ m_in, const unsigned *__restrict__ id_in, double2 *__restrict__ pos_out,
@@ -213,19 +215,38 @@ k_merge_pieces(int ncells, int npieces, const int *__restrict__ piece_first, con
     const int c = t / LANES, lane = t % LANES;
     if (c >= ncells) return;
     int dst = cs_new[c];
-    for (int p = 0; p < npieces; p++) {
-        const int *cs = cs_pieces + (size_t)p * (ncells + 1);
-        const int s = cs[c], e = cs[c + 1], base = piece_first[p];
-        for (int k = s + lane; k < e; k += LANES) {
-            const int i = base + k, o = dst + (k - s);
-            const double2 pp = pos_in[i], vv = vel_in[i];
-            const double mm = m_in[i];
-            const unsigned id = id_in[i];
-            pos_out[o] = pp;
-            vel_out[o] = vv;
-            m_out[o] = mm;
-            id_out[o] = id;
-            cell_out[o] = c;
+    int ss[MAXP > 0 ? MAXP : 1], ee[MAXP > 0 ? MAXP : 1];
+    if (MAXP > 0) {
+#pragma unroll
+        for (int p = 0; p < MAXP; p++) {
+            const int *cs = cs_pieces + (size_t)p * (ncells + 1);
+            ss[p] = p < npieces ? cs[c] : 0;
+            ee[p] = p < npieces ? cs[c + 1] : 0;
+        }
+    }
+#pragma unroll
+    for (int p = 0; p < (MAXP > 0 ? MAXP : npieces); p++) {
+        if (MAXP > 0 && p >= npieces) break;
+        int s, e;
+        if (MAXP > 0) {
+            s = ss[p]; e = ee[p];
+        } else {
+            const int *cs = cs_pieces + (size_t)p * (ncells + 1);
+            s = cs[c]; e = cs[c + 1];
+        }
+        if (e > s) {
+            const int base = piece_first[p];
+            for (int k = s + lane; k < e; k += LANES) {
+                const int i = base + k, o = dst + (k - s);
+                const double2 pp = pos_in[i], vv = vel_in[i];
+                const double mm = m_in[i];
+                const unsigned id = id_in[i];
+                pos_out[o] = pp;
+                vel_out[o] = vv;
+                m_out[o] = mm;
+                id_out[o] = id;
+                cell_out[o] = c;
+            }
         }
         dst += e - s;
     }

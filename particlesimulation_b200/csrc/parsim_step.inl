@@ -136,14 +136,22 @@ static int merge_pieces(Rank *c) {
         if (device_scan(c, c->count, g.ncells, c->cs_alt, nullptr)) return 1;
         PS_CUDA(c, cudaMemsetAsync(c->count, 0, sizeof(int) * (size_t)g.ncells, c->stream));  // the step loop expects zeros
         const double occ = (double)c->n_alive / std::max(1, g.ncells) / P;
-#define PS_MERGE(L)                                                                                                  \
-    k_merge_pieces<L><<<grid_for((long long)g.ncells * L), kThreads, 0, c->stream>>>(                                \
-        g.ncells, P, c->d_piece_first, c->cs_pieces, c->cs_alt, c->pos_alt, c->vel_alt, c->m_alt, c->id_alt, c->pos_cur, \
-        c->vel_cur, c->m_cur, c->id_cur, c->cell_cur)
+        static const bool preload = !getenv("PARSIM_MERGE_PRELOAD") || atoi(getenv("PARSIM_MERGE_PRELOAD")) != 0;  // A/B
+#define PS_MERGE_ARGS                                                                                                \
+    g.ncells, P, c->d_piece_first, c->cs_pieces, c->cs_alt, c->pos_alt, c->vel_alt, c->m_alt, c->id_alt, c->pos_cur, \
+        c->vel_cur, c->m_cur, c->id_cur, c->cell_cur
+#define PS_MERGE(L)                                                                                          \
+    do {                                                                                                     \
+        if (P <= 16 && preload)                                                                              \
+            k_merge_pieces<L, 16><<<grid_for((long long)g.ncells * L), kThreads, 0, c->stream>>>(PS_MERGE_ARGS); \
+        else                                                                                                 \
+            k_merge_pieces<L, 0><<<grid_for((long long)g.ncells * L), kThreads, 0, c->stream>>>(PS_MERGE_ARGS);  \
+    } while (0)
         PS_LAUNCH(c, K_SORT_GATHER, 92.0 * c->n_alive + 8.0 * P * g.ncells, "k_merge_pieces", {
             if (occ <= 6) PS_MERGE(4); else if (occ <= 12) PS_MERGE(8); else if (occ <= 24) PS_MERGE(16); else PS_MERGE(32);
         });
 #undef PS_MERGE
+#undef PS_MERGE_ARGS
         std::swap(c->cs_cur, c->cs_alt);
         return 0;  // the merged state is already in the *_cur arrays
     }
@@ -165,10 +173,11 @@ static int bin_initial(Rank *c) {
 }
 
 template <int LANES>
-static void launch_move(Rank *c, const MoveArgs &a, bool big) {
+static void launch_move(Rank *c, const MoveArgs &a, bool big, bool com) {
     long long threads = (long long)c->g.ncells * LANES;
-    if (big) k_move<LANES, true><<<grid_for(threads), kThreads, 0, c->stream>>>(c->g, a);
-    else k_move<LANES, false><<<grid_for(threads), kThreads, 0, c->stream>>>(c->g, a);
+    if (big) k_move<LANES, true, false><<<grid_for(threads), kThreads, 0, c->stream>>>(c->g, a);
+    else if (com) k_move<LANES, false, true><<<grid_for(threads), kThreads, 0, c->stream>>>(c->g, a);
+    else k_move<LANES, false, false><<<grid_for(threads), kThreads, 0, c->stream>>>(c->g, a);
 }
 
 // End of step: new cell_start (and tombstone_start) by scan, then the per-cell merge.
@@ -202,22 +211,27 @@ static int merge_step(Rank *c, int n_src, int n_surv, bool with_dead) {
     a.pos_out = c->pos_cur; a.vel_out = c->vel_alt; a.m_out = c->m_alt; a.id_out = c->id_alt;
     a.cell_out = c->cell_alt;
     a.big_list = c->move_big_list; a.big_count = c->d_move_big_count; a.big_min = c->move_big_min;
+    a.com_xy = c->com_xy + g.nc; a.com_m = c->com_m + g.nc;
+    // lanes per cell from the CURRENT occupancy (the layout does not depend on it)
+    const double occ = (double)n_src / std::max(1, g.ncells);
+    const int lanes = occ <= 6 ? 4 : occ <= 12 ? 8 : occ <= 24 ? 16 : 32;
+    // huge cells / tombstone lists on average (BASELINE config 5): those go to k_move_big
+    const bool big = c->move_big_force || occ > 0.125 * c->move_big_min ||
+                     (with_dead && (double)c->n_tomb > 0.125 * c->move_big_min * g.ncells);
+    // the next step's centres of mass come out of the same kernel when its lane groups are the
+    // ones k_com would use (the lane count fixes the summation order); otherwise k_com runs
+    const bool com = c->fuse_com && !big && lanes == c->com_lanes;
     // 1 fate + 4 id read per source entry, 40 read + 48 written per survivor, 8 B per tombstone
-    PS_LAUNCH(c, K_MOVE, 5.0 * n_src + 88.0 * n_surv + 16.0 * g.ncells + (with_dead ? 8.0 * c->n_tomb : 0.0), "k_move", {
-        // lanes per cell from the CURRENT occupancy (the result does not depend on it)
-        const double occ = (double)n_src / std::max(1, g.ncells);
-        const int lanes = occ <= 6 ? 4 : occ <= 12 ? 8 : occ <= 24 ? 16 : 32;
-        // huge cells / tombstone lists on average (BASELINE config 5): those go to k_move_big
-        const bool big = c->move_big_force || occ > 0.125 * c->move_big_min ||
-                         (with_dead && (double)c->n_tomb > 0.125 * c->move_big_min * g.ncells);
+    PS_LAUNCH(c, K_MOVE, 5.0 * n_src + 88.0 * n_surv + (com ? 40.0 : 16.0) * g.ncells + (with_dead ? 8.0 * c->n_tomb : 0.0), "k_move", {
         switch (lanes) {
-        case 4: launch_move<4>(c, a, big); break;
-        case 8: launch_move<8>(c, a, big); break;
-        case 16: launch_move<16>(c, a, big); break;
-        default: launch_move<32>(c, a, big); break;
+        case 4: launch_move<4>(c, a, big, com); break;
+        case 8: launch_move<8>(c, a, big, com); break;
+        case 16: launch_move<16>(c, a, big, com); break;
+        default: launch_move<32>(c, a, big, com); break;
         }
         if (big) k_move_big<<<c->sm_count * 2, kThreads, 0, c->stream>>>(g, a);
     });
+    c->com_valid = com;
     std::swap(c->vel_cur, c->vel_alt);
     std::swap(c->m_cur, c->m_alt);
     std::swap(c->id_cur, c->id_alt);
@@ -259,7 +273,13 @@ static int stage_bin_com(Rank *c) {
         c->sorted = true;
     }
     k_step_reset<<<1, 1, 0, c->stream>>>(c->d_ctr, c->d_big_count, c->d_move_big_count);  // work-list counters of this step
-    PS_LAUNCH(c, K_COM, 24.0 * c->n_alive + 24.0 * g.ncells, "k_com", launch_com_any(c));
+    if (!c->com_valid) {
+        PS_LAUNCH(c, K_COM, 24.0 * c->n_alive + 24.0 * g.ncells, "k_com", launch_com_any(c));
+    } else if (c->opt_stats) {  // k_com also counts the ordered pairs of the force phase
+        k_count_pairs<<<grid_for(g.ncells), kThreads, 0, c->stream>>>(g.ncells, c->cs_cur, &c->d_ctr->force_pairs);
+        if (check_launch(c, "k_count_pairs")) return 1;
+    }
+    c->com_valid = false;  // consumed: the force phase moves the particles
     if (c->nranks == 1) {
         PS_LAUNCH(c, K_GHOST, 96.0 * g.nc, "k_ghost_wrap",
                   k_ghost_wrap<<<grid_for(g.nc), kThreads, 0, c->stream>>>(g, c->com_xy, c->com_m));
@@ -513,10 +533,12 @@ static int deferred_step_graph(Rank *c) {
     const unsigned long long occ_class = (unsigned long long)std::min(63.0, std::max(0.0, 4.0 * log2(occ + 1.0)));
     const unsigned long long key = (c->pos_cur < c->pos_alt ? 1ull : 0) | (c->vel_cur < c->vel_alt ? 2ull : 0) |
                                    (c->dead_start_cur < c->dead_start_alt ? 4ull : 0) |
-                                   ((unsigned long long)(c->ring_pos % kCounterRing) << 3) | (occ_class << 8);
+                                   ((unsigned long long)(c->ring_pos % kCounterRing) << 3) | (occ_class << 8) |
+                                   (c->com_valid ? 1ull << 62 : 0);  // does the step start with k_com?
+    bool com_after = false;
     cudaGraphExec_t exec = nullptr;
     for (auto &sg : c->graphs)
-        if (sg.key == key && sg.n_cap >= c->n_alive) { exec = sg.exec; break; }
+        if (sg.key == key && sg.n_cap >= c->n_alive) { exec = sg.exec; com_after = sg.com_after; break; }
     if (!exec) {
         const int n_cap = c->n_alive;
         PS_CUDA(c, cudaStreamBeginCapture(c->stream, cudaStreamCaptureModeThreadLocal));
@@ -533,7 +555,7 @@ static int deferred_step_graph(Rank *c) {
             cudaGraphExecDestroy(c->graphs.front().exec);
             c->graphs.erase(c->graphs.begin());
         }
-        c->graphs.push_back({key, n_cap, exec});
+        c->graphs.push_back({key, n_cap, exec, c->com_valid});
         PS_CUDA(c, cudaGraphLaunch(exec, c->stream));
         PS_CUDA(c, cudaEventRecord(c->ev_ring[(c->ring_pos - 1) % kCounterRing], c->stream));
         return 0;
@@ -541,6 +563,7 @@ static int deferred_step_graph(Rank *c) {
     PS_CUDA(c, cudaGraphLaunch(exec, c->stream));
     PS_CUDA(c, cudaEventRecord(c->ev_ring[c->ring_pos % kCounterRing], c->stream));
     deferred_host_advance(c);
+    c->com_valid = com_after;  // what the replayed merge left behind
     return 0;
 }
 

@@ -287,6 +287,47 @@ def test_deferred_steps_match_synchronised_steps(case, monkeypatch):
             assert np.array_equal(res[mode][1][k], res["sync"][1][k]), (mode, k)
 
 
+@pytest.mark.parametrize("case", [(1, 10, 100, 100000, 6), (5, 1, 20, 20000, 5), (7, 5, 200, 40000, 5), (-7, 10, 50, 20000, 6),
+                                  (9, 0.3, 4, 3000, 6), (3, 1, 2, 200, 5), (2, 4, 16, 4000, 5)], ids=lambda c: " ".join(map(str, c)))
+def test_centres_of_mass_left_by_the_merge_match_k_com(case, monkeypatch):
+    """The end-of-step merge leaves the NEXT step's centres of mass (k_move<.., COM>, summed in
+    k_com's order from the list it has just written), and stage 0 then skips k_com.
+    PARSIM_FUSE_COM=0 always runs k_com: same bits in every cell at every step, same run, same
+    pair statistics -- stage by stage, through parsim_run (graphs), and with instrumentation on."""
+    seed, side, nc, n, steps = case
+    res = {}
+    for fuse in ("0", "1"):
+        monkeypatch.setenv("PARSIM_FUSE_COM", fuse)
+        g = ParticleSimulation(seed, side, nc, n, options={"keep_initial": 1})
+        cells = []
+        for t in range(steps):
+            g.debug_stage(0)
+            cells.append(g.dump_cells())
+            for st in (1, 2, 3):
+                g.debug_stage(st)
+        staged = (g.result(), g.dump())
+        g.reset()
+        g.simulate(steps)
+        g.simulate(2)
+        run = (g.result(), g.dump())
+        g.reset()
+        g.set_option("stats", 1)
+        g.simulate(steps)
+        st = g.stats()
+        res[fuse] = (cells, staged, run, g.result(), st["force_pairs"], st["kernels"]["com"]["launches"])
+        g.close()
+    a, b = res["0"], res["1"]
+    for t in range(steps):
+        for q in range(3):
+            assert np.array_equal(a[0][t][q], b[0][t][q]), (t, q)
+    for which in (1, 2):
+        assert a[which][0] == b[which][0], which
+        for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+            assert np.array_equal(a[which][1][k], b[which][1][k]), (which, k)
+    assert a[3] == b[3] and a[4] == b[4]
+    assert a[5] == steps  # one k_com per step without the fusion
+
+
 @pytest.mark.parametrize("case", [(1, 10, 100, 100000, 4, 20000), (5, 1, 20, 200000, 3, 30000), (-7, 10, 50, 20000, 5, 3000),
                                   (3, 1, 2, 200, 4, 64), (1, 2, 3, 10, 3, 64), (7, 30, 300, 2000000, 2, 1 << 19)],
                          ids=lambda c: " ".join(map(str, c)))
