@@ -320,6 +320,23 @@ def main_ours(a):
     e2e_value = work * a.steps / e2e_s
     h2d_bytes = 40 * cnt + (4 * cnt if world > 1 else 0)
     h2d_gbs_slowest = h2d_bytes * a.steps / max_over_ranks(upload_s[0]) / 1e9
+    # the platform's ceiling for that copy: the same pinned buffers through plain cudaMemcpyAsync into
+    # scratch device memory, every rank at once, nothing else running (host DRAM / PCIe root complexes
+    # are shared by the ranks of a node)
+    scratch = [torch.empty(t.shape, dtype=t.dtype, device="cuda") for t in pinned]
+    raw_s = None
+    for rep in range(3):
+        torch.cuda.synchronize()
+        barrier()
+        t_raw = time.perf_counter()
+        for d_t, h_t in zip(scratch, pinned):
+            d_t.copy_(h_t, non_blocking=True)
+        torch.cuda.synchronize()
+        dt_raw = time.perf_counter() - t_raw
+        if rep:
+            raw_s = dt_raw if raw_s is None else min(raw_s, dt_raw)
+    h2d_raw_gbs_slowest = 40 * cnt / max_over_ranks(raw_s) / 1e9
+    del scratch
     assert res[2] == collisions, "end-to-end run disagrees with the device-resident run"
 
     # ---- the other BASELINE configurations, one short sub-line each (same code, same library) -----
@@ -453,6 +470,8 @@ def main_ours(a):
         "e2e": {"value": e2e_value, "unit": "particle-steps/s", "h2d_bytes_per_step": h2d_bytes,
                 "d2h_bytes_per_step": 24, "ms_per_step": 1e3 * e2e_s / a.steps,
                 "h2d_GBps_slowest_rank": h2d_gbs_slowest,
+                "h2d_raw_GBps_slowest_rank": h2d_raw_gbs_slowest,
+                "h2d_raw_note": "plain cudaMemcpyAsync of the same pinned buffers, all ranks at once: the platform's ceiling",
                 "inputs": "pinned host arrays of this rank's strip (x, y, vx, vy, m" + (", id" if world > 1 else "") + ")"},
         "gpu_launches": int(sum(v["launches"] for v in kern.values())),
         "roofline": roofline,

@@ -249,7 +249,7 @@ void rank_destroy(Rank *c) {
 static int reset_state(Rank *c) {
     c->n_uploaded = 0;
     const size_t C = (size_t)c->g.ncells;
-    c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->com_valid = false; c->next_stage = 0;
+    c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->com_valid = false; c->count_pending = false; c->next_stage = 0;
     c->piece_sorted = false;
     c->n_tomb = 0; c->n_grave = 0; c->steps_done = 0; c->collisions_total = 0;
     c->have_newcell = c->have_flags = false;

@@ -89,6 +89,7 @@ struct Rank {
     int n_alive = 0;
     int n_guest = 0;
     bool sorted = false;   // cell order valid for the coming step
+    bool count_pending = false;  // several strips: n_alive of the coming step is still on its way (ev_ring[0], h_ring[0])
     bool com_valid = false;  // the merge of the last step already left this step's centres of mass (k_move<.., COM>)
     bool fuse_com = true;    // PARSIM_FUSE_COM=0: always k_com (A/B)
     int next_stage = 0;    // debug stepping

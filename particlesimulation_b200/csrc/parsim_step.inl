@@ -265,9 +265,20 @@ static void launch_com_any(Rank *c) {
     }
 }
 
+// Several strips: the particle count the last merge left (see the end of stage_collide).
+static int settle_count(Rank *c) {
+    if (!c->count_pending) return 0;
+    c->count_pending = false;
+    PS_CUDA(c, cudaEventSynchronize(c->ev_ring[0]));
+    c->n_alive = c->h_ring[0].n_next;
+    return 0;
+}
+
 // stage 0: binning (only when the cell order is not valid yet) + centre of mass + ghost rows
 static int stage_bin_com(Rank *c) {
     const Geom &g = c->g;
+    // with the centres of mass already there, nothing before the force stage needs the new count
+    if (!(c->com_valid && c->sorted && !c->opt_stats) && settle_count(c)) return 1;
     if (!c->sorted) {
         if (bin_initial(c)) return 1;
         c->sorted = true;
@@ -288,7 +299,7 @@ static int stage_bin_com(Rank *c) {
     }
     c->pos_latest = c->pos_cur;
     c->have_newcell = c->have_flags = false;
-    return 0;
+    return settle_count(c);
 }
 
 // stage 1: forces + integration
@@ -413,18 +424,20 @@ static int stage_collide(Rank *c) {
         c->stats.steps++;
         return 0;
     }
-    PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
-    PS_CUDA(c, cudaStreamSynchronize(c->stream));
-    // several strips: a device error is not reported here but through the next exchange, which lets
-    // every strip leave together (parsim_exchange.cuh)
-    if (c->h_ctr->error && c->nranks == 1) return c->fail("device error code " + std::to_string(c->h_ctr->error));
+    int n_src = n_tot, tomb_in = 0;
+    if (c->nranks > 1) {
+        // several strips: the header round of the late exchange brings the counters to the host as well
+        // (one host round trip instead of two), and a device error is not reported here but through
+        // that exchange, which lets every strip leave together (parsim_exchange.cuh)
+        if (exchange_late(c, &n_src, &tomb_in)) return 1;
+    } else {
+        PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));
+        if (c->h_ctr->error) return c->fail("device error code " + std::to_string(c->h_ctr->error));
+    }
     const int grave_first = c->n_grave;
     const int deaths = c->h_ctr->grave_count - grave_first;
     c->n_grave = c->h_ctr->grave_count;
-    int n_src = n_tot, tomb_in = 0, n_next;
-    if (c->nranks > 1) {
-        if (exchange_late(c, &n_src, &tomb_in)) return 1;
-    }
     // the tombstone lists change only when somebody died or a tombstone arrived: otherwise they
     // stay where they are (no scan, no copy)
     const bool with_dead = deaths > 0 || tomb_in > 0;
@@ -437,17 +450,18 @@ static int stage_collide(Rank *c) {
     }
     if (merge_step(c, n_src, n_src - deaths, with_dead)) return 1;
     c->n_tomb += deaths + tomb_in;  // upper bound; exact total is dead_start[ncells]
-    if (c->nranks == 1) {
-        n_next = n_tot - deaths;
-    } else {
-        PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
-        PS_CUDA(c, cudaStreamSynchronize(c->stream));
-        n_next = c->h_ctr->n_next;
-    }
     c->stats.alive_particle_steps += c->n_alive;
     c->stats.movers += c->h_ctr->n_movers;
     c->stats.deaths += deaths;
-    c->n_alive = n_next;
+    if (c->nranks == 1) {
+        c->n_alive = n_tot - deaths;
+    } else {
+        // the strip's new particle count is the total of the scan: it is fetched without waiting, the next
+        // step's ghost-row exchange is enqueued behind it, and the host picks it up before the force stage
+        PS_CUDA(c, cudaMemcpyAsync(&c->h_ring[0].n_next, &c->d_ctr->n_next, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        PS_CUDA(c, cudaEventRecord(c->ev_ring[0], c->stream));
+        c->count_pending = true;
+    }
     c->n_guest = 0;
     c->pos_latest = c->pos_cur;
     c->have_newcell = c->have_flags = false;
@@ -482,7 +496,7 @@ int rank_stage(Rank *c, int stage) {
     }
     if (rc) return rc;
     c->next_stage = (stage + 1) & 3;
-    return 0;
+    return settle_count(c);  // callers between stages (dumps, results) see the final count
 }
 
 // The counters of the step before last, once they have arrived: the host stays at most two steps
@@ -591,6 +605,7 @@ int rank_run(Rank *c, long n_steps) {
         if (rc) { c->deferred = false; return 1; }
     }
     PS_CUDA(c, cudaEventRecord(c->run_b, c->stream));
+    if (settle_count(c)) return 1;
     if (c->deferred && n_steps > 0) {
         PS_CUDA(c, cudaMemcpyAsync(c->h_ctr, c->d_ctr, sizeof(Counters), cudaMemcpyDeviceToHost, c->stream));
         PS_CUDA(c, cudaStreamSynchronize(c->stream));
