@@ -489,8 +489,16 @@ __global__ void k_count_pairs(int ncells, const int *__restrict__ cell_start, un
 
 // Single strip: the ghost rows are the strip's own last / first row (periodic wrap,
 // serial/parsim.cpp:332-333).  Multi-strip runs fill them over NCCL instead.
-__global__ void k_ghost_wrap(Geom g, double2 *com_xy, double *com_m) {
+// It is the first kernel of a single strip's step that every step runs, so it also zeroes the
+// step's work-list counters (k_step_reset's job: one launch less per timestep, which is what a
+// launch-bound problem such as BASELINE configs[1] is made of).
+__global__ void k_ghost_wrap(Geom g, double2 *com_xy, double *com_m, Counters *ctr, int *big_count, int *move_big_count) {
     int gx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gx == 0 && ctr) {
+        ctr->n_movers = 0;
+        if (big_count) { big_count[0] = 0; big_count[1] = 0; }
+        *move_big_count = 0;
+    }
     if (gx >= g.nc) return;
     com_xy[gx] = com_xy[g.rows * g.nc + gx];
     com_m[gx] = com_m[g.rows * g.nc + gx];
@@ -995,6 +1003,56 @@ __global__ void k_scan2_top(int *tile_sums, int ntiles, int *total_a, int *total
             else *total_b = carry;
         }
         __syncthreads();
+    }
+}
+
+// Grids of up to kScanFewTiles tiles: every block of the apply kernel adds up the tile sums before
+// its own by itself, so the one-block k_scan2_top launch in the middle disappears (two launches
+// instead of three: launch-bound problems such as BASELINE configs[1] are made of launches).  A
+// one-block scan of the whole grid was measured SLOWER than the three launches (30-36 us against
+// 20 us at 1e4 cells, with 256 and with 1024 threads: one SM's load/store path is the limit).
+constexpr int kScanFewTiles = kThreads;
+__global__ void k_scan2_apply_few(const int *__restrict__ a, int *__restrict__ acc, int *__restrict__ add, int N, int ntiles,
+                                  const int *__restrict__ tile_sums, int *__restrict__ out_a, int *total_a2,
+                                  int *__restrict__ out_b) {
+    __shared__ int ws[33];
+    // tile sums before mine (and, for the last block, the totals)
+    const int ta = (int)threadIdx.x < ntiles ? tile_sums[threadIdx.x] : 0;
+    const int tb = (int)threadIdx.x < ntiles ? tile_sums[ntiles + threadIdx.x] : 0;
+    int tot_a, tot_b, tot;
+    block_exclusive_scan((int)threadIdx.x < (int)blockIdx.x ? ta : 0, ws, tot_a);
+    block_exclusive_scan((int)threadIdx.x < (int)blockIdx.x ? tb : 0, ws, tot_b);
+    int base = blockIdx.x * kScanTile + threadIdx.x * kScanItems;
+    int va[kScanItems], vb[kScanItems];
+    int sa = 0, sb = 0;
+#pragma unroll
+    for (int j = 0; j < kScanItems; j++) {
+        int k = base + j;
+        va[j] = k < N ? a[k] : 0;
+        vb[j] = k < N ? acc[k] + add[k] : 0;
+        sa += va[j];
+        sb += vb[j];
+    }
+    int ea = block_exclusive_scan(sa, ws, tot) + tot_a;
+    const int mine_a = tot;
+    int eb = block_exclusive_scan(sb, ws, tot) + tot_b;
+    const int mine_b = tot;
+#pragma unroll
+    for (int j = 0; j < kScanItems; j++) {
+        int k = base + j;
+        if (k < N) {
+            out_a[k] = ea;
+            out_b[k] = eb;
+            acc[k] = vb[j];
+            add[k] = 0;
+        }
+        ea += va[j];
+        eb += vb[j];
+    }
+    if ((int)blockIdx.x == ntiles - 1 && threadIdx.x == 0) {
+        out_a[N] = tot_a + mine_a;
+        if (total_a2) *total_a2 = tot_a + mine_a;
+        out_b[N] = tot_b + mine_b;
     }
 }
 

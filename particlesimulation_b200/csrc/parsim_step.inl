@@ -2,6 +2,11 @@
 // Stage numbering follows include/parsim_b200.h (parsim_debug_stage).
 namespace parsim {
 
+static bool scan_few_ok() {  // PARSIM_SCAN_FEW=0: always the three-launch scans (A/B)
+    static const bool v = !getenv("PARSIM_SCAN_FEW") || atoi(getenv("PARSIM_SCAN_FEW")) != 0;
+    return v;
+}
+
 // exclusive scan of in[0..N) into out[0..N], out[N] = total (also stored to *total2 if given)
 static int device_scan(Rank *c, const int *in, int N, int *out, int *total2) {
     int ntiles = (N + kScanTile - 1) / kScanTile;
@@ -14,10 +19,18 @@ static int device_scan(Rank *c, const int *in, int N, int *out, int *total2) {
     return 0;
 }
 
-// both scans of the end of a step in three launches (k_scan2_*): a -> out_a (total also to *total_a2),
+// both scans of the end of a step in three launches (k_scan2_*; two on grids of few tiles): a -> out_a (total also to *total_a2),
 // acc + add -> out_b with acc += add, add = 0
 static int device_scan2(Rank *c, const int *a, int *acc, int *add, int N, int *out_a, int *total_a2, int *out_b) {
     int ntiles = (N + kScanTile - 1) / kScanTile;
+    if (ntiles <= kScanFewTiles && scan_few_ok()) {
+        PS_LAUNCH(c, K_SCAN, 32.0 * N, "k_scan2_few", {
+            k_scan2_tile_sums<<<ntiles, kThreads, 0, c->stream>>>(a, acc, add, N, ntiles, c->tile_sums);
+            k_scan2_apply_few<<<ntiles, kThreads, 0, c->stream>>>(a, acc, add, N, ntiles, c->tile_sums, out_a, total_a2, out_b);
+        });
+        if (c->opt_stats) c->stats.kernel_launches[K_SCAN] += 1;
+        return 0;
+    }
     PS_LAUNCH(c, K_SCAN, 32.0 * N, "k_scan2", {
         k_scan2_tile_sums<<<ntiles, kThreads, 0, c->stream>>>(a, acc, add, N, ntiles, c->tile_sums);
         k_scan2_top<<<1, kThreads, 0, c->stream>>>(c->tile_sums, ntiles, out_a + N, total_a2, out_b + N);
@@ -283,7 +296,8 @@ static int stage_bin_com(Rank *c) {
         if (bin_initial(c)) return 1;
         c->sorted = true;
     }
-    k_step_reset<<<1, 1, 0, c->stream>>>(c->d_ctr, c->d_big_count, c->d_move_big_count);  // work-list counters of this step
+    // work-list counters of this step (a single strip's k_ghost_wrap below does it on the way)
+    if (c->nranks > 1) k_step_reset<<<1, 1, 0, c->stream>>>(c->d_ctr, c->d_big_count, c->d_move_big_count);
     if (!c->com_valid) {
         PS_LAUNCH(c, K_COM, 24.0 * c->n_alive + 24.0 * g.ncells, "k_com", launch_com_any(c));
     } else if (c->opt_stats) {  // k_com also counts the ordered pairs of the force phase
@@ -293,7 +307,8 @@ static int stage_bin_com(Rank *c) {
     c->com_valid = false;  // consumed: the force phase moves the particles
     if (c->nranks == 1) {
         PS_LAUNCH(c, K_GHOST, 96.0 * g.nc, "k_ghost_wrap",
-                  k_ghost_wrap<<<grid_for(g.nc), kThreads, 0, c->stream>>>(g, c->com_xy, c->com_m));
+                  k_ghost_wrap<<<grid_for(g.nc), kThreads, 0, c->stream>>>(g, c->com_xy, c->com_m, c->d_ctr, c->d_big_count,
+                                                                           c->d_move_big_count));
     } else if (exchange_halo(c)) {
         return 1;
     }
