@@ -889,13 +889,15 @@ __device__ __forceinline__ int find_first_partner(const Geom &g, int i, int n_re
                                                   const int *__restrict__ arr_head, const int *__restrict__ arr_next,
                                                   const int *__restrict__ guest_src, unsigned long long &tested) {
     const unsigned char f = flags[i];
+    int L = cell[i];  // issued together with flags[i]; only the rare removed mover pays a second, dependent load
     int best_idx = -1;
     if (f & F_EMIGRANT) return -1;  // emigrants are checked on the strip they moved to
-    const int L = (f & F_REMOVED) ? newcell[i] - g.cell_base : cell[i];
+    if (f & F_REMOVED) L = newcell[i] - g.cell_base;
     const double2 p = pos[i];
     const float2 pf = posf[i];
     unsigned long long best = ~0ull;
     const int s = cell_start[L], e = cell_start[L + 1];
+    int k_arr = arr_head[L];  // loaded with the bounds, not after the loop: one dependent round trip less
     // residents of L that are still listed there (stayers and strays), key = id, id-sorted.
     // FP32 pre-filter: thrf over-covers the rounding of the float copies, so every pair
     // that is close in FP64 passes it; the decision itself is the exact FP64 test.
@@ -912,7 +914,7 @@ __device__ __forceinline__ int find_first_partner(const Geom &g, int i, int n_re
     }
     // arrivals appended to L's list
     int walked = 0;
-    for (int k = arr_head[L]; k >= 0; k = arr_next[k]) {
+    for (int k = k_arr; k >= 0; k = arr_next[k]) {
         walked++;
         if (k == i) continue;
         if (is_close(p, pos[k], thr2)) {
