@@ -134,7 +134,22 @@ __global__ void k_ingest(Geom g, long long id_base, const unsigned *__restrict__
     if (t >= count) return;
     const unsigned pid = ids ? ids[t] : (unsigned)(id_base + t);
     if (pid >= (unsigned)capacity) { ctr->error = DE_CAPACITY; return; }
-    store_rec(rec, (int)pid, make_double2(x[t], y[t]), make_double2(vx[t], vy[t]), m[t], pid);
+    // vx == nullptr: the velocities arrive later (k_rec_vel), see rank_upload_chunk
+    store_rec(rec, (int)pid, make_double2(x[t], y[t]), vx ? make_double2(vx[t], vy[t]) : make_double2(0.0, 0.0), m[t], pid);
+}
+
+// Late velocities of a single-strip upload (slot = id): into the records ...
+__global__ void k_rec_vel(int n, const double *__restrict__ vx, const double *__restrict__ vy, InitRec *rec) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) reinterpret_cast<double2 *>(rec + i)[1] = make_double2(vx[i], vy[i]);
+}
+// ... and into the (cell, id)-ordered velocity array
+__global__ void k_vel_apply(int n, const unsigned *__restrict__ id, const double *__restrict__ vx,
+                            const double *__restrict__ vy, double2 *__restrict__ vel) {
+    const int p = blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    const unsigned s = id[p];
+    vel[p] = make_double2(__ldg(vx + s), __ldg(vy + s));
 }
 
 // ---------------------------------------------------------------------------------------
@@ -590,6 +605,40 @@ __global__ void k_pair_peak(int iters, double *out) {
     if (r == 123.456) out[0] = r;
 }
 
+// Particle::updatePositionAndVelocity (serial/parsim.cpp:54-60, same rounding sequence), the wrap
+// (:171-172), the new cell (:174-177) and the mover list: the tail of a particle's force stage.
+__device__ __forceinline__ void integrate_store(const Geom &g, int i, int c, double2 p, double2 v, double ax, double ay,
+                                                double2 *__restrict__ pos_out, float2 *__restrict__ posf_out,
+                                                double2 *__restrict__ vel, int *__restrict__ newcell,
+                                                unsigned char *__restrict__ flags, int *__restrict__ mover_list,
+                                                int *n_movers) {
+    double x = __dadd_rn(p.x, __dadd_rn(__dmul_rn(v.x, kDeltaT),
+                                        __dmul_rn(__dmul_rn(__dmul_rn(0.5, ax), kDeltaT), kDeltaT)));
+    double y = __dadd_rn(p.y, __dadd_rn(__dmul_rn(v.y, kDeltaT),
+                                        __dmul_rn(__dmul_rn(__dmul_rn(0.5, ay), kDeltaT), kDeltaT)));
+    v.x = __dadd_rn(v.x, __dmul_rn(ax, kDeltaT));
+    v.y = __dadd_rn(v.y, __dmul_rn(ay, kDeltaT));
+    x = wrap_coord(x, g.side);  // :171-172
+    y = wrap_coord(y, g.side);
+    double2 pn = make_double2(x, y);
+    pos_out[i] = pn;
+    if (posf_out) posf_out[i] = make_float2((float)x, (float)y);  // pre-filter of k_collide_find
+    vel[i] = v;
+    const int cnew = global_cell_fast(pn, g);  // :174-177
+    newcell[i] = cnew;
+    // movers (:183-190) are rare: they go on a list for k_classify, everybody else is done here
+    const bool mover = cnew != c + g.cell_base;
+    flags[i] = mover ? (unsigned char)F_MOVER : (unsigned char)0;
+    if (mover) {
+        const unsigned mm = __activemask();
+        const int lane = threadIdx.x & 31, leader = __ffs(mm) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(n_movers, __popc(mm));
+        base = __shfl_sync(mm, base, leader);
+        mover_list[base + __popc(mm & ((1u << lane) - 1u))] = i;
+    }
+}
+
 // A block of TB consecutive particles touches the segments of the cells from its first to its
 // last particle's cell: one contiguous range of the (cell, id)-ordered arrays.  The range is
 // staged in shared memory with coalesced loads (24 B per source), and the pair loop reads it
@@ -616,7 +665,9 @@ __device__ __forceinline__ void cp_async_wait_all() {
 // load latency in front of the pair loop (15 % + 13 % of the warp stall samples of the plain kernel,
 // profiles/ncu_force_r02_v2_stalls.txt) overlap with 104 FP64 instructions per thread.  Same
 // operations in the same order per target: bit-identical results.
-template <int TB, int UNROLL, int TILE, int CELLS, int MINB, bool EARLY = false>
+// ACC_ONLY: the kernel stops after the force sum and stores the acceleration (dbg_acc is the output);
+// k_integrate_acc finishes the step once the velocities are there (uploads with late velocities).
+template <int TB, int UNROLL, int TILE, int CELLS, int MINB, bool EARLY = false, bool ACC_ONLY = false>
 __global__ void __launch_bounds__(TB, MINB)
 k_force_integrate(Geom g, int n_val, const int *__restrict__ n_ptr, const double2 *__restrict__ pos_in,
                   const double *__restrict__ m, const int *__restrict__ cell,
@@ -683,7 +734,7 @@ k_force_integrate(Geom g, int n_val, const int *__restrict__ n_ptr, const double
     }
     double ax = 0.0, ay = 0.0;
     double2 v = make_double2(0.0, 0.0);
-    if (i < n) v = vel[i];
+    if (!ACC_ONLY && i < n) v = vel[i];
     if (!EARLY) {
         if (staged || nb_staged) __syncthreads();
         if (i >= n) return;
@@ -753,34 +804,24 @@ k_force_integrate(Geom g, int n_val, const int *__restrict__ n_ptr, const double
     }
     ax *= kG;
     ay *= kG;
-    if (dbg_acc) dbg_acc[i] = make_double2(ax, ay);
-
-    // Particle::updatePositionAndVelocity, serial/parsim.cpp:54-60, same rounding sequence
-    double x = __dadd_rn(p.x, __dadd_rn(__dmul_rn(v.x, kDeltaT),
-                                        __dmul_rn(__dmul_rn(__dmul_rn(0.5, ax), kDeltaT), kDeltaT)));
-    double y = __dadd_rn(p.y, __dadd_rn(__dmul_rn(v.y, kDeltaT),
-                                        __dmul_rn(__dmul_rn(__dmul_rn(0.5, ay), kDeltaT), kDeltaT)));
-    v.x = __dadd_rn(v.x, __dmul_rn(ax, kDeltaT));
-    v.y = __dadd_rn(v.y, __dmul_rn(ay, kDeltaT));
-    x = wrap_coord(x, g.side);  // :171-172
-    y = wrap_coord(y, g.side);
-    double2 pn = make_double2(x, y);
-    pos_out[i] = pn;
-    if (posf_out) posf_out[i] = make_float2((float)x, (float)y);  // pre-filter of k_collide_find
-    vel[i] = v;
-    const int cnew = global_cell_fast(pn, g);  // :174-177
-    newcell[i] = cnew;
-    // movers (:183-190) are rare: they go on a list for k_classify, everybody else is done here
-    const bool mover = cnew != c + g.cell_base;
-    flags[i] = mover ? (unsigned char)F_MOVER : (unsigned char)0;
-    if (mover) {
-        const unsigned mm = __activemask();
-        const int lane = threadIdx.x & 31, leader = __ffs(mm) - 1;
-        int base = 0;
-        if (lane == leader) base = atomicAdd(n_movers, __popc(mm));
-        base = __shfl_sync(mm, base, leader);
-        mover_list[base + __popc(mm & ((1u << lane) - 1u))] = i;
+    if (ACC_ONLY) {
+        dbg_acc[i] = make_double2(ax, ay);
+        return;
     }
+    if (dbg_acc) dbg_acc[i] = make_double2(ax, ay);
+    integrate_store(g, i, c, p, v, ax, ay, pos_out, posf_out, vel, newcell, flags, mover_list, n_movers);
+}
+
+// The second half of a step whose force sums were taken early (k_force_integrate<.., ACC_ONLY>).
+__global__ void __launch_bounds__(kThreads)
+k_integrate_acc(Geom g, int n, const double2 *__restrict__ pos_in, const int *__restrict__ cell,
+                const double2 *__restrict__ acc, double2 *__restrict__ pos_out, float2 *__restrict__ posf_out,
+                double2 *__restrict__ vel, int *__restrict__ newcell, unsigned char *__restrict__ flags,
+                int *__restrict__ mover_list, int *n_movers) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double2 a = acc[i];
+    integrate_store(g, i, cell[i], pos_in[i], vel[i], a.x, a.y, pos_out, posf_out, vel, newcell, flags, mover_list, n_movers);
 }
 
 // ---------------------------------------------------------------------------------------

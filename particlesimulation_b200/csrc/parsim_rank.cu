@@ -14,6 +14,7 @@ namespace parsim {
 
 static int device_scan(Rank *c, const int *in, int N, int *out, int *total2);  // parsim_step.inl
 static int sort_piece(Rank *c, int first, int cnt, int piece);                  // parsim_step.inl
+static int upload_prestep(Rank *c);                                              // parsim_step.inl
 
 template <typename T>
 static int dev_alloc(Rank *c, T **p, size_t count, bool zero = false) {
@@ -199,6 +200,7 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     if (const char *e = getenv("PARSIM_GRAPHS")) c->use_graphs = atoi(e) != 0;
     if (const char *e = getenv("PARSIM_PIECE_SORT")) c->opt_piece_sort = atoi(e) != 0;
     if (const char *e = getenv("PARSIM_FUSE_COM")) c->fuse_com = atoi(e) != 0;
+    if (const char *e = getenv("PARSIM_VEL_LATE")) c->opt_vel_late = atoi(e) != 0;
     if (const char *e = getenv("PARSIM_STAGE_PIECE")) c->stage_piece_len = std::max(64, atoi(e));
     PS_CUDA(c, cudaEventCreate(&c->run_a));
     PS_CUDA(c, cudaEventCreate(&c->run_b));
@@ -235,6 +237,8 @@ void rank_destroy(Rank *c) {
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
     for (auto &sg : c->graphs) cudaGraphExecDestroy(sg.exec);
     c->graphs.clear();
+    if (c->late_vx) cudaFree(c->late_vx);
+    if (c->late_vy) cudaFree(c->late_vy);
     if (c->h_ring) cudaFreeHost(c->h_ring);
     for (int k = 0; k < kCounterRing; k++) if (c->ev_ring[k]) cudaEventDestroy(c->ev_ring[k]);
     for (auto &t : c->pending) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
@@ -249,7 +253,7 @@ void rank_destroy(Rank *c) {
 static int reset_state(Rank *c) {
     c->n_uploaded = 0;
     const size_t C = (size_t)c->g.ncells;
-    c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->com_valid = false; c->count_pending = false; c->next_stage = 0;
+    c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->com_valid = false; c->count_pending = false; c->acc0 = nullptr; c->next_stage = 0;
     c->piece_sorted = false;
     c->n_tomb = 0; c->n_grave = 0; c->steps_done = 0; c->collisions_total = 0;
     c->have_newcell = c->have_flags = false;
@@ -340,6 +344,13 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
     PS_CUDA(c, cudaSetDevice(c->device));
     if (rank_stage_alloc(c)) return 1;
     const double *src[5] = {x, y, vx, vy, m};
+    // Late velocities: a single strip that gets ALL its particles in this one call (parsim_upload) and
+    // sorts the pieces as they arrive copies x, y, m of every piece first and the two velocity arrays
+    // last, and runs the part of the first timestep that needs no velocity -- the merge of the pieces,
+    // the centres of mass, the force sums -- while those 16 bytes per particle are still on the link.
+    const bool vel_late = c->opt_vel_late && c->nranks == 1 && !ids && id_base == 0 && count == c->n_part &&
+                          c->n_uploaded == 0 && c->pieces_ok && count > c->stage_cap && c->force_variant <= 0 &&
+                          !c->opt_stats && !c->opt_sync_check && !c->dbg_acc;
     for (long long off = 0; off < count; off += c->stage_cap) {
         const int cnt = (int)std::min<long long>(c->stage_cap, count - off);
         const int b = (int)(c->stage_pieces & 1);
@@ -347,14 +358,16 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
         // the set is free once the k_ingest of two passes ago has read it
         if (c->stage_pieces >= 2) PS_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_ingested[b], 0));
         for (int k = 0; k < 5; k++)
-            PS_CUDA(c, cudaMemcpyAsync(st[k], src[k] + off, sizeof(double) * cnt, cudaMemcpyHostToDevice,
-                                       c->copy_stream));
+            if (!vel_late || (k != 2 && k != 3))
+                PS_CUDA(c, cudaMemcpyAsync(st[k], src[k] + off, sizeof(double) * cnt, cudaMemcpyHostToDevice,
+                                           c->copy_stream));
         if (ids)
             PS_CUDA(c, cudaMemcpyAsync(c->stage_ids[b], ids + off, sizeof(unsigned) * cnt,
                                        cudaMemcpyHostToDevice, c->copy_stream));
         PS_CUDA(c, cudaEventRecord(c->ev_copied[b], c->copy_stream));
         PS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[b], 0));
-        if (rank_ingest_piece(c, id_base + off, ids ? c->stage_ids[b] : nullptr, cnt, st)) return 1;
+        double *const late_set[5] = {st[0], st[1], nullptr, nullptr, st[4]};
+        if (rank_ingest_piece(c, id_base + off, ids ? c->stage_ids[b] : nullptr, cnt, vel_late ? late_set : st)) return 1;
         PS_CUDA(c, cudaEventRecord(c->ev_ingested[b], c->stream));
         c->stage_pieces++;
         // sort the piece now, under the shadow of the next piece's copy (parsim_step.inl sort_piece):
@@ -366,6 +379,29 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
             c->piece_first.push_back((int)(id_base + off));
             if (sort_piece(c, (int)(id_base + off), cnt, piece)) return 1;
         }
+    }
+    if (vel_late) {
+        if (!c->late_vx) {
+            PS_ALLOC(c, c->late_vx, (size_t)c->n_part, false);
+            PS_ALLOC(c, c->late_vy, (size_t)c->n_part, false);
+        }
+        PS_CUDA(c, cudaMemcpyAsync(c->late_vx, vx, sizeof(double) * count, cudaMemcpyHostToDevice, c->copy_stream));
+        PS_CUDA(c, cudaMemcpyAsync(c->late_vy, vy, sizeof(double) * count, cudaMemcpyHostToDevice, c->copy_stream));
+        c->n_uploaded = count;
+        const bool pre = c->pieces_ok;  // (false: more pieces than tables -- the records are completed, step 0 sorts them)
+        if (pre) {
+            c->n_alive = c->n0 = (int)c->n_part;
+            c->piece_sorted = true;
+            c->slots_id_ordered = true;
+            k_set_int<<<1, 1, 0, c->stream>>>(&c->d_ctr->n_next, c->n_alive);
+            if (upload_prestep(c)) return 1;
+        }
+        PS_CUDA(c, cudaStreamSynchronize(c->copy_stream));  // the caller's arrays are free again
+        k_rec_vel<<<grid_for((int)count), kThreads, 0, c->stream>>>((int)count, c->late_vx, c->late_vy, c->rec0);
+        if (pre)
+            k_vel_apply<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(c->n_alive, c->id_cur, c->late_vx, c->late_vy,
+                                                                         c->vel_cur);
+        return check_launch(c, "k_vel_apply");
     }
     // the caller's arrays are free again when this returns ("they are copied"); the ingest kernels
     // may still be running -- parsim_upload_end waits for them
@@ -388,7 +424,8 @@ int rank_upload_end(Rank *c) {
     else c->n_alive = (int)c->n_part;
     c->pos_latest = c->pos_cur;
     c->n0 = c->n_alive;
-    c->piece_sorted = c->pieces_ok && !c->piece_first.empty() && c->n_uploaded == c->n_part;
+    // (an upload with late velocities has merged its pieces already: c->sorted)
+    c->piece_sorted = !c->sorted && c->pieces_ok && !c->piece_first.empty() && c->n_uploaded == c->n_part;
     k_set_int<<<1, 1, 0, c->stream>>>(&c->d_ctr->n_next, c->n_alive);  // the kernels' particle count
     c->slots_id_ordered = true;
     if (c->nranks > 1 && c->n_alive > 1) {  // explicit-id uploads may come in any order

@@ -318,6 +318,26 @@ static int stage_bin_com(Rank *c) {
 }
 
 // stage 1: forces + integration
+// the force sums alone (accelerations into `acc`): the first half of a step whose velocities are
+// still on their way from the host (rank_upload_chunk); stage_force then only integrates
+static int force_acc_only(Rank *c, double2 *acc) {
+#define PS_FORCE_ACC(UN, TILE, CELLS, MINB, EARLY)                                                          \
+    k_force_integrate<128, UN, TILE, CELLS, MINB, EARLY, true><<<grid_for(c->n_alive, 128), 128, 0, c->stream>>>( \
+        c->g, c->n_alive, nullptr, c->pos_cur, c->m_cur, c->cell_cur, c->cs_cur, c->com_xy, c->com_m, nullptr,    \
+        nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, acc)
+    const int v = (double)c->n_alive < 28.0 * c->g.ncells ? c->sparse_variant : 2;  // as stage_force
+    if (c->n_alive > 0)
+    PS_LAUNCH(c, K_FORCE, 49.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate<acc>", {
+        switch (v) {
+        case 1: PS_FORCE_ACC(2, 256, 0, 16, false); break;
+        case 5: PS_FORCE_ACC(2, 256, 0, 16, true); break;
+        default: PS_FORCE_ACC(4, 768, 16, 8, false); break;
+        }
+    });
+#undef PS_FORCE_ACC
+    return 0;
+}
+
 static int stage_force(Rank *c) {
 #define PS_FORCE_TB(TB, UN, TILE, CELLS, MINB, ...)                                                 \
     k_force_integrate<TB, UN, TILE, CELLS, MINB, ##__VA_ARGS__><<<grid_for(c->n_alive, TB), TB, 0, c->stream>>>( \
@@ -330,7 +350,16 @@ static int stage_force(Rank *c) {
     if (v <= 0) v = (double)c->n_alive < 28.0 * c->g.ncells ? c->sparse_variant : 2;  // measured crossover: about 30 per cell
     // an empty strip (everybody dead, or a strip the cloud does not reach) has nothing to move; the
     // kernels read cell[first] / cell[last] of their block unconditionally, so they are not launched
-    if (c->n_alive > 0)
+    if (c->acc0) {
+        // the force sums of this step were taken while the velocities were uploaded
+        double2 *acc = c->acc0;
+        c->acc0 = nullptr;
+        if (c->n_alive > 0)
+        PS_LAUNCH(c, K_FORCE, 77.0 * c->n_alive, "k_integrate_acc",
+                  k_integrate_acc<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(
+                      c->g, c->n_alive, c->pos_cur, c->cell_cur, acc, c->pos_alt, c->posf, c->vel_cur, c->newcell,
+                      c->flags, c->partner, &c->d_ctr->n_movers));
+    } else if (c->n_alive > 0)
     PS_LAUNCH(c, K_FORCE, 81.0 * c->n_alive + 24.0 * c->g.ncells, "k_force_integrate", {
         switch (v) {
         case 1: PS_FORCE(2, 256, 0, 16); break;   // sparse cells: neighbourhood through L1, 32 registers, full occupancy
@@ -347,6 +376,24 @@ static int stage_force(Rank *c) {
 #undef PS_FORCE_TB
     c->pos_latest = c->pos_alt;
     c->have_newcell = true;
+    return 0;
+}
+
+// Upload with late velocities (rank_upload_chunk): everything of the first timestep that needs
+// positions and masses only -- the merge of the sorted pieces, the centres of mass, the force sums --
+// runs while the velocity arrays are still crossing PCIe.  stage_bin_com / stage_force of the first
+// step then find the centres of mass and the accelerations in place.
+static int upload_prestep(Rank *c) {
+    const Geom &g = c->g;
+    if (bin_initial(c)) return 1;
+    c->sorted = true;
+    PS_LAUNCH(c, K_COM, 24.0 * c->n_alive + 24.0 * g.ncells, "k_com", launch_com_any(c));
+    PS_LAUNCH(c, K_GHOST, 96.0 * g.nc, "k_ghost_wrap",
+              k_ghost_wrap<<<grid_for(g.nc), kThreads, 0, c->stream>>>(g, c->com_xy, c->com_m, nullptr, nullptr, nullptr));
+    c->com_valid = true;
+    if (force_acc_only(c, c->vel_alt)) return 1;  // vel_alt is free until the merge at the end of the step
+    c->acc0 = c->vel_alt;
+    c->pos_latest = c->pos_cur;
     return 0;
 }
 
@@ -545,6 +592,7 @@ static void deferred_host_advance(Rank *c) {
     std::swap(c->dead_start_cur, c->dead_start_alt);
     std::swap(c->dead_id_cur, c->dead_id_alt);
     c->n_guest = 0;
+    c->acc0 = nullptr;  // consumed by the step's force stage, if it was there
     c->ring_pos++;
     c->pos_latest = c->pos_cur;
     c->have_newcell = c->have_flags = false;
@@ -563,7 +611,9 @@ static int deferred_step_graph(Rank *c) {
     const unsigned long long key = (c->pos_cur < c->pos_alt ? 1ull : 0) | (c->vel_cur < c->vel_alt ? 2ull : 0) |
                                    (c->dead_start_cur < c->dead_start_alt ? 4ull : 0) |
                                    ((unsigned long long)(c->ring_pos % kCounterRing) << 3) | (occ_class << 8) |
-                                   (c->com_valid ? 1ull << 62 : 0);  // does the step start with k_com?
+                                   (c->cs_cur < c->cs_alt ? 16ull : 0) |  // (the merge of upload pieces swaps the cell_start tables alone)
+                                   (c->com_valid ? 1ull << 62 : 0) |  // does the step start with k_com?
+                                   (c->acc0 ? 1ull << 61 : 0);        // ... and are its force sums already there?
     bool com_after = false;
     cudaGraphExec_t exec = nullptr;
     for (auto &sg : c->graphs)

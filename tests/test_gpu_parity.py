@@ -340,8 +340,12 @@ def test_upload_pieces_match_full_sort(case, monkeypatch):
     seed, side, nc, n, steps, piece = case
     monkeypatch.setenv("PARSIM_STAGE_PIECE", str(piece))
     res = {}
-    for mode in ("pieces", "full"):
-        monkeypatch.setenv("PARSIM_PIECE_SORT", "1" if mode == "pieces" else "0")
+    # "pieces": the default -- with more than one piece the velocity arrays travel LAST and the merge,
+    # the centres of mass and the force sums of the first timestep run under their copy
+    # (rank_upload_chunk / upload_prestep); "early": velocities with every piece (PARSIM_VEL_LATE=0)
+    for mode in ("pieces", "early", "full"):
+        monkeypatch.setenv("PARSIM_PIECE_SORT", "0" if mode == "full" else "1")
+        monkeypatch.setenv("PARSIM_VEL_LATE", "0" if mode == "early" else "1")
         g = ParticleSimulation(seed, side, nc, n, options={"keep_initial": 1})
         g.debug_stage(0)
         first = g.dump()
@@ -354,12 +358,22 @@ def test_upload_pieces_match_full_sort(case, monkeypatch):
             g.simulate(steps + 1)
             res["reset"] = (first, g.result(), g.dump())
         g.close()
-    for mode in ("pieces", "reset"):
+        if mode != "full":  # straight from the upload into parsim_run (graph-replayed steps on small problems), twice
+            g = ParticleSimulation(seed, side, nc, n)
+            g.simulate(steps + 1)
+            res[mode + " run"] = (first, g.result(), g.dump())
+            g.upload(*init_particles(seed, side, nc, n))
+            g.simulate(1)
+            g.simulate(steps)
+            res[mode + " rerun"] = (first, g.result(), g.dump())
+            g.close()
+    for mode in ("pieces", "early", "reset", "pieces run", "pieces rerun", "early run", "early rerun"):
         assert res[mode][1] == res["full"][1], mode
         for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
             assert np.array_equal(res[mode][2][k], res["full"][2][k]), (mode, k)
-    for k in ("x", "y", "vx", "vy", "m", "cell", "list_rank"):
-        assert np.array_equal(res["pieces"][0][k], res["full"][0][k]), k
+    for mode in ("pieces", "early"):
+        for k in ("x", "y", "vx", "vy", "m", "cell", "list_rank"):
+            assert np.array_equal(res[mode][0][k], res["full"][0][k]), (mode, k)
 
 
 def test_close_encounters_throw_particles_far():
