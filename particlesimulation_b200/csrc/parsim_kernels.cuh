@@ -143,13 +143,19 @@ __global__ void k_rec_vel(int n, const double *__restrict__ vx, const double *__
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) reinterpret_cast<double2 *>(rec + i)[1] = make_double2(vx[i], vy[i]);
 }
-// ... and into the (cell, id)-ordered velocity array
-__global__ void k_vel_apply(int n, const unsigned *__restrict__ id, const double *__restrict__ vx,
-                            const double *__restrict__ vy, double2 *__restrict__ vel) {
+// ... and into the (cell, id)-ordered velocity array: where[slot] = position of the particle in the
+// ordered arrays (built while the velocities are still on the link), then every arriving piece of
+// (vx, vy) is scattered through it
+__global__ void k_slot_positions(int n, const unsigned *__restrict__ id, int *__restrict__ where) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n) return;
-    const unsigned s = id[p];
-    vel[p] = make_double2(__ldg(vx + s), __ldg(vy + s));
+    if (p < n) where[id[p]] = p;
+}
+__global__ void k_vel_scatter(int first, int count, const int *__restrict__ where, const double *__restrict__ vx,
+                              const double *__restrict__ vy, double2 *__restrict__ vel) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const int s = first + t;
+    vel[where[s]] = make_double2(vx[s], vy[s]);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -15,6 +15,7 @@ namespace parsim {
 static int device_scan(Rank *c, const int *in, int N, int *out, int *total2);  // parsim_step.inl
 static int sort_piece(Rank *c, int first, int cnt, int piece);                  // parsim_step.inl
 static int upload_prestep(Rank *c);                                              // parsim_step.inl
+int rank_settle_rec_vel(Rank *c);
 
 template <typename T>
 static int dev_alloc(Rank *c, T **p, size_t count, bool zero = false) {
@@ -254,6 +255,7 @@ static int reset_state(Rank *c) {
     c->n_uploaded = 0;
     const size_t C = (size_t)c->g.ncells;
     c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->com_valid = false; c->count_pending = false; c->acc0 = nullptr; c->next_stage = 0;
+    c->rec_vel_pending = false;
     c->piece_sorted = false;
     c->n_tomb = 0; c->n_grave = 0; c->steps_done = 0; c->collisions_total = 0;
     c->have_newcell = c->have_flags = false;
@@ -272,6 +274,16 @@ static int reset_state(Rank *c) {
     PS_CUDA(c, cudaMemsetAsync(c->mv_head, 0xFF, sizeof(int) * C, c->stream));
     PS_CUDA(c, cudaMemsetAsync(c->dm_head, 0xFF, sizeof(int) * C, c->stream));
     return 0;
+}
+
+// An upload with late velocities leaves the records' velocity fields for later (late_vx / late_vy
+// hold them in slot order): whoever reads the records' velocities calls this first.
+int rank_settle_rec_vel(Rank *c) {
+    if (!c->rec_vel_pending) return 0;
+    c->rec_vel_pending = false;
+    const int n = (int)c->n_part;
+    k_rec_vel<<<grid_for(n), kThreads, 0, c->stream>>>(n, c->late_vx, c->late_vy, c->rec0);
+    return check_launch(c, "k_rec_vel");
 }
 
 int rank_upload_begin(Rank *c) {
@@ -385,23 +397,32 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
             PS_ALLOC(c, c->late_vx, (size_t)c->n_part, false);
             PS_ALLOC(c, c->late_vy, (size_t)c->n_part, false);
         }
-        PS_CUDA(c, cudaMemcpyAsync(c->late_vx, vx, sizeof(double) * count, cudaMemcpyHostToDevice, c->copy_stream));
-        PS_CUDA(c, cudaMemcpyAsync(c->late_vy, vy, sizeof(double) * count, cudaMemcpyHostToDevice, c->copy_stream));
         c->n_uploaded = count;
         const bool pre = c->pieces_ok;  // (false: more pieces than tables -- the records are completed, step 0 sorts them)
+        int *where = c->mv_next;        // slot -> ordered position; free until the collision phase
         if (pre) {
             c->n_alive = c->n0 = (int)c->n_part;
             c->piece_sorted = true;
             c->slots_id_ordered = true;
             k_set_int<<<1, 1, 0, c->stream>>>(&c->d_ctr->n_next, c->n_alive);
             if (upload_prestep(c)) return 1;
+            k_slot_positions<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(c->n_alive, c->id_cur, where);
         }
+        // the velocity arrays, piece by piece: every piece is scattered into the ordered array as soon as
+        // it is there, so only the last one is not hidden behind the copy
+        for (long long off = 0; off < count; off += c->stage_cap) {
+            const int cnt = (int)std::min<long long>(c->stage_cap, count - off);
+            PS_CUDA(c, cudaMemcpyAsync(c->late_vx + off, vx + off, sizeof(double) * cnt, cudaMemcpyHostToDevice, c->copy_stream));
+            PS_CUDA(c, cudaMemcpyAsync(c->late_vy + off, vy + off, sizeof(double) * cnt, cudaMemcpyHostToDevice, c->copy_stream));
+            PS_CUDA(c, cudaEventRecord(c->ev_copied[0], c->copy_stream));
+            PS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[0], 0));
+            if (pre)
+                k_vel_scatter<<<grid_for(cnt), kThreads, 0, c->stream>>>((int)off, cnt, where, c->late_vx, c->late_vy, c->vel_cur);
+        }
+        c->rec_vel_pending = true;  // the records get theirs when somebody needs them (reset, full sort, download)
+        if (!pre && rank_settle_rec_vel(c)) return 1;
         PS_CUDA(c, cudaStreamSynchronize(c->copy_stream));  // the caller's arrays are free again
-        k_rec_vel<<<grid_for((int)count), kThreads, 0, c->stream>>>((int)count, c->late_vx, c->late_vy, c->rec0);
-        if (pre)
-            k_vel_apply<<<grid_for(c->n_alive), kThreads, 0, c->stream>>>(c->n_alive, c->id_cur, c->late_vx, c->late_vy,
-                                                                         c->vel_cur);
-        return check_launch(c, "k_vel_apply");
+        return check_launch(c, "k_vel_scatter");
     }
     // the caller's arrays are free again when this returns ("they are copied"); the ingest kernels
     // may still be running -- parsim_upload_end waits for them
@@ -444,6 +465,7 @@ int rank_reset(Rank *c) {
     PS_CUDA(c, cudaSetDevice(c->device));
     if (c->n0 <= 0 || c->uploading) return c->fail("parsim_reset: nothing uploaded yet");
     const int n0 = c->n0;
+    if (rank_settle_rec_vel(c)) return 1;  // (reset_state drops the flag)
     if (reset_state(c)) return 1;
     c->n_alive = c->n0 = n0;
     k_set_int<<<1, 1, 0, c->stream>>>(&c->d_ctr->n_next, c->n_alive);
@@ -461,6 +483,8 @@ int rank_download(Rank *c, long long capacity, unsigned *ids, double *x, double 
     *count_out = (long long)n;
     if ((long long)n > capacity) return c->fail("parsim_download: host arrays too small");
     if (!c->sorted) {  // still the uploaded records, slot order
+        if (rank_settle_rec_vel(c)) return 1;
+        PS_CUDA(c, cudaStreamSynchronize(c->stream));
         const size_t piece = 1 << 22;
         std::vector<InitRec> tmp(std::min(n, piece));
         for (size_t off = 0; off < n; off += piece) {

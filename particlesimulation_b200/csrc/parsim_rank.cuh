@@ -92,6 +92,7 @@ struct Rank {
     bool count_pending = false;  // several strips: n_alive of the coming step is still on its way (ev_ring[0], h_ring[0])
     double2 *acc0 = nullptr;     // accelerations of the coming step, taken during the upload (late velocities)
     double *late_vx = nullptr, *late_vy = nullptr;  // the velocity arrays of such an upload, slot order
+    bool rec_vel_pending = false;  // the records' velocities are still in late_vx / late_vy (written on demand: reset, full sort)
     bool opt_vel_late = true;    // PARSIM_VEL_LATE=0: velocities travel with every piece (A/B)
     bool com_valid = false;  // the merge of the last step already left this step's centres of mass (k_move<.., COM>)
     bool fuse_com = true;    // PARSIM_FUSE_COM=0: always k_com (A/B)

@@ -75,6 +75,7 @@ static int bits_for(unsigned long long max_value) {
 static int sort_initial(Rank *c) {
     const Geom &g = c->g;
     const int n = c->n_alive;
+    if (rank_settle_rec_vel(c)) return 1;  // an upload with late velocities may still owe the records theirs
     if (n == 0) {
         PS_CUDA(c, cudaMemsetAsync(c->cs_cur, 0, sizeof(int) * ((size_t)g.ncells + 1), c->stream));
         return 0;
