@@ -304,7 +304,7 @@ def main_ours(a):
         if world == 1:
             sim.upload_ptrs([t.data_ptr() for t in pinned])
         else:
-            sim.upload_strip_ptrs(cnt, pinned_ids.data_ptr(), [t.data_ptr() for t in pinned])
+            sim.upload_whole_strip_ptrs(cnt, pinned_ids.data_ptr(), [t.data_ptr() for t in pinned])  # collective
         upload_s[0] += time.perf_counter() - t_up  # parsim_upload returns when the records are on the device
         sim.simulate(nstep)
         return sim.result()

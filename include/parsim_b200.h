@@ -84,6 +84,16 @@ int parsim_upload_end(parsim_ctx *ctx);
  * its own strip's particles in host memory); same begin/end bracket. */
 int parsim_upload_chunk_ids(parsim_ctx *ctx, long long count, const unsigned *ids, const double *x,
                             const double *y, const double *vx, const double *vy, const double *m);
+/* The WHOLE strip of this rank in one call (begin + chunk_ids + end), for one-process-per-GPU jobs
+ * (what mpi/parsim-mpi.cpp:338-342 does with MPI_Scatterv of the initial particles, here from each
+ * rank's own host memory).  On a context created with parsim_create_rank* and more than one rank the
+ * call is COLLECTIVE -- every rank makes it, like parsim_run: the strips agree that all uploads went
+ * well (one fails, all fail), bin their particles, take their centres of mass and exchange the
+ * ghost rows before it returns, and x, y, m, ids travel before vx, vy so that this work (and the
+ * force sums of the first timestep) runs while the velocities are still crossing PCIe.  The
+ * arrays are free again when it returns.  One strip per context. */
+int parsim_upload_strip(parsim_ctx *ctx, long long count, const unsigned *ids, const double *x,
+                        const double *y, const double *vx, const double *vy, const double *m);
 /* The alive particles of this context's strip, in device order, into host arrays of
  * `capacity` elements; *count = how many.  One strip per context. */
 int parsim_download(parsim_ctx *ctx, long long capacity, unsigned *ids, double *x, double *y,

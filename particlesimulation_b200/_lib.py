@@ -40,6 +40,7 @@ SIGNATURES = {
     "parsim_upload_chunk": (C.c_int, [_ctx, C.c_longlong, C.c_longlong, _dp, _dp, _dp, _dp, _dp]),
     "parsim_upload_end": (C.c_int, [_ctx]),
     "parsim_upload_chunk_ids": (C.c_int, [_ctx, C.c_longlong, C.POINTER(C.c_uint), _dp, _dp, _dp, _dp, _dp]),
+    "parsim_upload_strip": (C.c_int, [_ctx, C.c_longlong, C.POINTER(C.c_uint), _dp, _dp, _dp, _dp, _dp]),
     "parsim_download": (C.c_int, [_ctx, C.c_longlong, C.POINTER(C.c_uint), _dp, _dp, _dp, _dp, _dp,
                                   C.POINTER(C.c_longlong)]),
     "parsim_reset": (C.c_int, [_ctx]),

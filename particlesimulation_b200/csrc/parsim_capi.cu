@@ -289,6 +289,15 @@ int parsim_upload_chunk_ids(parsim_ctx *ctx, long long count, const unsigned *id
     return for_ranks(ctx, [&](Rank *c) { return rank_upload_chunk(c, 0, ids, count, x, y, vx, vy, m); });
 }
 
+int parsim_upload_strip(parsim_ctx *ctx, long long count, const unsigned *ids, const double *x, const double *y,
+                        const double *vx, const double *vy, const double *m) {
+    if (ctx->ranks.size() != 1) return ctx_fail(ctx, "parsim_upload_strip: one strip per context only (one process per GPU)");
+    if (count > 0 && (!ids || !x || !y || !vx || !vy || !m)) return ctx_fail(ctx, "parsim_upload_strip: NULL array");
+    Rank *c = ctx->ranks[0].get();
+    if (rank_upload_strip(c, count, ids, x, y, vx, vy, m)) return ctx_fail(ctx, c->err);
+    return 0;
+}
+
 int parsim_reset(parsim_ctx *ctx) { return for_ranks(ctx, rank_reset); }
 
 int parsim_download(parsim_ctx *ctx, long long capacity, unsigned *ids, double *x, double *y, double *vx,

@@ -328,7 +328,9 @@ __global__ void __launch_bounds__(kThreads)
 k_ingest_strip(Geom g, long long id_base, const unsigned *__restrict__ ids, int count,
                const double *__restrict__ x, const double *__restrict__ y, const double *__restrict__ vx,
                const double *__restrict__ vy, const double *__restrict__ m, int capacity,
-               int *__restrict__ blk, InitRec *rec, Counters *ctr) {
+               int *__restrict__ blk, InitRec *rec, Counters *ctr, int *__restrict__ up_slot = nullptr) {
+    // up_slot (PHASE 1, optional): the slot every uploaded particle went to, -1 if another strip owns it --
+    // velocities that arrive later find their records through it (vx == nullptr: they do, rank_upload_strip)
     __shared__ int ws[33];
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     bool keep = false;
@@ -344,11 +346,36 @@ k_ingest_strip(Geom g, long long id_base, const unsigned *__restrict__ ids, int 
         if (threadIdx.x == 0) blk[blockIdx.x] = tot;
         return;
     }
-    if (!keep) return;
+    if (!keep) {
+        if (up_slot && t < count) up_slot[t] = -1;
+        return;
+    }
     const int slot = ctr->n_staged + blk[blockIdx.x] + rank;
-    if (slot >= capacity) { ctr->error = DE_CAPACITY; return; }
+    if (slot >= capacity) {
+        ctr->error = DE_CAPACITY;
+        if (up_slot) up_slot[t] = -1;
+        return;
+    }
+    if (up_slot) up_slot[t] = slot;
     const unsigned pid = ids ? ids[t] : (unsigned)(id_base + t);
-    store_rec(rec, slot, make_double2(x[t], py), make_double2(vx[t], vy[t]), m[t], pid);
+    store_rec(rec, slot, make_double2(x[t], py), vx ? make_double2(vx[t], vy[t]) : make_double2(0.0, 0.0), m[t], pid);
+}
+
+// Late velocities of a strip upload (upload order, up_slot from k_ingest_strip): into the ordered
+// velocity array through where[slot] = ordered position (k_sort_gather), and into the records
+__global__ void k_vel_scatter_strip(int first, int count, const int *__restrict__ up_slot, const int *__restrict__ where,
+                                    const double *__restrict__ vx, const double *__restrict__ vy, double2 *__restrict__ vel) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const int s = up_slot[first + t];
+    if (s >= 0) vel[where[s]] = make_double2(vx[first + t], vy[first + t]);
+}
+__global__ void k_rec_vel_strip(int count, const int *__restrict__ up_slot, const double *__restrict__ vx,
+                                const double *__restrict__ vy, InitRec *rec) {
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    const int s = up_slot[t];
+    if (s >= 0) reinterpret_cast<double2 *>(rec + s)[1] = make_double2(vx[t], vy[t]);
 }
 
 __global__ void k_advance_staged(Counters *ctr, const int *total) { ctr->n_staged += *total; }

@@ -15,6 +15,7 @@ namespace parsim {
 static int device_scan(Rank *c, const int *in, int N, int *out, int *total2);  // parsim_step.inl
 static int sort_piece(Rank *c, int first, int cnt, int piece);                  // parsim_step.inl
 static int upload_prestep(Rank *c);                                              // parsim_step.inl
+static int upload_prestep_strip(Rank *c, bool late, int **where_out);            // parsim_step.inl
 int rank_settle_rec_vel(Rank *c);
 
 template <typename T>
@@ -238,6 +239,7 @@ void rank_destroy(Rank *c) {
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
     for (auto &sg : c->graphs) cudaGraphExecDestroy(sg.exec);
     c->graphs.clear();
+    if (c->up_slot) cudaFree(c->up_slot);
     if (c->late_vx) cudaFree(c->late_vx);
     if (c->late_vy) cudaFree(c->late_vy);
     if (c->h_ring) cudaFreeHost(c->h_ring);
@@ -255,7 +257,7 @@ static int reset_state(Rank *c) {
     c->n_uploaded = 0;
     const size_t C = (size_t)c->g.ncells;
     c->n_alive = 0; c->n_guest = 0; c->sorted = false; c->com_valid = false; c->count_pending = false; c->acc0 = nullptr; c->next_stage = 0;
-    c->rec_vel_pending = false;
+    c->rec_vel_pending = false; c->halo_valid = false; c->late_count = 0;
     c->piece_sorted = false;
     c->n_tomb = 0; c->n_grave = 0; c->steps_done = 0; c->collisions_total = 0;
     c->have_newcell = c->have_flags = false;
@@ -281,9 +283,26 @@ static int reset_state(Rank *c) {
 int rank_settle_rec_vel(Rank *c) {
     if (!c->rec_vel_pending) return 0;
     c->rec_vel_pending = false;
-    const int n = (int)c->n_part;
-    k_rec_vel<<<grid_for(n), kThreads, 0, c->stream>>>(n, c->late_vx, c->late_vy, c->rec0);
+    if (c->late_count > 0) {  // strip upload: upload order, through up_slot
+        const int n = (int)c->late_count;
+        k_rec_vel_strip<<<grid_for(n), kThreads, 0, c->stream>>>(n, c->up_slot, c->late_vx, c->late_vy, c->rec0);
+    } else {
+        const int n = (int)c->n_part;
+        k_rec_vel<<<grid_for(n), kThreads, 0, c->stream>>>(n, c->late_vx, c->late_vy, c->rec0);
+    }
     return check_launch(c, "k_rec_vel");
+}
+
+static int late_alloc(Rank *c, size_t count) {
+    if (count <= c->late_cap) return 0;
+    if (c->late_vx) cudaFree(c->late_vx);
+    if (c->late_vy) cudaFree(c->late_vy);
+    c->late_vx = c->late_vy = nullptr;
+    c->late_cap = 0;
+    PS_ALLOC(c, c->late_vx, count, false);
+    PS_ALLOC(c, c->late_vy, count, false);
+    c->late_cap = count;
+    return 0;
 }
 
 int rank_upload_begin(Rank *c) {
@@ -327,7 +346,7 @@ int rank_stage_alloc(Rank *c) {
 
 // `cnt` staged particles (device SoA `st`, ids `dids` or id_base + index) into this strip's records.
 // The staging arrays may live on another GPU of the process (peer access, group upload).
-int rank_ingest_piece(Rank *c, long long id_base, const unsigned *dids, int cnt, double *const st[5]) {
+int rank_ingest_piece(Rank *c, long long id_base, const unsigned *dids, int cnt, double *const st[5], int *up_slot) {
     if (c->nranks == 1) {
         PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest",
                   k_ingest<<<grid_for(cnt), kThreads, 0, c->stream>>>(
@@ -342,7 +361,7 @@ int rank_ingest_piece(Rank *c, long long id_base, const unsigned *dids, int cnt,
         PS_LAUNCH(c, K_INGEST, 84.0 * cnt, "k_ingest_strip<1>",
                   k_ingest_strip<1><<<nb, kThreads, 0, c->stream>>>(
                       c->g, id_base, dids, cnt, st[0], st[1], st[2], st[3], st[4],
-                      c->cap - 2 * c->mig_cap, c->sort_hist_scan, c->rec0, c->d_ctr));
+                      c->cap - 2 * c->mig_cap, c->sort_hist_scan, c->rec0, c->d_ctr, up_slot));
         k_advance_staged<<<1, 1, 0, c->stream>>>(c->d_ctr, c->sort_hist_scan + nb);
     }
     return 0;
@@ -393,10 +412,7 @@ int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long
         }
     }
     if (vel_late) {
-        if (!c->late_vx) {
-            PS_ALLOC(c, c->late_vx, (size_t)c->n_part, false);
-            PS_ALLOC(c, c->late_vy, (size_t)c->n_part, false);
-        }
+        if (late_alloc(c, (size_t)c->n_part)) return 1;
         c->n_uploaded = count;
         const bool pre = c->pieces_ok;  // (false: more pieces than tables -- the records are completed, step 0 sorts them)
         int *where = c->mv_next;        // slot -> ordered position; free until the collision phase
@@ -458,6 +474,79 @@ int rank_upload_end(Rank *c) {
         c->slots_id_ordered = !unordered;
     }
     return 0;
+}
+
+// parsim_upload_strip: the whole strip of this rank in ONE call.  On a multi-rank context the call is
+// COLLECTIVE (every rank makes it): the strips agree that their uploads went well, bin, take their
+// centres of mass and exchange the ghost rows before it returns, so the first timestep starts with
+// the force stage.  Where nothing forbids it (instrumentation, explicit kernel variants) x, y, m and
+// the ids of every piece travel first and the two velocity arrays last, and the binning, the centres
+// of mass, the ghost rows and the force sums of the first timestep run under their copy.
+int rank_upload_strip(Rank *c, long long count, const unsigned *ids, const double *x, const double *y,
+                      const double *vx, const double *vy, const double *m) {
+    if (c->nranks == 1 || c->bus) {  // nothing to agree on: the plain sequence
+        if (rank_upload_begin(c)) return 1;
+        if (rank_upload_chunk(c, 0, ids, count, x, y, vx, vy, m)) return 1;
+        return rank_upload_end(c);
+    }
+    if (count < 0 || !ids) return c->fail("parsim_upload_strip needs the ids of the strip's particles");
+    if (rank_upload_begin(c)) return 1;
+    if (rank_stage_alloc(c)) return 1;
+    const bool late = c->opt_vel_late && c->force_variant <= 0 && !c->opt_stats && !c->opt_sync_check && !c->dbg_acc &&
+                      count > 0;
+    if (late) {
+        if (late_alloc(c, (size_t)count)) return 1;
+        if ((size_t)count > c->up_slot_cap) {
+            if (c->up_slot) cudaFree(c->up_slot);
+            c->up_slot = nullptr;
+            c->up_slot_cap = 0;
+            PS_ALLOC(c, c->up_slot, (size_t)count, false);
+            c->up_slot_cap = (size_t)count;
+        }
+    }
+    const double *src[5] = {x, y, vx, vy, m};
+    for (long long off = 0; off < count; off += c->stage_cap) {
+        const int cnt = (int)std::min<long long>(c->stage_cap, count - off);
+        const int b = (int)(c->stage_pieces & 1);
+        double *const *st = c->stage[b];
+        if (c->stage_pieces >= 2) PS_CUDA(c, cudaStreamWaitEvent(c->copy_stream, c->ev_ingested[b], 0));
+        for (int k = 0; k < 5; k++)
+            if (!late || (k != 2 && k != 3))
+                PS_CUDA(c, cudaMemcpyAsync(st[k], src[k] + off, sizeof(double) * cnt, cudaMemcpyHostToDevice, c->copy_stream));
+        PS_CUDA(c, cudaMemcpyAsync(c->stage_ids[b], ids + off, sizeof(unsigned) * cnt, cudaMemcpyHostToDevice, c->copy_stream));
+        PS_CUDA(c, cudaEventRecord(c->ev_copied[b], c->copy_stream));
+        PS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[b], 0));
+        double *const late_set[5] = {st[0], st[1], nullptr, nullptr, st[4]};
+        if (rank_ingest_piece(c, off, c->stage_ids[b], cnt, late ? late_set : st, late ? c->up_slot + off : nullptr)) return 1;
+        PS_CUDA(c, cudaEventRecord(c->ev_ingested[b], c->stream));
+        c->stage_pieces++;
+    }
+    c->n_uploaded = count;
+    c->pieces_ok = false;
+    // what rank_upload_end does: the strip's particle count, errors, slot order
+    if (rank_upload_end(c)) {
+        // a failed strip still takes part in the agreement below, so that the others do not wait for it
+        exchange_soft_fail(c, c->err);
+    }
+    c->uploading = false;
+    int *where = nullptr;
+    if (upload_prestep_strip(c, late, &where)) return 1;
+    if (late) {
+        for (long long off = 0; off < count; off += c->stage_cap) {
+            const int cnt = (int)std::min<long long>(c->stage_cap, count - off);
+            PS_CUDA(c, cudaMemcpyAsync(c->late_vx + off, vx + off, sizeof(double) * cnt, cudaMemcpyHostToDevice, c->copy_stream));
+            PS_CUDA(c, cudaMemcpyAsync(c->late_vy + off, vy + off, sizeof(double) * cnt, cudaMemcpyHostToDevice, c->copy_stream));
+            PS_CUDA(c, cudaEventRecord(c->ev_copied[0], c->copy_stream));
+            PS_CUDA(c, cudaStreamWaitEvent(c->stream, c->ev_copied[0], 0));
+            k_vel_scatter_strip<<<grid_for(cnt), kThreads, 0, c->stream>>>((int)off, cnt, c->up_slot, where, c->late_vx,
+                                                                           c->late_vy, c->vel_cur);
+        }
+        c->late_count = count;
+        c->rec_vel_pending = true;
+        PS_CUDA(c, cudaStreamSynchronize(c->copy_stream));  // the caller's arrays are free again
+    }
+    PS_CUDA(c, cudaStreamSynchronize(c->stream));
+    return check_launch(c, "parsim_upload_strip");
 }
 
 // Restart from the uploaded state: the records in rec0 are untouched by the step loop.

@@ -92,6 +92,10 @@ struct Rank {
     bool count_pending = false;  // several strips: n_alive of the coming step is still on its way (ev_ring[0], h_ring[0])
     double2 *acc0 = nullptr;     // accelerations of the coming step, taken during the upload (late velocities)
     double *late_vx = nullptr, *late_vy = nullptr;  // the velocity arrays of such an upload, slot order
+    bool halo_valid = false;       // the ghost rows of the coming step are in place (collective strip upload)
+    int *up_slot = nullptr;        // strip upload with late velocities: slot of every uploaded particle (-1: not mine)
+    size_t up_slot_cap = 0, late_cap = 0;
+    long long late_count = 0;      // entries of late_vx / late_vy / up_slot the pending record patch covers (0: slot order, n_part)
     bool rec_vel_pending = false;  // the records' velocities are still in late_vx / late_vy (written on demand: reset, full sort)
     bool opt_vel_late = true;    // PARSIM_VEL_LATE=0: velocities travel with every piece (A/B)
     bool com_valid = false;  // the merge of the last step already left this step's centres of mass (k_move<.., COM>)
@@ -318,13 +322,15 @@ int rank_upload_begin(Rank *c);
 int rank_upload_chunk(Rank *c, long long id_base, const unsigned *ids, long long count, const double *x,
                       const double *y, const double *vx, const double *vy, const double *m);
 int rank_stage_alloc(Rank *c);
-int rank_ingest_piece(Rank *c, long long id_base, const unsigned *dids, int cnt, double *const st[5]);
+int rank_ingest_piece(Rank *c, long long id_base, const unsigned *dids, int cnt, double *const st[5], int *up_slot = nullptr);
 int rank_reset(Rank *c);
 int rank_download(Rank *c, long long capacity, unsigned *ids, double *x, double *y, double *vx,
                   double *vy, double *m, long long *count_out);
 int rank_fp64_peak(Rank *c, double *tflops);
 int rank_pair_peak(Rank *c, double *pairs_per_s);
 int rank_upload_end(Rank *c);
+int rank_upload_strip(Rank *c, long long count, const unsigned *ids, const double *x, const double *y,
+                      const double *vx, const double *vy, const double *m);
 int rank_init_device(Rank *c, long seed);
 int rank_stage(Rank *c, int stage);
 int rank_ensure_sorted(Rank *c);

@@ -169,9 +169,10 @@ __global__ void __launch_bounds__(kThreads)
 k_sort_gather(int n, int ncells, const unsigned *__restrict__ keys, const int *__restrict__ src,
               const InitRec *__restrict__ rec, double2 *__restrict__ pos_out, double2 *__restrict__ vel_out,
               double *__restrict__ m_out, unsigned *__restrict__ id_out, int *__restrict__ cell_out,
-              int *__restrict__ cell_start) {
+              int *__restrict__ cell_start, int *__restrict__ where = nullptr) {
     int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
+    if (where) where[src[p]] = p;  // slot -> ordered position (late velocities of a strip upload)
     const int c = (int)keys[p];
     const double2 *q = reinterpret_cast<const double2 *>(rec + src[p]);
     const double2 a = __ldg(q), v = __ldg(q + 1), mi = __ldg(q + 2);

@@ -72,7 +72,7 @@ static int bits_for(unsigned long long max_value) {
 
 // Step 0: bring the uploaded particles (arbitrary slots) into (cell, id) order -- the binning of
 // updateCOM (serial/parsim.cpp:265-285) done once; later steps keep the order by merging.
-static int sort_initial(Rank *c) {
+static int sort_initial(Rank *c, int *where = nullptr) {  // where (optional): slot -> ordered position
     const Geom &g = c->g;
     const int n = c->n_alive;
     if (rank_settle_rec_vel(c)) return 1;  // an upload with late velocities may still owe the records theirs
@@ -103,7 +103,7 @@ static int sort_initial(Rank *c) {
     PS_LAUNCH(c, K_SORT_GATHER, 120.0 * n + 4.0 * g.ncells, "k_sort_gather",
               k_sort_gather<<<grid_for(n), kThreads, 0, c->stream>>>(
                   n, g.ncells, keyA, srcA, c->rec0, c->pos_alt, c->vel_alt, c->m_alt, c->id_alt, c->cell_alt,
-                  c->cs_alt));
+                  c->cs_alt, where));
     std::swap(c->pos_cur, c->pos_alt);
     std::swap(c->vel_cur, c->vel_alt);
     std::swap(c->m_cur, c->m_alt);
@@ -310,9 +310,10 @@ static int stage_bin_com(Rank *c) {
         PS_LAUNCH(c, K_GHOST, 96.0 * g.nc, "k_ghost_wrap",
                   k_ghost_wrap<<<grid_for(g.nc), kThreads, 0, c->stream>>>(g, c->com_xy, c->com_m, c->d_ctr, c->d_big_count,
                                                                            c->d_move_big_count));
-    } else if (exchange_halo(c)) {
+    } else if (!c->halo_valid && exchange_halo(c)) {  // (a collective strip upload has exchanged them already)
         return 1;
     }
+    c->halo_valid = false;
     c->pos_latest = c->pos_cur;
     c->have_newcell = c->have_flags = false;
     return settle_count(c);
@@ -394,6 +395,29 @@ static int upload_prestep(Rank *c) {
     c->com_valid = true;
     if (force_acc_only(c, c->vel_alt)) return 1;  // vel_alt is free until the merge at the end of the step
     c->acc0 = c->vel_alt;
+    c->pos_latest = c->pos_cur;
+    return 0;
+}
+
+// parsim_upload_strip on a multi-rank context (COLLECTIVE): all strips agree that their uploads went
+// well, then every strip bins its particles, takes its centres of mass, exchanges the ghost rows and --
+// when its velocities travel last (`late`) -- takes the force sums of the first timestep, all of it
+// while the velocity arrays are still crossing PCIe.  *where_out: slot -> ordered position.
+static int upload_prestep_strip(Rank *c, bool late, int **where_out) {
+    const Geom &g = c->g;
+    if (exchange_final_check(c)) return 1;
+    int *where = late ? c->cell_cur : nullptr;  // the buffer that is cell_alt (free until the merge) after the sort's swap
+    if (sort_initial(c, where)) return 1;
+    c->sorted = true;
+    *where_out = where;
+    PS_LAUNCH(c, K_COM, 24.0 * c->n_alive + 24.0 * g.ncells, "k_com", launch_com_any(c));
+    if (exchange_halo(c)) return 1;
+    c->com_valid = true;
+    c->halo_valid = true;
+    if (late) {
+        if (force_acc_only(c, c->vel_alt)) return 1;
+        c->acc0 = c->vel_alt;
+    }
     c->pos_latest = c->pos_cur;
     return 0;
 }

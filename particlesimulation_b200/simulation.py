@@ -162,6 +162,12 @@ class ParticleSimulation:
             self._ctx, int(count), C.cast(C.c_void_p(id_ptr), C.POINTER(C.c_uint)), *cast))
         self._check(self.lib.parsim_upload_end(self._ctx))
 
+    def upload_whole_strip_ptrs(self, count, id_ptr, ptrs):
+        """parsim_upload_strip: this rank's whole strip in one call (collective on multi-rank contexts)."""
+        cast = [C.cast(C.c_void_p(p), C.POINTER(C.c_double)) for p in ptrs]
+        self._check(self.lib.parsim_upload_strip(
+            self._ctx, int(count), C.cast(C.c_void_p(id_ptr), C.POINTER(C.c_uint)), *cast))
+
     def download(self, capacity=None):
         """ids, x, y, vx, vy, m of the alive particles of this strip (device order)."""
         cnt = C.c_longlong()

@@ -376,6 +376,27 @@ def test_upload_pieces_match_full_sort(case, monkeypatch):
             assert np.array_equal(res[mode][0][k], res["full"][0][k]), (mode, k)
 
 
+def test_whole_strip_upload_on_a_single_rank_context():
+    """parsim_upload_strip (the one-call, collective form of the explicit-id upload) on a context with
+    one rank is the plain begin / chunk_ids / end sequence; the multi-rank form runs under torchrun in
+    tests/test_gpu_multi.py::test_bench_under_torchrun (bench.py's end-to-end leg uses it and checks the
+    result against the device-resident run)."""
+    seed, side, nc, n, steps = 4, 3.0, 30, 50000, 4
+    arrs = [np.ascontiguousarray(a) for a in init_particles(seed, side, nc, n)]
+    a = ParticleSimulation(seed, side, nc, n, arrays=arrs)
+    a.simulate(steps)
+    b = ParticleSimulation(seed, side, nc, n, upload=False)
+    ids = np.arange(n, dtype=np.uint32)
+    b.upload_whole_strip_ptrs(n, ids.ctypes.data, [x.ctypes.data for x in arrs])
+    b.simulate(steps)
+    assert a.result() == b.result()
+    da, db = a.dump(), b.dump()
+    for k in ("x", "y", "vx", "vy", "m", "alive", "cell"):
+        assert np.array_equal(da[k], db[k]), k
+    a.close()
+    b.close()
+
+
 def test_close_encounters_throw_particles_far():
     """Two particles a few 1e-6 apart fly tens of cells in one step; the result must still be the
     reference's (alive flags and collision count exact, positions to 1e-9 of the box side)."""
