@@ -489,7 +489,7 @@ int rank_upload_strip(Rank *c, long long count, const unsigned *ids, const doubl
         if (rank_upload_chunk(c, 0, ids, count, x, y, vx, vy, m)) return 1;
         return rank_upload_end(c);
     }
-    if (count < 0 || !ids) return c->fail("parsim_upload_strip needs the ids of the strip's particles");
+    if (count < 0 || (count > 0 && !ids)) return c->fail("parsim_upload_strip needs the ids of the strip's particles");
     if (rank_upload_begin(c)) return 1;
     if (rank_stage_alloc(c)) return 1;
     const bool late = c->opt_vel_late && c->force_variant <= 0 && !c->opt_stats && !c->opt_sync_check && !c->dbg_acc &&
