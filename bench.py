@@ -472,7 +472,10 @@ def main_ours(a):
                 "h2d_GBps_slowest_rank": h2d_gbs_slowest,
                 "h2d_raw_GBps_slowest_rank": h2d_raw_gbs_slowest,
                 "h2d_raw_note": "plain cudaMemcpyAsync of the same pinned buffers, all ranks at once: the platform's ceiling",
-                "inputs": "pinned host arrays of this rank's strip (x, y, vx, vy, m" + (", id" if world > 1 else "") + ")"},
+                "inputs": "pinned host arrays of this rank's strip (x, y, vx, vy, m" + (", id" if world > 1 else "") + ")",
+                "upload": ("parsim_upload_strip, collective" if world > 1 else "parsim_upload") +
+                          ": x, y, m travel first, vx, vy last; binning, centres of mass and the first timestep's force "
+                          "sums run under the velocity copy (PARSIM_VEL_LATE=0 switches that off)"},
         "gpu_launches": int(sum(v["launches"] for v in kern.values())),
         "roofline": roofline,
         "fp64": fp64, "kernels": table,
