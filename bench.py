@@ -337,7 +337,8 @@ def main_ours(a):
             raw_s = dt_raw if raw_s is None else min(raw_s, dt_raw)
     h2d_raw_gbs_slowest = 40 * cnt / max_over_ranks(raw_s) / 1e9
     del scratch
-    assert res[2] == collisions, "end-to-end run disagrees with the device-resident run"
+    # same particles, same arithmetic: the uploaded run must end where the device-resident one did, bit for bit
+    assert tuple(res) == (x0, y0, collisions), f"end-to-end run {tuple(res)} disagrees with the device-resident run {(x0, y0, collisions)}"
 
     # ---- the other BASELINE configurations, one short sub-line each (same code, same library) -----
     def side_run(label, tup, reps=3, pin_note=None):
