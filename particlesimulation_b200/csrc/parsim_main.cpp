@@ -2,9 +2,10 @@
 // parsing, output and error behaviour as the reference's main (serial/parsim.cpp:457-489):
 // stdout "x0 y0" (3 decimals) then the collision count (:450-453), stderr the wall time of
 // the step loop only ("%.1lfs", :475-479), "Error: ..." + exit 1 on failure (:484-488).
-// The initial condition is generated on the host exactly like init_particles; the step loop
-// runs on the GPU(s) through the C ABI.  PARSIM_NGPU=<n> selects the number of B200s
-// (row strips); PARSIM_DEVICE_INIT=1 generates non-negative seeds on the device instead;
+// The initial condition is init_particles': for non-negative seeds generated on the device (bit-
+// identical to the host generator; PARSIM_DEVICE_INIT=0 streams it from the host instead), for
+// negative seeds (the clustered case) on the host; the step loop runs on the GPU(s) through the
+// C ABI.  PARSIM_NGPU=<n> selects the number of B200s (row strips);
 // PARSIM_BALANCE=1 cuts the strips so that they hold equal numbers of PARTICLES (clustered
 // inputs, i.e. negative seeds) instead of equal numbers of rows.  PARSIM_TRACE=<file> writes the
 // per-particle trace the reference keeps commented out in simulate() (serial/parsim.cpp:424-431,
@@ -79,7 +80,9 @@ int main(int argc, char *argv[]) {
         } else {
             check(nullptr, parsim_create(&ctx, side_length, grid_size, n_particles, n_gpus));
         }
-        if (dev_init && std::atoi(dev_init) && seed >= 0) {
+        // non-negative seeds: the uniform generator runs on the device (xorshift32 jump-ahead, bit-identical
+        // to the host generator: tests/test_gpu_parity.py) unless PARSIM_DEVICE_INIT=0 asks for the host stream
+        if (seed >= 0 && !(dev_init && std::atoi(dev_init) == 0)) {
             check(ctx, parsim_init_device(ctx, seed));
         } else {
             // stream the generator through a bounded host buffer (8e8 particles = 32 GB otherwise)

@@ -431,10 +431,18 @@ def test_upload_arrays_path_and_errors():
     g.close()
 
 
-def test_cli_matches_reference_output():
+@pytest.mark.parametrize("host_init", [False, True], ids=["device init (default)", "PARSIM_DEVICE_INIT=0"])
+def test_cli_matches_reference_output(host_init):
+    """Non-negative seeds are generated on the device by default; PARSIM_DEVICE_INIT=0 streams the
+    host generator through parsim_upload_chunk.  Same output either way (the reference's)."""
     cli = os.path.join(ROOT, "particlesimulation_b200", "parsim")
+    env = dict(os.environ)
+    if host_init:
+        env["PARSIM_DEVICE_INIT"] = "0"
+    else:
+        env.pop("PARSIM_DEVICE_INIT", None)
     for args, exp in [("1 2 3 10 1", "1.570 0.056\n0\n"), ("1 10 100 100000 5", "7.872 0.263\n5226\n")]:
-        p = subprocess.run([cli] + args.split(), capture_output=True, text=True)
+        p = subprocess.run([cli] + args.split(), capture_output=True, text=True, env=env)
         assert p.returncode == 0, p.stderr
         assert p.stdout == exp
         assert p.stderr.strip().endswith("s")
