@@ -292,8 +292,7 @@ int parsim_upload_chunk_ids(parsim_ctx *ctx, long long count, const unsigned *id
 int parsim_upload_strip(parsim_ctx *ctx, long long count, const unsigned *ids, const double *x, const double *y,
                         const double *vx, const double *vy, const double *m) {
     if (ctx->ranks.size() != 1) return ctx_fail(ctx, "parsim_upload_strip: one strip per context only (one process per GPU)");
-    if (count > 0 && (!ids || !x || !y || !vx || !vy || !m)) return ctx_fail(ctx, "parsim_upload_strip: NULL array");
-    Rank *c = ctx->ranks[0].get();
+    Rank *c = ctx->ranks[0].get();  // (arguments are checked inside: a strip with bad ones must still reach the agreement)
     if (rank_upload_strip(c, count, ids, x, y, vx, vy, m)) return ctx_fail(ctx, c->err);
     return 0;
 }

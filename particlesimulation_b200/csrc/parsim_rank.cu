@@ -485,15 +485,20 @@ int rank_upload_end(Rank *c) {
 int rank_upload_strip(Rank *c, long long count, const unsigned *ids, const double *x, const double *y,
                       const double *vx, const double *vy, const double *m) {
     if (c->nranks == 1 || c->bus) {  // nothing to agree on: the plain sequence
+        if (count < 0 || (count > 0 && (!ids || !x || !y || !vx || !vy || !m))) return c->fail("parsim_upload_strip: NULL array");
         if (rank_upload_begin(c)) return 1;
         if (rank_upload_chunk(c, 0, ids, count, x, y, vx, vy, m)) return 1;
         return rank_upload_end(c);
     }
-    if (count < 0 || (count > 0 && !ids)) return c->fail("parsim_upload_strip needs the ids of the strip's particles");
+    // Whatever goes wrong on THIS strip before the agreement (bad arguments, allocation, capacity) must not
+    // keep it from the agreement: the other strips would wait for it there.
+    bool late = false;
+    auto phase_a = [&]() -> int {
+    if (count < 0 || (count > 0 && (!ids || !x || !y || !vx || !vy || !m)))
+        return c->fail("parsim_upload_strip: NULL array (ids, x, y, vx, vy, m of the strip's particles)");
     if (rank_upload_begin(c)) return 1;
     if (rank_stage_alloc(c)) return 1;
-    const bool late = c->opt_vel_late && c->force_variant <= 0 && !c->opt_stats && !c->opt_sync_check && !c->dbg_acc &&
-                      count > 0;
+    late = c->opt_vel_late && c->force_variant <= 0 && !c->opt_stats && !c->opt_sync_check && !c->dbg_acc && count > 0;
     if (late) {
         if (late_alloc(c, (size_t)count)) return 1;
         if ((size_t)count > c->up_slot_cap) {
@@ -523,11 +528,9 @@ int rank_upload_strip(Rank *c, long long count, const unsigned *ids, const doubl
     }
     c->n_uploaded = count;
     c->pieces_ok = false;
-    // what rank_upload_end does: the strip's particle count, errors, slot order
-    if (rank_upload_end(c)) {
-        // a failed strip still takes part in the agreement below, so that the others do not wait for it
-        exchange_soft_fail(c, c->err);
-    }
+    return rank_upload_end(c);  // the strip's particle count, errors, slot order
+    };
+    if (phase_a()) exchange_soft_fail(c, c->err);
     c->uploading = false;
     int *where = nullptr;
     if (upload_prestep_strip(c, late, &where)) return 1;

@@ -213,6 +213,49 @@ def test_bad_strip_rows_are_rejected():
             ParticleSimulation(1, 1.0, 10, 100, n_gpus=2, first_rows=rows)
 
 
+def _torchrun_upload_worker(tmp_path, mode, case, port):
+    seed, side, nc, n, steps = case
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tests", "_nccl_upload_worker.py"), str(tmp_path), mode,
+           str(seed), str(side), str(nc), str(n), str(steps)]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    outs = []
+    for r in range(2):
+        f = os.path.join(str(tmp_path), f"rank{r}.json")
+        assert os.path.exists(f), (p.returncode, p.stderr[-3000:])
+        outs.append(json.load(open(f)))
+    return outs
+
+
+@pytest.mark.parametrize("case", [(1, 10.0, 100, 200000, 5), (5, 1.0, 20, 50000, 4)], ids=lambda c: " ".join(map(str, c)))
+def test_collective_strip_upload_matches_one_gpu(case, tmp_path):
+    """parsim_upload_strip, one process per GPU over NCCL: every rank hands over its strip in one
+    collective call (ids, x, y, m first; binning, centres of mass, ghost rows and the first force sums
+    under the copy of vx, vy), twice in a row on the same contexts; same result as one GPU, bit for bit."""
+    if ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    seed, side, nc, n, steps = case
+    one = ParticleSimulation(seed, side, nc, n)
+    one.simulate(steps)
+    want = list(one.result())
+    one.close()
+    outs = _torchrun_upload_worker(tmp_path, "ok", case, 29551)
+    assert sum(o["count"] for o in outs) == n
+    for o in outs:
+        assert "error" not in o, o
+        assert o["result"] == want, (o, want)
+
+
+def test_collective_strip_upload_fails_on_every_rank_together(tmp_path):
+    """Rank 1 hands in a NULL id array: its own call fails, and rank 0 -- whose upload was fine --
+    must come back with an error too instead of waiting for rank 1 in the ghost-row exchange."""
+    if ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    outs = _torchrun_upload_worker(tmp_path, "fail", (1, 10.0, 100, 200000, 3), 29552)
+    assert "NULL array" in outs[1].get("error", ""), outs
+    assert "strip 1" in outs[0].get("error", ""), outs
+
+
 @pytest.mark.parametrize("n_gpus", [2, 4, 8])
 def test_bench_under_torchrun(n_gpus):
     if ngpu() < n_gpus:
