@@ -472,7 +472,8 @@ def main_ours(a):
                 "d2h_bytes_per_step": 24, "ms_per_step": 1e3 * e2e_s / a.steps,
                 "h2d_GBps_slowest_rank": h2d_gbs_slowest,
                 "h2d_raw_GBps_slowest_rank": h2d_raw_gbs_slowest,
-                "h2d_raw_note": "plain cudaMemcpyAsync of the same pinned buffers, all ranks at once: the platform's ceiling",
+                "h2d_raw_note": "plain cudaMemcpyAsync of the same pinned buffers, all ranks at once, best of two: what the host "
+                                "delivers to concurrent copies at that moment (a reference point for the upload rate, not a bound)",
                 "inputs": "pinned host arrays of this rank's strip (x, y, vx, vy, m" + (", id" if world > 1 else "") + ")",
                 "upload": ("parsim_upload_strip, collective" if world > 1 else "parsim_upload") +
                           ": x, y, m travel first, vx, vy last; binning, centres of mass and the first timestep's force "
