@@ -360,6 +360,16 @@ def test_upload_pieces_match_full_sort(case, monkeypatch):
         g.close()
         if mode != "full":  # straight from the upload into parsim_run (graph-replayed steps on small problems), twice
             g = ParticleSimulation(seed, side, nc, n)
+            # what was uploaded comes back (download and dump right after the upload: velocities included)
+            arrs0 = init_particles(seed, side, nc, n)
+            got = g.download()
+            order = np.argsort(got[0], kind="stable")
+            assert np.array_equal(got[0][order], np.arange(n, dtype=np.uint32)), mode
+            for a0, a1 in zip(arrs0, got[1:]):
+                assert np.array_equal(np.asarray(a0), a1[order]), mode
+            d0 = g.dump()
+            for k, a0 in zip(("x", "y", "vx", "vy", "m"), arrs0):
+                assert np.array_equal(d0[k], np.asarray(a0)), (mode, k)
             g.simulate(steps + 1)
             res[mode + " run"] = (first, g.result(), g.dump())
             g.upload(*init_particles(seed, side, nc, n))
