@@ -61,13 +61,6 @@ int rank_create(Rank *c, double side, long ncside, long long n_part, int rank, i
     PS_CUDA(c, cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
     PS_CUDA(c, cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device));
     c->bus = nranks > 1 ? bus : nullptr;
-    if (const char *e = getenv("PARSIM_L2_FETCH")) {  // experiment: L2 fetch granularity hint (32 / 64 / 128 bytes)
-        size_t before = 0, after = 0;
-        cudaDeviceGetLimit(&before, cudaLimitMaxL2FetchGranularity);
-        cudaError_t rc = cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, (size_t)atoi(e));
-        cudaDeviceGetLimit(&after, cudaLimitMaxL2FetchGranularity);
-        fprintf(stderr, "parsim: L2 fetch granularity %zu -> %zu (%s)\n", before, after, cudaGetErrorString(rc));
-    }
 
     Geom &g = c->g;
     g.side = side;
